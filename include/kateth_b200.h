@@ -1,0 +1,131 @@
+/*
+ * kateth_b200.h -- C ABI of the B200-native KZG engine (libkateth_b200.so).
+ *
+ * Drop-in boundary for kateth's EIP-4844 path.  kateth has no FFI of its own; its public surface is the seven
+ * `pub fn`s of `Setup<4096, 65>` (/root/reference/src/kzg/setup.rs:46,96,167,177,185,208,247) plus
+ * `Compress::compress` (/root/reference/src/bls.rs:55-65) that callers use to obtain bytes.  Each entry point
+ * below names the reference function it replaces; INTEGRATION.md shows the Rust `extern "C"` block and the
+ * `Setup` wrapper a kateth maintainer would add.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; the caller owns every host buffer, the library copies.
+ *   - blobs: n contiguous 131072-byte blobs (4096 big-endian 32-byte field elements each).
+ *   - G1 points travel as the 48-byte ZCash compressed encoding (the parity criterion of kateth's tests);
+ *     scalars as 32-byte big-endian.
+ *   - every function returns 0 on success, a positive KB200_E_* code mirroring kateth's error enums
+ *     (kzg::Error / blob::Error / bls::Error, /root/reference/src/kzg/mod.rs:15-31, src/blob.rs:6-16,
+ *     src/bls.rs:21-50), or a negative code for CUDA / internal failures.  `Ok(false)` is *ok = 0 with return 0.
+ *   - batch calls also fill `status[i]` per item (0 or a KB200_E_* code); the function's return value is the first
+ *     non-zero status in kateth's evaluation order (all blobs, then all commitments, then all proofs).
+ *   - `*_device` variants take device pointers (data already resident in HBM, 16-byte aligned) and run on the
+ *     stream set by kb200_set_stream (default: the legacy default stream); they return after enqueueing AND
+ *     synchronising that stream unless noted.
+ *   - no function aborts or throws across the ABI.  A handle may be used from one host thread at a time.
+ *   - there is NO CPU fallback: without a CUDA device kb200_setup_load_* returns KB200_E_CUDA.
+ */
+#ifndef KATETH_B200_H
+#define KATETH_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KB200_FIELD_ELEMENTS_PER_BLOB 4096
+#define KB200_BYTES_PER_BLOB 131072
+#define KB200_BYTES_PER_G1 48
+#define KB200_BYTES_PER_G2 96
+#define KB200_BYTES_PER_SCALAR 32
+#define KB200_RECORD_BYTES 320 /* per-GPU partial of batch verification: 3 affine G1 sums + 1 Fr */
+
+/* status codes */
+#define KB200_OK 0
+#define KB200_E_INVALID_LEN 1              /* blob::Error::InvalidLen */
+#define KB200_E_INVALID_FIELD_ELEMENT 2    /* blob::Error::InvalidFieldElement */
+#define KB200_E_G1_INVALID_ENCODING 3      /* ECGroupError::InvalidEncoding */
+#define KB200_E_G1_NOT_ON_CURVE 4          /* ECGroupError::NotOnCurve */
+#define KB200_E_G1_NOT_IN_GROUP 5          /* ECGroupError::NotInGroup */
+#define KB200_E_SCALAR_INVALID_ENCODING 6  /* FiniteFieldError::InvalidEncoding */
+#define KB200_E_SCALAR_NOT_IN_FIELD 7      /* FiniteFieldError::NotInFiniteField */
+#define KB200_E_CUDA (-1)                  /* CUDA runtime error (kb200_last_error has the text) */
+#define KB200_E_IO (-2)                    /* LoadSetupError::Io */
+#define KB200_E_PARSE (-3)                 /* LoadSetupError::Serde */
+#define KB200_E_SETUP_G1_LEN (-10)         /* LoadSetupError::InvalidLenG1Lagrange */
+#define KB200_E_SETUP_G2_LEN (-11)         /* LoadSetupError::InvalidLenG2Monomial */
+#define KB200_E_ARG (-20)                  /* null pointer / bad argument */
+
+typedef struct kb200_setup kb200_setup;
+
+/* ---- Setup::load_json (/root/reference/src/kzg/setup.rs:46-82) ----
+ * Parses {"g1_lagrange": [4096 x "0x" + 96 hex], "g2_monomial": [65 x "0x" + 192 hex]}, validates every point
+ * (curve + subgroup; G1 on the GPU, G2 on the host), bit-reverses the Lagrange points, builds the roots-of-unity
+ * table and the fixed-base window table on `device`.  window_bits: 0 = default (13 -> 32 GB table), else 8..14. */
+int kb200_setup_load_json(const char* path, int device, int window_bits, kb200_setup** out);
+/* Same from decoded bytes: n_g1 x 48 bytes, n_g2 x 96 bytes. */
+int kb200_setup_load_raw(const uint8_t* g1_lagrange48, size_t n_g1, const uint8_t* g2_monomial96, size_t n_g2, int device, int window_bits,
+                         kb200_setup** out);
+void kb200_setup_free(kb200_setup* s);
+/* Stream for all later work on this handle (a cudaStream_t passed as void*; NULL = default stream). */
+int kb200_set_stream(kb200_setup* s, void* cuda_stream);
+const char* kb200_last_error(void);
+
+/* ---- Setup::blob_to_commitment (src/kzg/setup.rs:167-171) + Compress::compress; n = 1 is the reference call ---- */
+int kb200_blob_to_commitment(kb200_setup* s, const uint8_t* blobs, size_t n, uint8_t* out48, int32_t* status);
+int kb200_blob_to_commitment_device(kb200_setup* s, const void* d_blobs, size_t n, void* d_out48, int32_t* d_status);
+
+/* ---- Setup::blob_proof (src/kzg/setup.rs:177-183) + compress ---- */
+int kb200_compute_blob_proof(kb200_setup* s, const uint8_t* blobs, const uint8_t* commitments48, size_t n, uint8_t* out48, int32_t* status);
+int kb200_compute_blob_proof_device(kb200_setup* s, const void* d_blobs, const void* d_commitments48, size_t n, void* d_out48, int32_t* d_status);
+
+/* ---- Setup::proof (src/kzg/setup.rs:185-194): (proof, y) at caller-supplied points z ---- */
+int kb200_compute_proof(kb200_setup* s, const uint8_t* blobs, const uint8_t* z32, size_t n, uint8_t* out_proof48, uint8_t* out_y32, int32_t* status);
+int kb200_compute_proof_device(kb200_setup* s, const void* d_blobs, const void* d_z32, size_t n, void* d_out_proof48, void* d_out_y32,
+                               int32_t* d_status);
+
+/* ---- Setup::verify_proof (src/kzg/setup.rs:96-113); argument order proof, commitment, point, eval as in kateth ---- */
+int kb200_verify_proof(kb200_setup* s, const uint8_t proof48[48], const uint8_t commitment48[48], const uint8_t z32[32], const uint8_t y32[32],
+                       int* ok);
+/* ---- private Setup::verify_proof_batch (src/kzg/setup.rs:115-161): one RLC check over n (proof, commitment, z, y) ---- */
+int kb200_verify_proof_batch(kb200_setup* s, const uint8_t* proofs48, const uint8_t* commitments48, const uint8_t* z32, const uint8_t* y32, size_t n,
+                             int* ok, int32_t* status);
+/* ---- Setup::verify_blob_proof (src/kzg/setup.rs:208-221) ---- */
+int kb200_verify_blob_proof(kb200_setup* s, const uint8_t* blob, const uint8_t commitment48[48], const uint8_t proof48[48], int* ok);
+/* ---- Setup::verify_blob_proof_batch (src/kzg/setup.rs:247-275); n = 0 -> *ok = 1 ---- */
+int kb200_verify_blob_proof_batch(kb200_setup* s, const uint8_t* blobs, const uint8_t* commitments48, const uint8_t* proofs48, size_t n, int* ok,
+                                  int32_t* status);
+int kb200_verify_blob_proof_batch_device(kb200_setup* s, const void* d_blobs, const void* d_commitments48, const void* d_proofs48, size_t n, int* ok,
+                                         int32_t* d_status);
+
+/* ---- multi-GPU batch verification: each rank computes the partial of its contiguous shard
+ *      [index_offset, index_offset + n_local) of a batch of n_total, the KB200_RECORD_BYTES records are exchanged with
+ *      one all-gather (NCCL over NVLink, done by the caller), and any rank finishes.  d_record: device memory. ---- */
+int kb200_verify_blob_proof_batch_partial_device(kb200_setup* s, const void* d_blobs, const void* d_commitments48, const void* d_proofs48,
+                                                 size_t n_local, size_t index_offset, size_t n_total, void* d_record, int32_t* d_status);
+/* d_records: n_records x KB200_RECORD_BYTES in device memory. */
+int kb200_verify_batch_finish_device(kb200_setup* s, const void* d_records, size_t n_records, int* ok);
+/* The two compressed G1 operands of the final pairing check of the last finish call (for diffing intermediate sums). */
+int kb200_last_pairing_operands(kb200_setup* s, uint8_t lhs48[48], uint8_t rhs48[48]);
+
+/* ---- introspection ---- */
+typedef struct {
+    int window_bits, windows;
+    uint64_t table_bytes;      /* fixed-base table resident in HBM */
+    uint64_t kernel_launches;  /* kernels launched by this handle since load */
+    int device, sm_count;
+    double setup_seconds;
+} kb200_info;
+int kb200_get_info(kb200_setup* s, kb200_info* info);
+
+/* ---- unit-test hooks (device field arithmetic against the oracle; not part of the kateth surface) ---- */
+int kb200_test_fp_mul(const uint32_t* a, const uint32_t* b, uint32_t* out, size_t n); /* n x 12 limbs, Montgomery */
+int kb200_test_fr_mul(const uint32_t* a, const uint32_t* b, uint32_t* out, size_t n); /* n x 8 limbs */
+int kb200_test_g1_decompress(kb200_setup* s, const uint8_t* in48, size_t n, int32_t* status, uint8_t* recompressed48);
+int kb200_test_mac_peak(int iters, double* tmacs_wide, double* tmacs_lohi);            /* K0: IMAD microbenchmark */
+/* host pairing alone: e(a1, [tau]_2) == e(b1, G2) for plain little-endian affine coordinates (12 x u32 each) */
+int kb200_test_host_pairing(kb200_setup* s, const uint32_t* a_xy24, int a_inf, const uint32_t* b_xy24, int b_inf, int* ok);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,692 @@
+// engine.cu -- C ABI of the B200-native KZG engine (include/kateth_b200.h): setup loading, workspace, kernel
+// sequencing for commit / prove / verify, and the hand-off of the final two-pairing check to the host bls module.
+// Mirrors the seven pub fns of kateth's Setup (/root/reference/src/kzg/setup.rs:46,96,167,177,185,208,247).
+// There is no CPU fallback anywhere in this file: every path launches the sm_100a kernels or fails.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <string>
+#include <vector>
+#include <chrono>
+
+#include "../../include/kateth_b200.h"
+#include "verify.cuh"
+#include "host_bls.hpp"
+
+using namespace kb200;
+
+static thread_local char g_err[512] = "";
+extern "C" const char* kb200_last_error(void) { return g_err; }
+#define CU(call)                                                                                          \
+    do {                                                                                                  \
+        cudaError_t e_ = (call);                                                                          \
+        if (e_ != cudaSuccess) {                                                                          \
+            snprintf(g_err, sizeof g_err, "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+            return KB200_E_CUDA;                                                                          \
+        }                                                                                                 \
+    } while (0)
+
+// grow-only device buffer
+struct DBuf {
+    void* p = nullptr; size_t cap = 0;
+    int ensure(size_t bytes) {
+        if (bytes <= cap) return 0;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        cudaError_t e = cudaMalloc(&p, bytes);
+        if (e != cudaSuccess) { snprintf(g_err, sizeof g_err, "cudaMalloc(%zu): %s", bytes, cudaGetErrorString(e)); return KB200_E_CUDA; }
+        cap = bytes; return 0;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <class T> T* as() { return reinterpret_cast<T*>(p); }
+};
+
+struct kb200_setup {
+    int device = 0, sm_count = 148;
+    cudaStream_t stream = 0;
+    G1Affine* d_bases = nullptr;     // g1_lagrange_brp, affine Montgomery   (src/kzg/setup.rs:39)
+    Fr* d_roots = nullptr;           // roots_of_unity_brp, Montgomery       (src/kzg/setup.rs:41)
+    uint4* d_table = nullptr;        // fixed-base window table (msm.cuh)
+    MsmTable tab{};
+    uint64_t table_bytes = 0;
+    host::G2Prepared tau_prep, g2_prep;   // g2_monomial[1] and the G2 generator, Miller lines precomputed
+    uint64_t launches = 0;
+    double setup_seconds = 0;
+    // workspace (per chunk)
+    DBuf blobs, c48, p48, zy32, out48, out32, st_blob, st_a, st_b, status, z, y, prod, indom, q, partials, aff_c, aff_p, rlc_part, rlc_s, rmont,
+        records, combine;
+    uint8_t last_lhs[48], last_rhs[48];
+    bool have_last = false;
+};
+
+#define LAUNCH(s, kern, grid, block, ...)                   \
+    do {                                                    \
+        kern<<<grid, block, 0, (s)->stream>>>(__VA_ARGS__); \
+        (s)->launches++;                                    \
+    } while (0)
+
+static const size_t CHUNK = 4096;   // blobs per internal pass (bounds the quotient scratch to 512 MiB)
+
+static int init_consts() {
+    DevConsts h;
+    using namespace kb200::consts;
+    memcpy(h.fp_mod, H_FP_P, 48); memcpy(h.fp_one, H_FP_ONE, 48); memcpy(h.fp_r2, H_FP_R2, 48); memcpy(h.fp_b4, H_FP_B4, 48);
+    memcpy(h.fp_half, H_FP_HALF, 48); memcpy(h.fp_sqrt_exp, H_FP_SQRT_EXP, 48); memcpy(h.fp_pm2, H_FP_PM2, 48); memcpy(h.fp_beta, H_FP_BETA, 48);
+    memcpy(h.fr_one, H_FR_ONE, 32); memcpy(h.fr_r2, H_FR_R2, 32); memcpy(h.fr_rm2, H_FR_RM2, 32); memcpy(h.fr_omega, H_FR_OMEGA, 32);
+    memcpy(h.fr_ninv, H_FR_NINV, 32); memcpy(h.fr_mod, H_FR_R, 32);
+    memcpy(h.g1_gen_x, H_G1_GEN_X, 48); memcpy(h.g1_gen_y, H_G1_GEN_Y, 48); memcpy(h.g1_neg_gen_y, H_G1_NEG_GEN_Y, 48);
+    CU(cudaMemcpyToSymbol(c_k, &h, sizeof h));
+    return 0;
+}
+
+// ------------------------------------------------------------------ small glue kernels
+__global__ void k_brp_permute(const G1Affine* in, G1Affine* out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < KB_N) out[i] = in[brp12(i)];
+}
+// status[i] = first non-zero of a[i], b[i], c[i] (kateth's per-item evaluation order: blob, commitment, proof)
+__global__ void k_merge_status(const int32_t* a, const int32_t* b, const int32_t* c, int n, int32_t* out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int32_t v = a ? a[i] : 0;
+    if (v == 0 && b) v = b[i];
+    if (v == 0 && c) v = c[i];
+    out[i] = v;
+}
+__global__ void k_store_scalars_be(const Fr* in, int n, const int32_t* status, uint32_t* out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Fr v = in[i];
+    if (status[i] != 0) fr_zero(v);
+    fr_store_be(out + (size_t)i * 8, v);
+}
+// unit-test kernels (K1)
+__global__ void k_test_fp_mul(const Fp* a, const Fp* b, Fp* o, int n) { int i = blockIdx.x * blockDim.x + threadIdx.x; if (i < n) { Fp r; fp_mul(r, a[i], b[i]); o[i] = r; } }
+__global__ void k_test_fr_mul(const Fr* a, const Fr* b, Fr* o, int n) { int i = blockIdx.x * blockDim.x + threadIdx.x; if (i < n) { Fr r; fr_mul(r, a[i], b[i]); o[i] = r; } }
+__global__ void k_test_compress(const G1Affine* in, int n, const int32_t* status, uint32_t* out48) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t w[12];
+    if (status[i] != 0) { for (int k = 0; k < 12; k++) w[k] = 0; } else g1_compress(w, in[i]);
+    for (int k = 0; k < 12; k++) out48[(size_t)i * 12 + k] = w[k];
+}
+// K0: integer multiply-add peak.  (a) 16 independent mad.wide.u32 chains per thread; (b) a chain of Fp products.
+__global__ void __launch_bounds__(256) k_mac_wide(uint64_t* out, int iters, uint32_t seed) {
+    uint64_t acc[16];
+    uint32_t a = seed + threadIdx.x, b = seed * 2654435761u + blockIdx.x;
+#pragma unroll
+    for (int k = 0; k < 16; k++) acc[k] = k;
+#pragma unroll 1
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int k = 0; k < 16; k++) asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc[k]) : "r"(a), "r"(b));
+    }
+    uint64_t s = 0;
+#pragma unroll
+    for (int k = 0; k < 16; k++) s ^= acc[k];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+__global__ void __launch_bounds__(256) k_mac_fpmul(Fp* out, int iters, uint32_t seed) {
+    Fp a, b;
+    for (int k = 0; k < 12; k++) { a.l[k] = seed + threadIdx.x + k; b.l[k] = seed * 31 + blockIdx.x + k; }
+    a.l[11] &= 0x0fffffff; b.l[11] &= 0x0fffffff;
+#pragma unroll 1
+    for (int it = 0; it < iters; it++) { fp_mul(a, a, b); fp_mul(b, b, a); }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = a;
+}
+
+// ------------------------------------------------------------------ setup loading
+static int hexval(int c) { if (c >= '0' && c <= '9') return c - '0'; if (c >= 'a' && c <= 'f') return c - 'a' + 10; if (c >= 'A' && c <= 'F') return c - 'A' + 10; return -1; }
+// Pull the array of "0x.."-strings stored under `key`.  Each string is hex-decoded (src/bytes.rs:30-37).
+static int json_hex_array(const std::string& doc, const char* key, std::vector<std::vector<uint8_t>>& out) {
+    std::string k = std::string("\"") + key + "\"";
+    size_t p = doc.find(k);
+    if (p == std::string::npos) return KB200_E_PARSE;
+    p = doc.find('[', p);
+    if (p == std::string::npos) return KB200_E_PARSE;
+    for (p++;;) {
+        while (p < doc.size() && (doc[p] == ' ' || doc[p] == '\n' || doc[p] == '\r' || doc[p] == '\t' || doc[p] == ',')) p++;
+        if (p >= doc.size()) return KB200_E_PARSE;
+        if (doc[p] == ']') return 0;
+        if (doc[p] != '"') return KB200_E_PARSE;
+        size_t e = doc.find('"', p + 1);
+        if (e == std::string::npos) return KB200_E_PARSE;
+        size_t b = p + 1;
+        if (e - b >= 2 && doc[b] == '0' && (doc[b + 1] == 'x' || doc[b + 1] == 'X')) b += 2;
+        if ((e - b) & 1) return KB200_E_PARSE;
+        std::vector<uint8_t> v((e - b) / 2);
+        for (size_t i = 0; i < v.size(); i++) {
+            int h = hexval(doc[b + 2 * i]), l = hexval(doc[b + 2 * i + 1]);
+            if (h < 0 || l < 0) return KB200_E_PARSE;
+            v[i] = (uint8_t)(h * 16 + l);
+        }
+        out.push_back(std::move(v));
+        p = e + 1;
+    }
+}
+
+static int first_nonzero(const std::vector<int32_t>& v) { for (int32_t x : v) if (x) return x; return 0; }
+
+static int build_setup(kb200_setup* s, const uint8_t* g1, const uint8_t* g2, int window_bits) {
+    auto t0 = std::chrono::steady_clock::now();
+    CU(cudaSetDevice(s->device));
+    cudaDeviceProp prop; CU(cudaGetDeviceProperties(&prop, s->device));
+    s->sm_count = prop.multiProcessorCount;
+    if (int rc = init_consts()) return rc;
+    // G1: decompress + subgroup-check the 4096 Lagrange points on the GPU (src/kzg/setup.rs:59-65)
+    uint32_t* d_in; G1Affine* d_pts; int32_t* d_st;
+    CU(cudaMalloc(&d_in, KB_N * 48)); CU(cudaMalloc(&d_pts, KB_N * sizeof(G1Affine))); CU(cudaMalloc(&d_st, KB_N * 4));
+    CU(cudaMemcpy(d_in, g1, KB_N * 48, cudaMemcpyHostToDevice));
+    CU(cudaMemset(d_st, 0, KB_N * 4));
+    LAUNCH(s, k_g1_decompress, KB_N / 64, 64, d_in, KB_N, d_pts, d_st);
+    std::vector<int32_t> st(KB_N);
+    CU(cudaMemcpy(st.data(), d_st, KB_N * 4, cudaMemcpyDeviceToHost));
+    cudaFree(d_in); cudaFree(d_st);
+    if (int e = first_nonzero(st)) { cudaFree(d_pts); return e; }
+    CU(cudaMalloc(&s->d_bases, KB_N * sizeof(G1Affine)));
+    LAUNCH(s, k_brp_permute, KB_N / 256, 256, d_pts, s->d_bases);
+    // G2: all 65 points are validated on the host (src/kzg/setup.rs:68-72); only [1] is ever used (:91,:158)
+    host::G2A tau, gen;
+    for (int i = 0; i < 65; i++) {
+        host::G2A q; int e = host::g2_decompress(q, g2 + 96 * i);
+        if (e) { cudaFree(d_pts); return e; }
+        if (i == 1) tau = q;
+    }
+    host::g2_generator(gen);
+    host::g2_prepare(s->tau_prep, tau); host::g2_prepare(s->g2_prep, gen);
+    // roots of unity, bit-reversed (src/kzg/setup.rs:74-75)
+    CU(cudaMalloc(&s->d_roots, KB_N * sizeof(Fr)));
+    LAUNCH(s, k_roots, KB_N / 256, 256, s->d_roots);
+    // fixed-base window table
+    int c = window_bits ? window_bits : 13;
+    if (c < 4 || c > 15) { cudaFree(d_pts); return KB200_E_ARG; }
+    int nwin = 255 / c + 1, blast = 255 - c * (nwin - 1), dlast = 1 << blast;
+    size_t rows = (size_t)(nwin - 1) * ((size_t)1 << (c - 1)) + dlast;
+    size_t bytes = rows * KB_N * sizeof(G1Affine);
+    uint4* scratch;
+    CU(cudaMalloc(&s->d_table, bytes));
+    CU(cudaMalloc(&scratch, bytes));
+    LAUNCH(s, k_table_build, (KB_N * nwin + 127) / 128, 128, s->d_table, scratch, s->d_bases, c, nwin, dlast);
+    CU(cudaStreamSynchronize(s->stream));
+    CU(cudaGetLastError());
+    cudaFree(scratch); cudaFree(d_pts);
+    s->tab.data = s->d_table; s->tab.c = c; s->tab.nwin = nwin; s->tab.dlast = dlast;
+    s->table_bytes = bytes;
+    s->setup_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    return 0;
+}
+
+extern "C" int kb200_setup_load_raw(const uint8_t* g1, size_t n_g1, const uint8_t* g2, size_t n_g2, int device, int window_bits, kb200_setup** out) {
+    if (!g1 || !g2 || !out) return KB200_E_ARG;
+    if (n_g1 != KB_N) return KB200_E_SETUP_G1_LEN;
+    if (n_g2 != 65) return KB200_E_SETUP_G2_LEN;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { snprintf(g_err, sizeof g_err, "no CUDA device: this engine has no CPU fallback"); return KB200_E_CUDA; }
+    kb200_setup* s = new kb200_setup();
+    s->device = device;
+    int rc = build_setup(s, g1, g2, window_bits);
+    if (rc) { kb200_setup_free(s); return rc; }
+    *out = s; return 0;
+}
+extern "C" int kb200_setup_load_json(const char* path, int device, int window_bits, kb200_setup** out) {
+    if (!path || !out) return KB200_E_ARG;
+    FILE* f = fopen(path, "rb");
+    if (!f) { snprintf(g_err, sizeof g_err, "cannot open %s", path); return KB200_E_IO; }
+    std::string doc; char buf[65536]; size_t k;
+    while ((k = fread(buf, 1, sizeof buf, f)) > 0) doc.append(buf, k);
+    fclose(f);
+    std::vector<std::vector<uint8_t>> g1, g2;
+    if (int rc = json_hex_array(doc, "g1_lagrange", g1)) return rc;
+    if (int rc = json_hex_array(doc, "g2_monomial", g2)) return rc;
+    if (g1.size() != KB_N) return KB200_E_SETUP_G1_LEN;
+    if (g2.size() != 65) return KB200_E_SETUP_G2_LEN;
+    std::vector<uint8_t> b1(KB_N * 48), b2(65 * 96);
+    // kateth reads 48/96 bytes behind the pointer without a length check (src/bls.rs:514); the ABI checks.
+    for (size_t i = 0; i < g1.size(); i++) { if (g1[i].size() != 48) return KB200_E_G1_INVALID_ENCODING; memcpy(&b1[48 * i], g1[i].data(), 48); }
+    for (size_t i = 0; i < g2.size(); i++) { if (g2[i].size() != 96) return KB200_E_G1_INVALID_ENCODING; memcpy(&b2[96 * i], g2[i].data(), 96); }
+    return kb200_setup_load_raw(b1.data(), KB_N, b2.data(), 65, device, window_bits, out);
+}
+extern "C" void kb200_setup_free(kb200_setup* s) {
+    if (!s) return;
+    cudaSetDevice(s->device);
+    if (s->d_bases) cudaFree(s->d_bases);
+    if (s->d_roots) cudaFree(s->d_roots);
+    if (s->d_table) cudaFree(s->d_table);
+    DBuf* bufs[] = {&s->blobs, &s->c48, &s->p48, &s->zy32, &s->out48, &s->out32, &s->st_blob, &s->st_a, &s->st_b, &s->status, &s->z, &s->y, &s->prod,
+                    &s->indom, &s->q, &s->partials, &s->aff_c, &s->aff_p, &s->rlc_part, &s->rlc_s, &s->rmont, &s->records, &s->combine};
+    for (DBuf* b : bufs) b->release();
+    delete s;
+}
+extern "C" int kb200_set_stream(kb200_setup* s, void* stream) { if (!s) return KB200_E_ARG; s->stream = (cudaStream_t)stream; return 0; }
+extern "C" int kb200_get_info(kb200_setup* s, kb200_info* info) {
+    if (!s || !info) return KB200_E_ARG;
+    info->window_bits = s->tab.c; info->windows = s->tab.nwin; info->table_bytes = s->table_bytes; info->kernel_launches = s->launches;
+    info->device = s->device; info->sm_count = s->sm_count; info->setup_seconds = s->setup_seconds;
+    return 0;
+}
+
+// ------------------------------------------------------------------ pipelines (all pointers are device pointers)
+static inline int pick_slices(kb200_setup* s, size_t n) {
+    // aim for >= 4 CTAs per SM; one CTA per blob once the batch alone fills the GPU
+    size_t target = (size_t)s->sm_count * 4;
+    int S = 1;
+    while (S < 32 && n * S < target) S <<= 1;
+    return S;
+}
+static inline int blocks(size_t n, int t) { return (int)((n + t - 1) / t); }
+
+// MSM of n scalar vectors (FMT 0: blobs, FMT 1: LE limbs) -> n compressed points
+template <int FMT>
+static int run_msm(kb200_setup* s, const uint32_t* d_scalars, size_t n, const int32_t* d_status, uint32_t* d_out48) {
+    int S = pick_slices(s, n);
+    if (int rc = s->partials.ensure(n * S * sizeof(G1))) return rc;
+    LAUNCH(s, (k_msm<FMT>), (unsigned)(n * S), MSM_THREADS, s->tab, d_scalars, d_status, s->partials.as<G1>(), S);
+    LAUNCH(s, k_msm_finish, blocks(n, 32), 32, s->partials.as<G1>(), S, (int)n, d_status, d_out48, (G1Affine*)nullptr);
+    return 0;
+}
+// evaluation (and optionally quotient) of n blobs at z (canonical limbs in s->z)
+template <bool WANT_Q>
+static int run_eval(kb200_setup* s, const uint32_t* d_blobs, size_t n, const int32_t* d_status) {
+    if (int rc = s->prod.ensure(n * sizeof(Fr))) return rc;
+    if (int rc = s->indom.ensure(n * 4)) return rc;
+    if (int rc = s->y.ensure(n * sizeof(Fr))) return rc;
+    if (WANT_Q) if (int rc = s->q.ensure(n * (size_t)KB_BLOB_BYTES)) return rc;
+    LAUNCH(s, k_eval_prod, (unsigned)n, EV_THREADS, s->z.as<Fr>(), s->d_roots, (int)n, s->prod.as<Fr>(), s->indom.as<int32_t>());
+    LAUNCH(s, k_eval_inv, blocks(n, 32), 32, s->prod.as<Fr>(), (int)n);
+    LAUNCH(s, (k_eval_finish<WANT_Q>), (unsigned)n, EV_THREADS, d_blobs, s->z.as<Fr>(), s->d_roots, s->prod.as<Fr>(), s->indom.as<int32_t>(), d_status,
+           (int)n, s->y.as<Fr>(), s->q.as<uint32_t>());
+    return 0;
+}
+static int fetch_status(kb200_setup* s, const int32_t* d_status, size_t n, std::vector<int32_t>& h) {
+    h.resize(n);
+    if (n == 0) return 0;
+    CU(cudaMemcpyAsync(h.data(), d_status, n * 4, cudaMemcpyDeviceToHost, s->stream));
+    CU(cudaStreamSynchronize(s->stream));
+    CU(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int kb200_blob_to_commitment_device(kb200_setup* s, const void* d_blobs, size_t n, void* d_out48, int32_t* d_status) {
+    if (!s || (n && (!d_blobs || !d_out48 || !d_status))) return KB200_E_ARG;
+    CU(cudaSetDevice(s->device));
+    if (n == 0) return 0;
+    CU(cudaMemsetAsync(d_status, 0, n * 4, s->stream));
+    LAUNCH(s, k_blob_check, blocks(n * KB_N, 256), 256, (const uint32_t*)d_blobs, (int)n, d_status);
+    if (int rc = run_msm<0>(s, (const uint32_t*)d_blobs, n, d_status, (uint32_t*)d_out48)) return rc;
+    std::vector<int32_t> h; if (int rc = fetch_status(s, d_status, n, h)) return rc;
+    return first_nonzero(h);
+}
+
+// shared tail of blob_proof / proof: z in s->z, status final -> quotient -> MSM -> compressed proofs
+static int prove_tail(kb200_setup* s, const uint32_t* d_blobs, size_t n, int32_t* d_status, uint32_t* d_out48) {
+    for (size_t off = 0; off < n; off += CHUNK) {
+        size_t m = (n - off < CHUNK) ? n - off : CHUNK;
+        // run_eval works on chunk-local arrays: shift the inputs
+        DBuf zsave = s->z; s->z.p = (char*)zsave.p + off * sizeof(Fr);
+        int rc = run_eval<true>(s, d_blobs + off * (KB_N * 8), m, d_status + off);
+        s->z = zsave;
+        if (rc) return rc;
+        if (int rc2 = run_msm<1>(s, s->q.as<uint32_t>(), m, d_status + off, d_out48 + off * 12)) return rc2;
+        // keep y for the caller (proof-at-z returns it)
+        if (int rc3 = s->out32.ensure(n * sizeof(Fr))) return rc3;
+        CU(cudaMemcpyAsync((char*)s->out32.p + off * sizeof(Fr), s->y.p, m * sizeof(Fr), cudaMemcpyDeviceToDevice, s->stream));
+    }
+    return 0;
+}
+
+extern "C" int kb200_compute_blob_proof_device(kb200_setup* s, const void* d_blobs, const void* d_comm48, size_t n, void* d_out48, int32_t* d_status) {
+    if (!s || (n && (!d_blobs || !d_comm48 || !d_out48 || !d_status))) return KB200_E_ARG;
+    CU(cudaSetDevice(s->device));
+    if (n == 0) return 0;
+    if (int rc = s->st_blob.ensure(n * 4)) return rc;
+    if (int rc = s->st_a.ensure(n * 4)) return rc;
+    if (int rc = s->aff_c.ensure(n * sizeof(G1Affine))) return rc;
+    if (int rc = s->z.ensure(n * sizeof(Fr))) return rc;
+    CU(cudaMemsetAsync(s->st_blob.p, 0, n * 4, s->stream));
+    CU(cudaMemsetAsync(s->st_a.p, 0, n * 4, s->stream));
+    LAUNCH(s, k_blob_check, blocks(n * KB_N, 256), 256, (const uint32_t*)d_blobs, (int)n, s->st_blob.as<int32_t>());
+    LAUNCH(s, k_g1_decompress, blocks(n, 64), 64, (const uint32_t*)d_comm48, (int)n, s->aff_c.as<G1Affine>(), s->st_a.as<int32_t>());
+    LAUNCH(s, k_merge_status, blocks(n, 256), 256, s->st_blob.as<int32_t>(), s->st_a.as<int32_t>(), (const int32_t*)nullptr, (int)n, d_status);
+    LAUNCH(s, k_challenge, blocks(n, 32), 32, (const uint32_t*)d_blobs, (const uint32_t*)d_comm48, (int)n, d_status, s->z.as<Fr>());
+    if (int rc = prove_tail(s, (const uint32_t*)d_blobs, n, d_status, (uint32_t*)d_out48)) return rc;
+    std::vector<int32_t> hb, ha;
+    if (int rc = fetch_status(s, s->st_blob.as<int32_t>(), n, hb)) return rc;
+    if (int rc = fetch_status(s, s->st_a.as<int32_t>(), n, ha)) return rc;
+    if (int e = first_nonzero(hb)) return e;
+    return first_nonzero(ha);
+}
+
+extern "C" int kb200_compute_proof_device(kb200_setup* s, const void* d_blobs, const void* d_z32, size_t n, void* d_out48, void* d_y32, int32_t* d_status) {
+    if (!s || (n && (!d_blobs || !d_z32 || !d_out48 || !d_y32 || !d_status))) return KB200_E_ARG;
+    CU(cudaSetDevice(s->device));
+    if (n == 0) return 0;
+    if (int rc = s->st_blob.ensure(n * 4)) return rc;
+    if (int rc = s->st_a.ensure(n * 4)) return rc;
+    if (int rc = s->z.ensure(n * sizeof(Fr))) return rc;
+    CU(cudaMemsetAsync(s->st_blob.p, 0, n * 4, s->stream));
+    CU(cudaMemsetAsync(s->st_a.p, 0, n * 4, s->stream));
+    LAUNCH(s, k_blob_check, blocks(n * KB_N, 256), 256, (const uint32_t*)d_blobs, (int)n, s->st_blob.as<int32_t>());
+    LAUNCH(s, k_scalar_check, blocks(n, 128), 128, (const uint32_t*)d_z32, (int)n, s->z.as<Fr>(), s->st_a.as<int32_t>());
+    LAUNCH(s, k_merge_status, blocks(n, 256), 256, s->st_blob.as<int32_t>(), s->st_a.as<int32_t>(), (const int32_t*)nullptr, (int)n, d_status);
+    if (int rc = prove_tail(s, (const uint32_t*)d_blobs, n, d_status, (uint32_t*)d_out48)) return rc;
+    LAUNCH(s, k_store_scalars_be, blocks(n, 128), 128, s->out32.as<Fr>(), (int)n, d_status, (uint32_t*)d_y32);
+    std::vector<int32_t> hb, ha;
+    if (int rc = fetch_status(s, s->st_blob.as<int32_t>(), n, hb)) return rc;
+    if (int rc = fetch_status(s, s->st_a.as<int32_t>(), n, ha)) return rc;
+    if (int e = first_nonzero(hb)) return e;
+    return first_nonzero(ha);
+}
+
+// ---- verification ----
+// RLC partial over n items whose affine proofs/commitments are in s->aff_p / s->aff_c and z, y in s->z / s->y.
+static int run_rlc(kb200_setup* s, size_t n, size_t index_offset, size_t n_total, int raw, RlcRecord* d_record) {
+    int nb = blocks(n, RLC_THREADS);
+    if (int rc = s->rlc_part.ensure((size_t)3 * nb * sizeof(G1))) return rc;
+    if (int rc = s->rlc_s.ensure((size_t)nb * sizeof(Fr))) return rc;
+    if (int rc = s->rmont.ensure(sizeof(Fr))) return rc;
+    if (!raw) LAUNCH(s, k_batch_r, 1, 1, (uint32_t)n_total, s->rmont.as<Fr>());
+    LAUNCH(s, k_rlc, dim3(nb, 3), RLC_THREADS, s->aff_p.as<G1Affine>(), s->aff_c.as<G1Affine>(), s->z.as<Fr>(), s->y.as<Fr>(), (int)n, (uint32_t)index_offset,
+           s->rmont.as<Fr>(), raw, s->rlc_part.as<G1>(), s->rlc_s.as<Fr>());
+    LAUNCH(s, k_rlc_finish, 3, RLC_FIN_THREADS, s->rlc_part.as<G1>(), s->rlc_s.as<Fr>(), nb, d_record);
+    return 0;
+}
+static void u32_to_be48(uint8_t* out, const uint32_t* limbs12) { for (int i = 0; i < 12; i++) { uint32_t w = limbs12[11 - i]; out[4 * i] = w >> 24; out[4 * i + 1] = w >> 16; out[4 * i + 2] = w >> 8; out[4 * i + 3] = w; } }
+static void compress_plain(uint8_t out[48], const uint32_t* xy24, bool inf) {
+    if (inf) { memset(out, 0, 48); out[0] = 0xc0; return; }
+    u32_to_be48(out, xy24);
+    out[0] |= 0x80;
+    // y > (p-1)/2 ?
+    using namespace kb200::consts;
+    bool gt = false;
+    for (int i = 11; i >= 0; i--) { if (xy24[12 + i] > H_FP_HALF[i]) { gt = true; break; } if (xy24[12 + i] < H_FP_HALF[i]) break; }
+    if (gt) out[0] |= 0x20;
+}
+static int finish_records(kb200_setup* s, const RlcRecord* d_records, size_t nrec, int* ok) {
+    if (int rc = s->combine.ensure(64 * 4)) return rc;
+    LAUNCH(s, k_rlc_combine, 1, 32, d_records, (int)nrec, s->combine.as<uint32_t>());
+    uint32_t h[50];
+    CU(cudaMemcpyAsync(h, s->combine.p, sizeof h, cudaMemcpyDeviceToHost, s->stream));
+    CU(cudaStreamSynchronize(s->stream));
+    CU(cudaGetLastError());
+    host::G1A a, b;
+    a.inf = h[48] != 0; b.inf = h[49] != 0;
+    host::fp_from_plain_u32(a.x, h); host::fp_from_plain_u32(a.y, h + 12);
+    host::fp_from_plain_u32(b.x, h + 24); host::fp_from_plain_u32(b.y, h + 36);
+    compress_plain(s->last_lhs, h, a.inf); compress_plain(s->last_rhs, h + 24, b.inf); s->have_last = true;
+    // bls::verify_pairings((lhs, [tau]_2), (rhs, G2))  (src/kzg/setup.rs:157-160, src/bls.rs:572-598)
+    *ok = host::verify_pairings(a, s->tau_prep, b, s->g2_prep) ? 1 : 0;
+    return 0;
+}
+extern "C" int kb200_last_pairing_operands(kb200_setup* s, uint8_t lhs48[48], uint8_t rhs48[48]) {
+    if (!s || !s->have_last) return KB200_E_ARG;
+    memcpy(lhs48, s->last_lhs, 48); memcpy(rhs48, s->last_rhs, 48); return 0;
+}
+
+// decode + decompress + challenge + evaluate for a shard; leaves aff_c, aff_p, z, y filled. Returns kateth-ordered first error.
+static int verify_prepare(kb200_setup* s, const uint32_t* d_blobs, const uint32_t* d_c48, const uint32_t* d_p48, size_t n, int32_t* d_status) {
+    if (int rc = s->st_blob.ensure(n * 4)) return rc;
+    if (int rc = s->st_a.ensure(n * 4)) return rc;
+    if (int rc = s->st_b.ensure(n * 4)) return rc;
+    if (int rc = s->aff_c.ensure(n * sizeof(G1Affine))) return rc;
+    if (int rc = s->aff_p.ensure(n * sizeof(G1Affine))) return rc;
+    if (int rc = s->z.ensure(n * sizeof(Fr))) return rc;
+    CU(cudaMemsetAsync(s->st_blob.p, 0, n * 4, s->stream));
+    CU(cudaMemsetAsync(s->st_a.p, 0, n * 4, s->stream));
+    CU(cudaMemsetAsync(s->st_b.p, 0, n * 4, s->stream));
+    LAUNCH(s, k_blob_check, blocks(n * KB_N, 256), 256, d_blobs, (int)n, s->st_blob.as<int32_t>());
+    LAUNCH(s, k_g1_decompress, blocks(n, 64), 64, d_c48, (int)n, s->aff_c.as<G1Affine>(), s->st_a.as<int32_t>());
+    LAUNCH(s, k_g1_decompress, blocks(n, 64), 64, d_p48, (int)n, s->aff_p.as<G1Affine>(), s->st_b.as<int32_t>());
+    LAUNCH(s, k_merge_status, blocks(n, 256), 256, s->st_blob.as<int32_t>(), s->st_a.as<int32_t>(), s->st_b.as<int32_t>(), (int)n, d_status);
+    LAUNCH(s, k_challenge, blocks(n, 32), 32, d_blobs, d_c48, (int)n, d_status, s->z.as<Fr>());
+    if (int rc = run_eval<false>(s, d_blobs, n, d_status)) return rc;
+    std::vector<int32_t> h0, h1, h2;
+    if (int rc = fetch_status(s, s->st_blob.as<int32_t>(), n, h0)) return rc;
+    if (int rc = fetch_status(s, s->st_a.as<int32_t>(), n, h1)) return rc;
+    if (int rc = fetch_status(s, s->st_b.as<int32_t>(), n, h2)) return rc;
+    if (int e = first_nonzero(h0)) return e;
+    if (int e = first_nonzero(h1)) return e;
+    return first_nonzero(h2);
+}
+extern "C" int kb200_verify_blob_proof_batch_partial_device(kb200_setup* s, const void* d_blobs, const void* d_c48, const void* d_p48, size_t n,
+                                                            size_t index_offset, size_t n_total, void* d_record, int32_t* d_status) {
+    if (!s || !d_record || (n && (!d_blobs || !d_c48 || !d_p48 || !d_status))) return KB200_E_ARG;
+    CU(cudaSetDevice(s->device));
+    int err = 0;
+    if (n) { err = verify_prepare(s, (const uint32_t*)d_blobs, (const uint32_t*)d_c48, (const uint32_t*)d_p48, n, d_status); if (err < 0) return err; }
+    else { if (int rc = s->aff_c.ensure(16)) return rc; if (int rc = s->aff_p.ensure(16)) return rc; if (int rc = s->z.ensure(32)) return rc; if (int rc = s->y.ensure(32)) return rc; }
+    if (int rc = run_rlc(s, n, index_offset, n_total, 0, (RlcRecord*)d_record)) return rc;
+    CU(cudaStreamSynchronize(s->stream));
+    CU(cudaGetLastError());
+    return err;
+}
+extern "C" int kb200_verify_batch_finish_device(kb200_setup* s, const void* d_records, size_t n_records, int* ok) {
+    if (!s || !ok || (n_records && !d_records)) return KB200_E_ARG;
+    CU(cudaSetDevice(s->device));
+    return finish_records(s, (const RlcRecord*)d_records, n_records, ok);
+}
+extern "C" int kb200_verify_blob_proof_batch_device(kb200_setup* s, const void* d_blobs, const void* d_c48, const void* d_p48, size_t n, int* ok,
+                                                    int32_t* d_status) {
+    if (!s || !ok) return KB200_E_ARG;
+    CU(cudaSetDevice(s->device));
+    if (n == 0) { *ok = 1; return 0; }     // empty lincombs are the identity: e(O, .) e(O, .) == 1
+    if (int rc = s->records.ensure(sizeof(RlcRecord))) return rc;
+    int err = kb200_verify_blob_proof_batch_partial_device(s, d_blobs, d_c48, d_p48, n, 0, n, s->records.p, d_status);
+    if (err) return err;
+    return finish_records(s, s->records.as<RlcRecord>(), 1, ok);
+}
+
+// ------------------------------------------------------------------ host-buffer entry points (copy in, run, copy out)
+static int h2d(kb200_setup* s, DBuf& b, const void* src, size_t bytes) {
+    if (int rc = b.ensure(bytes ? bytes : 16)) return rc;
+    if (bytes) CU(cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, s->stream));
+    return 0;
+}
+static int d2h(kb200_setup* s, void* dst, const void* src, size_t bytes) {
+    if (bytes) CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, s->stream));
+    CU(cudaStreamSynchronize(s->stream));
+    return 0;
+}
+extern "C" int kb200_blob_to_commitment(kb200_setup* s, const uint8_t* blobs, size_t n, uint8_t* out48, int32_t* status) {
+    if (!s || (n && (!blobs || !out48))) return KB200_E_ARG;
+    CU(cudaSetDevice(s->device));
+    int first = 0;
+    for (size_t off = 0; off < n; off += CHUNK) {
+        size_t m = (n - off < CHUNK) ? n - off : CHUNK;
+        if (int rc = h2d(s, s->blobs, blobs + off * KB_BLOB_BYTES, m * KB_BLOB_BYTES)) return rc;
+        if (int rc = s->out48.ensure(m * 48)) return rc;
+        if (int rc = s->status.ensure(m * 4)) return rc;
+        int e = kb200_blob_to_commitment_device(s, s->blobs.p, m, s->out48.p, s->status.as<int32_t>());
+        if (e < 0) return e;
+        if (e && !first) first = e;
+        if (int rc = d2h(s, out48 + off * 48, s->out48.p, m * 48)) return rc;
+        if (status) if (int rc = d2h(s, status + off, s->status.p, m * 4)) return rc;
+    }
+    return first;
+}
+extern "C" int kb200_compute_blob_proof(kb200_setup* s, const uint8_t* blobs, const uint8_t* comm48, size_t n, uint8_t* out48, int32_t* status) {
+    if (!s || (n && (!blobs || !comm48 || !out48))) return KB200_E_ARG;
+    CU(cudaSetDevice(s->device));
+    // kateth's order within one call is blob first, then commitment; across a batch we report the first item's error
+    int first = 0;
+    for (size_t off = 0; off < n; off += CHUNK) {
+        size_t m = (n - off < CHUNK) ? n - off : CHUNK;
+        if (int rc = h2d(s, s->blobs, blobs + off * KB_BLOB_BYTES, m * KB_BLOB_BYTES)) return rc;
+        if (int rc = h2d(s, s->c48, comm48 + off * 48, m * 48)) return rc;
+        if (int rc = s->out48.ensure(m * 48)) return rc;
+        if (int rc = s->status.ensure(m * 4)) return rc;
+        int e = kb200_compute_blob_proof_device(s, s->blobs.p, s->c48.p, m, s->out48.p, s->status.as<int32_t>());
+        if (e < 0) return e;
+        if (e && !first) first = e;
+        if (int rc = d2h(s, out48 + off * 48, s->out48.p, m * 48)) return rc;
+        if (status) if (int rc = d2h(s, status + off, s->status.p, m * 4)) return rc;
+    }
+    return first;
+}
+extern "C" int kb200_compute_proof(kb200_setup* s, const uint8_t* blobs, const uint8_t* z32, size_t n, uint8_t* out48, uint8_t* y32, int32_t* status) {
+    if (!s || (n && (!blobs || !z32 || !out48 || !y32))) return KB200_E_ARG;
+    CU(cudaSetDevice(s->device));
+    int first = 0;
+    for (size_t off = 0; off < n; off += CHUNK) {
+        size_t m = (n - off < CHUNK) ? n - off : CHUNK;
+        if (int rc = h2d(s, s->blobs, blobs + off * KB_BLOB_BYTES, m * KB_BLOB_BYTES)) return rc;
+        if (int rc = h2d(s, s->zy32, z32 + off * 32, m * 32)) return rc;
+        if (int rc = s->out48.ensure(m * 48)) return rc;
+        if (int rc = s->p48.ensure(m * 32)) return rc;     // reused as the y output staging
+        if (int rc = s->status.ensure(m * 4)) return rc;
+        int e = kb200_compute_proof_device(s, s->blobs.p, s->zy32.p, m, s->out48.p, s->p48.p, s->status.as<int32_t>());
+        if (e < 0) return e;
+        if (e && !first) first = e;
+        if (int rc = d2h(s, out48 + off * 48, s->out48.p, m * 48)) return rc;
+        if (int rc = d2h(s, y32 + off * 32, s->p48.p, m * 32)) return rc;
+        if (status) if (int rc = d2h(s, status + off, s->status.p, m * 4)) return rc;
+    }
+    return first;
+}
+extern "C" int kb200_verify_blob_proof_batch(kb200_setup* s, const uint8_t* blobs, const uint8_t* comm48, const uint8_t* proofs48, size_t n, int* ok,
+                                             int32_t* status) {
+    if (!s || !ok || (n && (!blobs || !comm48 || !proofs48))) return KB200_E_ARG;
+    CU(cudaSetDevice(s->device));
+    if (n == 0) { *ok = 1; return 0; }
+    size_t nch = (n + CHUNK - 1) / CHUNK;
+    if (int rc = s->records.ensure(nch * sizeof(RlcRecord))) return rc;
+    // kateth checks ALL blobs, then ALL commitments, then ALL proofs (src/kzg/setup.rs:259-271); with chunking we
+    // remember the first error of each class across chunks.
+    int e_blob = 0, e_comm = 0, e_proof = 0;
+    for (size_t c = 0; c < nch; c++) {
+        size_t off = c * CHUNK, m = (n - off < CHUNK) ? n - off : CHUNK;
+        if (int rc = h2d(s, s->blobs, blobs + off * KB_BLOB_BYTES, m * KB_BLOB_BYTES)) return rc;
+        if (int rc = h2d(s, s->c48, comm48 + off * 48, m * 48)) return rc;
+        if (int rc = h2d(s, s->p48, proofs48 + off * 48, m * 48)) return rc;
+        if (int rc = s->status.ensure(m * 4)) return rc;
+        int e = kb200_verify_blob_proof_batch_partial_device(s, s->blobs.p, s->c48.p, s->p48.p, m, off, n, (char*)s->records.p + c * sizeof(RlcRecord),
+                                                             s->status.as<int32_t>());
+        if (e < 0) return e;
+        if (e) {
+            std::vector<int32_t> h0, h1, h2;
+            if (int rc = fetch_status(s, s->st_blob.as<int32_t>(), m, h0)) return rc;
+            if (int rc = fetch_status(s, s->st_a.as<int32_t>(), m, h1)) return rc;
+            if (int rc = fetch_status(s, s->st_b.as<int32_t>(), m, h2)) return rc;
+            if (!e_blob) e_blob = first_nonzero(h0);
+            if (!e_comm) e_comm = first_nonzero(h1);
+            if (!e_proof) e_proof = first_nonzero(h2);
+        }
+        if (status) if (int rc = d2h(s, status + off, s->status.p, m * 4)) return rc;
+    }
+    if (e_blob) return e_blob;
+    if (e_comm) return e_comm;
+    if (e_proof) return e_proof;
+    return finish_records(s, s->records.as<RlcRecord>(), nch, ok);
+}
+// points given directly: mirrors the private Setup::verify_proof_batch (raw = 0) and verify_proof_inner (raw = 1)
+static int verify_points(kb200_setup* s, const uint8_t* proofs48, const uint8_t* comm48, const uint8_t* z32, const uint8_t* y32, size_t n, int raw, int* ok,
+                         int32_t* status) {
+    if (!s || !ok || (n && (!proofs48 || !comm48 || !z32 || !y32))) return KB200_E_ARG;
+    CU(cudaSetDevice(s->device));
+    if (n == 0) { *ok = 1; return 0; }
+    if (int rc = h2d(s, s->p48, proofs48, n * 48)) return rc;
+    if (int rc = h2d(s, s->c48, comm48, n * 48)) return rc;
+    if (int rc = h2d(s, s->zy32, z32, n * 32)) return rc;
+    if (int rc = h2d(s, s->out32, y32, n * 32)) return rc;
+    DBuf* need[] = {&s->st_blob, &s->st_a, &s->st_b, &s->status};
+    for (DBuf* b : need) { if (int rc = b->ensure(n * 4)) return rc; CU(cudaMemsetAsync(b->p, 0, n * 4, s->stream)); }
+    if (int rc = s->aff_c.ensure(n * sizeof(G1Affine))) return rc;
+    if (int rc = s->aff_p.ensure(n * sizeof(G1Affine))) return rc;
+    if (int rc = s->z.ensure(n * sizeof(Fr))) return rc;
+    if (int rc = s->y.ensure(n * sizeof(Fr))) return rc;
+    if (int rc = s->prod.ensure(n * 4)) return rc;   // 4th status class (y)
+    CU(cudaMemsetAsync(s->prod.p, 0, n * 4, s->stream));
+    // kateth's order in verify_proof: proof, commitment, point, eval (src/kzg/setup.rs:103-110)
+    LAUNCH(s, k_g1_decompress, blocks(n, 64), 64, s->p48.as<uint32_t>(), (int)n, s->aff_p.as<G1Affine>(), s->st_blob.as<int32_t>());
+    LAUNCH(s, k_g1_decompress, blocks(n, 64), 64, s->c48.as<uint32_t>(), (int)n, s->aff_c.as<G1Affine>(), s->st_a.as<int32_t>());
+    LAUNCH(s, k_scalar_check, blocks(n, 128), 128, s->zy32.as<uint32_t>(), (int)n, s->z.as<Fr>(), s->st_b.as<int32_t>());
+    LAUNCH(s, k_scalar_check, blocks(n, 128), 128, s->out32.as<uint32_t>(), (int)n, s->y.as<Fr>(), s->prod.as<int32_t>());
+    std::vector<int32_t> h[4];
+    if (int rc = fetch_status(s, s->st_blob.as<int32_t>(), n, h[0])) return rc;
+    if (int rc = fetch_status(s, s->st_a.as<int32_t>(), n, h[1])) return rc;
+    if (int rc = fetch_status(s, s->st_b.as<int32_t>(), n, h[2])) return rc;
+    if (int rc = fetch_status(s, s->prod.as<int32_t>(), n, h[3])) return rc;
+    if (status) for (size_t i = 0; i < n; i++) status[i] = h[0][i] ? h[0][i] : h[1][i] ? h[1][i] : h[2][i] ? h[2][i] : h[3][i];
+    for (int k = 0; k < 4; k++) if (int e = first_nonzero(h[k])) return e;
+    if (int rc = s->records.ensure(sizeof(RlcRecord))) return rc;
+    if (int rc = run_rlc(s, n, 0, n, raw, s->records.as<RlcRecord>())) return rc;
+    return finish_records(s, s->records.as<RlcRecord>(), 1, ok);
+}
+extern "C" int kb200_verify_proof(kb200_setup* s, const uint8_t proof48[48], const uint8_t comm48[48], const uint8_t z32[32], const uint8_t y32[32], int* ok) {
+    return verify_points(s, proof48, comm48, z32, y32, 1, 1, ok, nullptr);
+}
+extern "C" int kb200_verify_proof_batch(kb200_setup* s, const uint8_t* proofs48, const uint8_t* comm48, const uint8_t* z32, const uint8_t* y32, size_t n,
+                                        int* ok, int32_t* status) {
+    return verify_points(s, proofs48, comm48, z32, y32, n, 0, ok, status);
+}
+extern "C" int kb200_verify_blob_proof(kb200_setup* s, const uint8_t* blob, const uint8_t comm48[48], const uint8_t proof48[48], int* ok) {
+    if (!s || !ok || !blob || !comm48 || !proof48) return KB200_E_ARG;
+    CU(cudaSetDevice(s->device));
+    if (int rc = h2d(s, s->blobs, blob, KB_BLOB_BYTES)) return rc;
+    if (int rc = h2d(s, s->c48, comm48, 48)) return rc;
+    if (int rc = h2d(s, s->p48, proof48, 48)) return rc;
+    if (int rc = s->status.ensure(4)) return rc;
+    int e = verify_prepare(s, s->blobs.as<uint32_t>(), s->c48.as<uint32_t>(), s->p48.as<uint32_t>(), 1, s->status.as<int32_t>());
+    if (e) return e;
+    if (int rc = s->records.ensure(sizeof(RlcRecord))) return rc;
+    if (int rc = run_rlc(s, 1, 0, 1, 1, s->records.as<RlcRecord>())) return rc;
+    return finish_records(s, s->records.as<RlcRecord>(), 1, ok);
+}
+
+// ------------------------------------------------------------------ unit-test hooks
+extern "C" int kb200_test_fp_mul(const uint32_t* a, const uint32_t* b, uint32_t* out, size_t n) {
+    if (int rc = init_consts()) return rc;
+    Fp *da, *db, *dout; CU(cudaMalloc(&da, n * 48)); CU(cudaMalloc(&db, n * 48)); CU(cudaMalloc(&dout, n * 48));
+    CU(cudaMemcpy(da, a, n * 48, cudaMemcpyHostToDevice)); CU(cudaMemcpy(db, b, n * 48, cudaMemcpyHostToDevice));
+    k_test_fp_mul<<<blocks(n, 128), 128>>>(da, db, dout, (int)n);
+    CU(cudaMemcpy(out, dout, n * 48, cudaMemcpyDeviceToHost));
+    cudaFree(da); cudaFree(db); cudaFree(dout); return 0;
+}
+extern "C" int kb200_test_fr_mul(const uint32_t* a, const uint32_t* b, uint32_t* out, size_t n) {
+    if (int rc = init_consts()) return rc;
+    Fr *da, *db, *dout; CU(cudaMalloc(&da, n * 32)); CU(cudaMalloc(&db, n * 32)); CU(cudaMalloc(&dout, n * 32));
+    CU(cudaMemcpy(da, a, n * 32, cudaMemcpyHostToDevice)); CU(cudaMemcpy(db, b, n * 32, cudaMemcpyHostToDevice));
+    k_test_fr_mul<<<blocks(n, 128), 128>>>(da, db, dout, (int)n);
+    CU(cudaMemcpy(out, dout, n * 32, cudaMemcpyDeviceToHost));
+    cudaFree(da); cudaFree(db); cudaFree(dout); return 0;
+}
+extern "C" int kb200_test_g1_decompress(kb200_setup* s, const uint8_t* in48, size_t n, int32_t* status, uint8_t* re48) {
+    if (!s || !in48 || !status || !re48) return KB200_E_ARG;
+    CU(cudaSetDevice(s->device));
+    if (int rc = h2d(s, s->c48, in48, n * 48)) return rc;
+    if (int rc = s->aff_c.ensure(n * sizeof(G1Affine))) return rc;
+    if (int rc = s->status.ensure(n * 4)) return rc;
+    if (int rc = s->out48.ensure(n * 48)) return rc;
+    CU(cudaMemsetAsync(s->status.p, 0, n * 4, s->stream));
+    LAUNCH(s, k_g1_decompress, blocks(n, 64), 64, s->c48.as<uint32_t>(), (int)n, s->aff_c.as<G1Affine>(), s->status.as<int32_t>());
+    LAUNCH(s, k_test_compress, blocks(n, 64), 64, s->aff_c.as<G1Affine>(), (int)n, s->status.as<int32_t>(), s->out48.as<uint32_t>());
+    if (int rc = d2h(s, status, s->status.p, n * 4)) return rc;
+    return d2h(s, re48, s->out48.p, n * 48);
+}
+extern "C" int kb200_test_mac_peak(int iters, double* tmacs_wide, double* tmacs_fpmul) {
+    if (int rc = init_consts()) return rc;
+    cudaDeviceProp prop; CU(cudaGetDeviceProperties(&prop, 0));
+    int grid = prop.multiProcessorCount * 8, block = 256;
+    void* buf; CU(cudaMalloc(&buf, (size_t)grid * block * 48));
+    cudaEvent_t e0, e1; CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
+    float ms;
+    k_mac_wide<<<grid, block>>>((uint64_t*)buf, 64, 1);   // warm-up
+    CU(cudaEventRecord(e0)); k_mac_wide<<<grid, block>>>((uint64_t*)buf, iters, 7); CU(cudaEventRecord(e1)); CU(cudaEventSynchronize(e1));
+    CU(cudaEventElapsedTime(&ms, e0, e1));
+    *tmacs_wide = (double)grid * block * iters * 16.0 / (ms * 1e-3) / 1e12;
+    int it2 = iters / 16 > 0 ? iters / 16 : 1;
+    k_mac_fpmul<<<grid, block>>>((Fp*)buf, 4, 1);
+    CU(cudaEventRecord(e0)); k_mac_fpmul<<<grid, block>>>((Fp*)buf, it2, 7); CU(cudaEventRecord(e1)); CU(cudaEventSynchronize(e1));
+    CU(cudaEventElapsedTime(&ms, e0, e1));
+    *tmacs_fpmul = (double)grid * block * it2 * 2.0 * 300.0 / (ms * 1e-3) / 1e12;
+    cudaFree(buf); cudaEventDestroy(e0); cudaEventDestroy(e1);
+    return 0;
+}
+extern "C" int kb200_test_host_pairing(kb200_setup* s, const uint32_t* a_xy24, int a_inf, const uint32_t* b_xy24, int b_inf, int* ok) {
+    if (!s || !ok) return KB200_E_ARG;
+    host::G1A a, b; a.inf = a_inf != 0; b.inf = b_inf != 0;
+    if (!a.inf) { host::fp_from_plain_u32(a.x, a_xy24); host::fp_from_plain_u32(a.y, a_xy24 + 12); }
+    if (!b.inf) { host::fp_from_plain_u32(b.x, b_xy24); host::fp_from_plain_u32(b.y, b_xy24 + 12); }
+    *ok = host::verify_pairings(a, s->tau_prep, b, s->g2_prep) ? 1 : 0;
+    return 0;
+}

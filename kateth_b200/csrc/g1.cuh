@@ -1,0 +1,165 @@
+// g1.cuh -- the group G1 of BLS12-381 (y^2 = x^3 + 4 over Fp) on the device.
+//
+// Replaces blst's P1 arithmetic behind kateth's `P1` wrapper (/root/reference/src/bls.rs:362-552):
+//   blst_p1_add (complete addition), blst_p1_cneg, blst_p1_mult, blst_p1_to_affine / from_affine,
+//   blst_p1_compress (src/bls.rs:491-503), blst_p1_uncompress + blst_p1_affine_in_g1 (src/bls.rs:505-531).
+// Accumulators use extended Jacobian "XYZZ" coordinates (x = X/ZZ, y = Y/ZZZ, ZZ^3 = ZZZ^2; ZZ == 0 is the point at
+// infinity); table / input points are affine with (0,0) standing for infinity ((0,0) is not on the curve).
+// Every addition handles P == Q, P == -Q and infinity, so the result is the unique group element blst returns.
+#pragma once
+#include "field.cuh"
+
+namespace kb200 {
+
+struct G1Affine { Fp x, y; };             // 96 bytes, Montgomery form; (0,0) = infinity
+struct G1 { Fp x, y, zz, zzz; };          // XYZZ
+
+__device__ __forceinline__ bool g1a_is_inf(const G1Affine& p) { return fp_is_zero(p.x) && fp_is_zero(p.y); }
+__device__ __forceinline__ bool g1_is_inf(const G1& p) { return fp_is_zero(p.zz); }
+__device__ __forceinline__ void g1_set_inf(G1& p) { fp_zero(p.x); fp_zero(p.y); fp_zero(p.zz); fp_zero(p.zzz); }
+__device__ __forceinline__ void g1_from_affine(G1& r, const G1Affine& p) {
+    if (g1a_is_inf(p)) { g1_set_inf(r); return; }
+    r.x = p.x; r.y = p.y; fp_set(r.zz, c_k.fp_one); fp_set(r.zzz, c_k.fp_one);
+}
+
+// r = 2*(x, y) for an affine, finite point
+__device__ __noinline__ void g1_dbl_affine(G1& r, const Fp& x, const Fp& y) {
+    Fp u, v, w, s, m, t;
+    fp_dbl(u, y); fp_sqr(v, u); fp_mul(w, u, v); fp_mul(s, x, v);
+    fp_sqr(m, x); fp_dbl(t, m); fp_add(m, m, t);
+    fp_sqr(r.x, m); fp_sub(r.x, r.x, s); fp_sub(r.x, r.x, s);
+    fp_sub(t, s, r.x); fp_mul(t, m, t); fp_mul(u, w, y); fp_sub(r.y, t, u);
+    r.zz = v; r.zzz = w;
+}
+// p = 2*p
+__device__ __noinline__ void g1_dbl(G1& p) {
+    if (g1_is_inf(p)) return;
+    Fp u, v, w, s, m, t;
+    fp_dbl(u, p.y); fp_sqr(v, u); fp_mul(w, u, v); fp_mul(s, p.x, v);
+    fp_sqr(m, p.x); fp_dbl(t, m); fp_add(m, m, t);
+    fp_mul(t, w, p.y);                      // W*Y1 before Y is overwritten
+    fp_sqr(p.x, m); fp_sub(p.x, p.x, s); fp_sub(p.x, p.x, s);
+    fp_sub(s, s, p.x); fp_mul(s, m, s); fp_sub(p.y, s, t);
+    fp_mul(p.zz, v, p.zz); fp_mul(p.zzz, w, p.zzz);
+}
+// rare paths of the mixed addition, kept out of line so the hot loop stays small
+__device__ __noinline__ void g1_madd_rare(G1* acc, const Fp* x2, const Fp* y2, bool same_y) {
+    if (same_y) { G1 t; g1_dbl_affine(t, *x2, *y2); *acc = t; } else g1_set_inf(*acc);
+}
+// acc += (x2, y2)   [affine, finite].  8M + 2S on the common path.
+__device__ __forceinline__ void g1_madd(G1& acc, const Fp& x2, const Fp& y2) {
+    if (g1_is_inf(acc)) { acc.x = x2; acc.y = y2; fp_set(acc.zz, c_k.fp_one); fp_set(acc.zzz, c_k.fp_one); return; }
+    Fp p, r, pp, ppp, q, t;
+    fp_mul(p, x2, acc.zz); fp_sub(p, p, acc.x);          // P = U2 - X1
+    fp_mul(r, y2, acc.zzz); fp_sub(r, r, acc.y);         // R = S2 - Y1
+    if (fp_is_zero(p)) { G1 tmp = acc; g1_madd_rare(&tmp, &x2, &y2, fp_is_zero(r)); acc = tmp; return; }
+    fp_sqr(pp, p); fp_mul(ppp, p, pp); fp_mul(q, acc.x, pp);
+    fp_sqr(t, r); fp_sub(t, t, ppp); fp_sub(t, t, q); fp_sub(acc.x, t, q);     // X3 = R^2 - PPP - 2Q
+    fp_sub(q, q, acc.x); fp_mul(q, r, q); fp_mul(t, acc.y, ppp); fp_sub(acc.y, q, t);
+    fp_mul(acc.zz, acc.zz, pp); fp_mul(acc.zzz, acc.zzz, ppp);
+}
+// acc += pt (affine, possibly the (0,0) infinity sentinel), optionally negated
+__device__ __forceinline__ void g1_madd_signed(G1& acc, const G1Affine& pt, bool neg) {
+    if (g1a_is_inf(pt)) return;
+    Fp y; fp_cneg(y, pt.y, neg);
+    g1_madd(acc, pt.x, y);
+}
+// acc += b   (both XYZZ).  12M + 2S on the common path.
+__device__ __noinline__ void g1_add(G1& acc, const G1& b) {
+    if (g1_is_inf(b)) return;
+    if (g1_is_inf(acc)) { acc = b; return; }
+    Fp u1, u2, s1, s2, p, r, pp, ppp, q, t;
+    fp_mul(u1, acc.x, b.zz); fp_mul(u2, b.x, acc.zz);
+    fp_mul(s1, acc.y, b.zzz); fp_mul(s2, b.y, acc.zzz);
+    fp_sub(p, u2, u1); fp_sub(r, s2, s1);
+    if (fp_is_zero(p)) {
+        if (fp_is_zero(r)) g1_dbl(acc); else g1_set_inf(acc);
+        return;
+    }
+    fp_sqr(pp, p); fp_mul(ppp, p, pp); fp_mul(q, u1, pp);
+    fp_sqr(t, r); fp_sub(t, t, ppp); fp_sub(t, t, q); fp_sub(acc.x, t, q);
+    fp_sub(q, q, acc.x); fp_mul(q, r, q); fp_mul(t, s1, ppp); fp_sub(acc.y, q, t);
+    fp_mul(acc.zz, acc.zz, b.zz); fp_mul(acc.zz, acc.zz, pp);
+    fp_mul(acc.zzz, acc.zzz, b.zzz); fp_mul(acc.zzz, acc.zzz, ppp);
+}
+// XYZZ -> affine (one field inversion)
+__device__ __noinline__ void g1_to_affine(G1Affine& r, const G1& p) {
+    if (g1_is_inf(p)) { fp_zero(r.x); fp_zero(r.y); return; }
+    Fp i3, zi, i2;
+    fp_inv(i3, p.zzz);                       // Z^-3
+    fp_mul(zi, p.zz, i3); fp_sqr(i2, zi);    // Z^-1, Z^-2
+    fp_mul(r.x, p.x, i2); fp_mul(r.y, p.y, i3);
+}
+// r = [k]P for a plain 255-bit scalar (little-endian limbs); MSB-first double-and-add  (blst_p1_mult(..., 255))
+__device__ __noinline__ void g1_mul(G1& r, const G1Affine& p, const Fr& k) {
+    G1 acc; g1_set_inf(acc);
+    if (!g1a_is_inf(p)) {
+#pragma unroll 1
+        for (int i = 254; i >= 0; i--) {
+            g1_dbl(acc);
+            if ((k.l[i >> 5] >> (i & 31)) & 1) g1_madd(acc, p.x, p.y);
+        }
+    }
+    r = acc;
+}
+
+// ---- ZCash 48-byte compressed form ----
+// out: 12 big-endian words.  p affine.
+__device__ __forceinline__ void g1_compress(uint32_t* out12, const G1Affine& p) {
+    if (g1a_is_inf(p)) {
+#pragma unroll
+        for (int i = 0; i < 12; i++) out12[i] = 0;
+        out12[0] = __byte_perm(0xc0000000u, 0, 0x0123);
+        return;
+    }
+    Fp x, y; fp_from_mont(x, p.x); fp_from_mont(y, p.y);
+    uint32_t top = x.l[11] | 0x80000000u; if (fp_plain_gt_half(y)) top |= 0x20000000u;
+    out12[0] = __byte_perm(top, 0, 0x0123);
+#pragma unroll
+    for (int i = 1; i < 12; i++) out12[i] = __byte_perm(x.l[11 - i], 0, 0x0123);
+}
+// status codes (include/kateth_b200.h)
+#define KB_OK 0
+#define KB_INVALID_LEN 1
+#define KB_INVALID_FIELD_ELEMENT 2
+#define KB_G1_INVALID_ENCODING 3
+#define KB_G1_NOT_ON_CURVE 4
+#define KB_G1_NOT_IN_GROUP 5
+#define KB_SCALAR_INVALID_ENCODING 6
+#define KB_SCALAR_NOT_IN_FIELD 7
+
+// in12: the 48 bytes as 12 words (memory order).  Curve check only (blst_p1_uncompress).
+__device__ __noinline__ int g1_uncompress(G1Affine& r, const uint32_t* in12) {
+    uint32_t w0 = __byte_perm(in12[0], 0, 0x0123);
+    if (!(w0 & 0x80000000u)) return KB_G1_INVALID_ENCODING;
+    if (w0 & 0x40000000u) {
+        uint32_t rest = w0 & 0x3fffffffu;
+        for (int i = 1; i < 12; i++) rest |= in12[i];
+        if (rest) return KB_G1_INVALID_ENCODING;
+        fp_zero(r.x); fp_zero(r.y); return KB_OK;
+    }
+    Fp x;
+    x.l[11] = w0 & 0x1fffffffu;
+#pragma unroll
+    for (int i = 1; i < 12; i++) x.l[11 - i] = __byte_perm(in12[i], 0, 0x0123);
+    if (fp_plain_geq_p(x)) return KB_G1_INVALID_ENCODING;
+    Fp xm, y2, y, t, b;
+    fp_to_mont(xm, x);
+    fp_sqr(y2, xm); fp_mul(y2, y2, xm); fp_set(b, c_k.fp_b4); fp_add(y2, y2, b);
+    fp_pow_c(y, y2, c_k.fp_sqrt_exp);
+    fp_sqr(t, y);
+    if (!fp_eq(t, y2)) return KB_G1_NOT_ON_CURVE;
+    fp_from_mont(t, y);
+    bool want = (w0 & 0x20000000u) != 0;
+    fp_cneg(y, y, fp_plain_gt_half(t) != want);
+    r.x = xm; r.y = y; return KB_OK;
+}
+// subgroup membership by definition: [r]P == infinity   (blst_p1_affine_in_g1)
+__device__ __noinline__ bool g1_in_subgroup(const G1Affine& p) {
+    if (g1a_is_inf(p)) return true;
+    Fr k; fr_set(k, c_k.fr_mod);
+    G1 t; g1_mul(t, p, k);
+    return g1_is_inf(t);
+}
+
+}  // namespace kb200

@@ -1,0 +1,326 @@
+// host_bls.cpp -- see host_bls.hpp.  Product code; shares nothing with oracle/.
+#include "host_bls.hpp"
+#include "constants.cuh"
+#include <string.h>
+
+namespace kb200 { namespace host {
+
+typedef unsigned __int128 u128;
+using namespace kb200::consts;
+
+// ------------------------------------------------------------------ Fp
+static Fp P_, ONE_, R2_, ZERO_;
+static uint64_t EXP_PM2[6], EXP_PM3D4[6], EXP_HALF[6], EXP_PM1D6[6];
+static void pack64(uint64_t* o, const uint32_t* w) { for (int i = 0; i < 6; i++) o[i] = (uint64_t)w[2 * i] | ((uint64_t)w[2 * i + 1] << 32); }
+
+static inline bool geq(const Fp& a, const Fp& b) {
+    for (int i = 5; i >= 0; i--) { if (a.l[i] > b.l[i]) return true; if (a.l[i] < b.l[i]) return false; }
+    return true;
+}
+static inline uint64_t add6(Fp& r, const Fp& a, const Fp& b) { u128 c = 0; for (int i = 0; i < 6; i++) { c += (u128)a.l[i] + b.l[i]; r.l[i] = (uint64_t)c; c >>= 64; } return (uint64_t)c; }
+static inline uint64_t sub6(Fp& r, const Fp& a, const Fp& b) { uint64_t bw = 0; for (int i = 0; i < 6; i++) { u128 t = (u128)a.l[i] - b.l[i] - bw; r.l[i] = (uint64_t)t; bw = (uint64_t)(t >> 64) & 1; } return bw; }
+static inline void fadd(Fp& r, const Fp& a, const Fp& b) { Fp t; uint64_t c = add6(t, a, b); if (c || geq(t, P_)) sub6(t, t, P_); r = t; }
+static inline void fsub(Fp& r, const Fp& a, const Fp& b) { Fp t; if (sub6(t, a, b)) add6(t, t, P_); r = t; }
+static inline bool fzero(const Fp& a) { uint64_t t = 0; for (int i = 0; i < 6; i++) t |= a.l[i]; return t == 0; }
+static inline bool feq(const Fp& a, const Fp& b) { uint64_t t = 0; for (int i = 0; i < 6; i++) t |= a.l[i] ^ b.l[i]; return t == 0; }
+static inline void fneg(Fp& r, const Fp& a) { if (fzero(a)) r = a; else sub6(r, P_, a); }
+static void fmul(Fp& r, const Fp& a, const Fp& b) {
+    uint64_t t[8] = {0};
+    for (int i = 0; i < 6; i++) {
+        u128 c = 0;
+        for (int j = 0; j < 6; j++) { c += (u128)a.l[j] * b.l[i] + t[j]; t[j] = (uint64_t)c; c >>= 64; }
+        c += t[6]; t[6] = (uint64_t)c; t[7] = (uint64_t)(c >> 64);
+        uint64_t m = t[0] * FP_INV64;
+        c = (u128)m * P_.l[0] + t[0]; c >>= 64;
+        for (int j = 1; j < 6; j++) { c += (u128)m * P_.l[j] + t[j]; t[j - 1] = (uint64_t)c; c >>= 64; }
+        c += t[6]; t[5] = (uint64_t)c; t[6] = t[7] + (uint64_t)(c >> 64);
+    }
+    Fp o; memcpy(o.l, t, 48);
+    if (t[6] || geq(o, P_)) sub6(o, o, P_);
+    r = o;
+}
+static inline void fsqr(Fp& r, const Fp& a) { fmul(r, a, a); }
+static void fpow(Fp& r, const Fp& a, const uint64_t* e) {
+    Fp acc = ONE_;
+    for (int i = 383; i >= 0; i--) { fsqr(acc, acc); if ((e[i >> 6] >> (i & 63)) & 1) fmul(acc, acc, a); }
+    r = acc;
+}
+static inline void finv(Fp& r, const Fp& a) { fpow(r, a, EXP_PM2); }
+static void fto_mont(Fp& r, const Fp& plain) { fmul(r, plain, R2_); }
+static void ffrom_mont(Fp& plain, const Fp& a) { Fp one = {{1, 0, 0, 0, 0, 0}}; fmul(plain, a, one); }
+static bool f_lex_largest(const Fp& a) { Fp t; ffrom_mont(t, a); Fp h; memcpy(h.l, EXP_HALF, 48); return !geq(h, t); }
+static bool fp_from_be48(Fp& r, const uint8_t* in) {
+    Fp t;
+    for (int i = 0; i < 6; i++) { uint64_t w = 0; for (int k = 0; k < 8; k++) w = (w << 8) | in[(5 - i) * 8 + k]; t.l[i] = w; }
+    if (geq(t, P_)) return false;
+    fto_mont(r, t); return true;
+}
+void fp_from_plain_u32(Fp& r, const uint32_t* w) { Fp t; pack64(t.l, w); fto_mont(r, t); }
+
+// ------------------------------------------------------------------ Fp2
+static inline void f2add(Fp2& r, const Fp2& a, const Fp2& b) { fadd(r.c0, a.c0, b.c0); fadd(r.c1, a.c1, b.c1); }
+static inline void f2sub(Fp2& r, const Fp2& a, const Fp2& b) { fsub(r.c0, a.c0, b.c0); fsub(r.c1, a.c1, b.c1); }
+static inline void f2neg(Fp2& r, const Fp2& a) { fneg(r.c0, a.c0); fneg(r.c1, a.c1); }
+static inline void f2dbl(Fp2& r, const Fp2& a) { f2add(r, a, a); }
+static inline void f2conj(Fp2& r, const Fp2& a) { r.c0 = a.c0; fneg(r.c1, a.c1); }
+static inline bool f2zero(const Fp2& a) { return fzero(a.c0) && fzero(a.c1); }
+static inline bool f2eq(const Fp2& a, const Fp2& b) { return feq(a.c0, b.c0) && feq(a.c1, b.c1); }
+static void f2mul(Fp2& r, const Fp2& a, const Fp2& b) {   // Karatsuba, 3 Fp products
+    Fp t0, t1, s0, s1, m;
+    fmul(t0, a.c0, b.c0); fmul(t1, a.c1, b.c1);
+    fadd(s0, a.c0, a.c1); fadd(s1, b.c0, b.c1); fmul(m, s0, s1);
+    fsub(r.c0, t0, t1); fsub(m, m, t0); fsub(r.c1, m, t1);
+}
+static void f2sqr(Fp2& r, const Fp2& a) {                  // (a0+a1)(a0-a1), 2 a0 a1
+    Fp s, d, m;
+    fadd(s, a.c0, a.c1); fsub(d, a.c0, a.c1); fmul(m, a.c0, a.c1);
+    fmul(r.c0, s, d); fadd(r.c1, m, m);
+}
+static inline void f2mulfp(Fp2& r, const Fp2& a, const Fp& b) { fmul(r.c0, a.c0, b); fmul(r.c1, a.c1, b); }
+static inline void f2mulxi(Fp2& r, const Fp2& a) { Fp t0, t1; fsub(t0, a.c0, a.c1); fadd(t1, a.c0, a.c1); r.c0 = t0; r.c1 = t1; }
+static void f2inv(Fp2& r, const Fp2& a) {
+    Fp n, t; fsqr(n, a.c0); fsqr(t, a.c1); fadd(n, n, t); finv(n, n);
+    fmul(r.c0, a.c0, n); fmul(t, a.c1, n); fneg(r.c1, t);
+}
+static Fp2 F2ONE, F2ZERO;
+static void f2pow(Fp2& r, const Fp2& a, const uint64_t* e, int nbits) {
+    Fp2 acc = F2ONE;
+    for (int i = nbits - 1; i >= 0; i--) { f2sqr(acc, acc); if ((e[i >> 6] >> (i & 63)) & 1) f2mul(acc, acc, a); }
+    r = acc;
+}
+static bool f2sqrt(Fp2& r, const Fp2& a) {
+    if (f2zero(a)) { r = a; return true; }
+    Fp2 a1, alpha, x0, m1, t;
+    f2pow(a1, a, EXP_PM3D4, 384);
+    f2sqr(alpha, a1); f2mul(alpha, alpha, a);
+    f2mul(x0, a1, a);
+    f2neg(m1, F2ONE);
+    if (f2eq(alpha, m1)) { fneg(t.c0, x0.c1); t.c1 = x0.c0; r = t; }
+    else { Fp2 b; f2add(b, F2ONE, alpha); f2pow(b, b, EXP_HALF, 384); f2mul(r, b, x0); }
+    f2sqr(t, r); return f2eq(t, a);
+}
+static bool f2_lex_largest(const Fp2& a) { return fzero(a.c1) ? f_lex_largest(a.c0) : f_lex_largest(a.c1); }
+
+// ------------------------------------------------------------------ Fp6 / Fp12
+struct Fp6 { Fp2 c0, c1, c2; };
+struct Fp12 { Fp6 c0, c1; };
+static inline void f6add(Fp6& r, const Fp6& a, const Fp6& b) { f2add(r.c0, a.c0, b.c0); f2add(r.c1, a.c1, b.c1); f2add(r.c2, a.c2, b.c2); }
+static inline void f6sub(Fp6& r, const Fp6& a, const Fp6& b) { f2sub(r.c0, a.c0, b.c0); f2sub(r.c1, a.c1, b.c1); f2sub(r.c2, a.c2, b.c2); }
+static inline void f6neg(Fp6& r, const Fp6& a) { f2neg(r.c0, a.c0); f2neg(r.c1, a.c1); f2neg(r.c2, a.c2); }
+static void f6mul(Fp6& r, const Fp6& a, const Fp6& b) {
+    Fp2 v0, v1, v2, t0, t1, t2, s, u;
+    f2mul(v0, a.c0, b.c0); f2mul(v1, a.c1, b.c1); f2mul(v2, a.c2, b.c2);
+    // c0 = v0 + xi((a1+a2)(b1+b2) - v1 - v2)
+    f2add(s, a.c1, a.c2); f2add(u, b.c1, b.c2); f2mul(t0, s, u); f2sub(t0, t0, v1); f2sub(t0, t0, v2); f2mulxi(t0, t0); f2add(t0, t0, v0);
+    // c1 = (a0+a1)(b0+b1) - v0 - v1 + xi v2
+    f2add(s, a.c0, a.c1); f2add(u, b.c0, b.c1); f2mul(t1, s, u); f2sub(t1, t1, v0); f2sub(t1, t1, v1); f2mulxi(s, v2); f2add(t1, t1, s);
+    // c2 = (a0+a2)(b0+b2) - v0 - v2 + v1
+    f2add(s, a.c0, a.c2); f2add(u, b.c0, b.c2); f2mul(t2, s, u); f2sub(t2, t2, v0); f2sub(t2, t2, v2); f2add(t2, t2, v1);
+    r.c0 = t0; r.c1 = t1; r.c2 = t2;
+}
+static inline void f6mulv(Fp6& r, const Fp6& a) { Fp2 t; f2mulxi(t, a.c2); Fp2 a0 = a.c0, a1 = a.c1; r.c0 = t; r.c1 = a0; r.c2 = a1; }
+static void f6inv(Fp6& r, const Fp6& a) {
+    Fp2 t0, t1, t2, s, d;
+    f2sqr(t0, a.c0); f2mul(s, a.c1, a.c2); f2mulxi(s, s); f2sub(t0, t0, s);          // a0^2 - xi a1 a2
+    f2sqr(t1, a.c2); f2mulxi(t1, t1); f2mul(s, a.c0, a.c1); f2sub(t1, t1, s);        // xi a2^2 - a0 a1
+    f2sqr(t2, a.c1); f2mul(s, a.c0, a.c2); f2sub(t2, t2, s);                          // a1^2 - a0 a2
+    f2mul(d, a.c2, t1); f2mul(s, a.c1, t2); f2add(d, d, s); f2mulxi(d, d); f2mul(s, a.c0, t0); f2add(d, d, s);
+    f2inv(d, d);
+    f2mul(r.c0, t0, d); f2mul(r.c1, t1, d); f2mul(r.c2, t2, d);
+}
+static void f12mul(Fp12& r, const Fp12& a, const Fp12& b) {
+    Fp6 t0, t1, s, u, m;
+    f6mul(t0, a.c0, b.c0); f6mul(t1, a.c1, b.c1);
+    f6add(s, a.c0, a.c1); f6add(u, b.c0, b.c1); f6mul(m, s, u); f6sub(m, m, t0); f6sub(m, m, t1);
+    f6mulv(s, t1); f6add(r.c0, t0, s); r.c1 = m;
+}
+static void f12sqr(Fp12& r, const Fp12& a) {
+    // (a0 + a1 w)^2 = (a0^2 + v a1^2) + 2 a0 a1 w ; complex squaring
+    Fp6 ab, s, t, va1;
+    f6mul(ab, a.c0, a.c1);
+    f6add(s, a.c0, a.c1); f6mulv(va1, a.c1); f6add(t, a.c0, va1);
+    f6mul(s, s, t); f6sub(s, s, ab); f6mulv(t, ab); f6sub(s, s, t);
+    r.c0 = s; f6add(r.c1, ab, ab);
+}
+static inline void f12conj(Fp12& r, const Fp12& a) { r.c0 = a.c0; f6neg(r.c1, a.c1); }
+static void f12inv(Fp12& r, const Fp12& a) {
+    Fp6 t0, t1; f6mul(t0, a.c0, a.c0); f6mul(t1, a.c1, a.c1); f6mulv(t1, t1); f6sub(t0, t0, t1); f6inv(t0, t0);
+    f6mul(r.c0, a.c0, t0); f6mul(t1, a.c1, t0); f6neg(r.c1, t1);
+}
+static Fp12 F12ONE;
+static bool f12isone(const Fp12& a) {
+    return f2eq(a.c0.c0, F2ONE) && f2zero(a.c0.c1) && f2zero(a.c0.c2) && f2zero(a.c1.c0) && f2zero(a.c1.c1) && f2zero(a.c1.c2);
+}
+// coefficient of w^k (k = 0..5) in the flat basis: w^0->c0.c0, w^1->c1.c0, w^2->c0.c1, w^3->c1.c1, w^4->c0.c2, w^5->c1.c2
+static inline Fp2& wcoef(Fp12& a, int k) { Fp6& h = (k & 1) ? a.c1 : a.c0; return (k >> 1) == 0 ? h.c0 : ((k >> 1) == 1 ? h.c1 : h.c2); }
+static Fp2 FROB1[6];   // gamma^k,  gamma = xi^((p-1)/6)
+static Fp FROB2[6];    // (gamma * conj(gamma))^k = xi^((p^2-1)/6 * k), in Fp
+static void f12frob(Fp12& r, const Fp12& a) {          // a^p
+    Fp12 t = a;
+    for (int k = 0; k < 6; k++) { Fp2 c; f2conj(c, wcoef(t, k)); f2mul(wcoef(t, k), c, FROB1[k]); }
+    r = t;
+}
+static void f12frob2(Fp12& r, const Fp12& a) {         // a^(p^2)
+    Fp12 t = a;
+    for (int k = 0; k < 6; k++) { Fp2 c = wcoef(t, k); f2mulfp(wcoef(t, k), c, FROB2[k]); }
+    r = t;
+}
+// multiply by the sparse line  l = c0 + c2 w^2 + c3 w^3  (c3 in Fp): in tower form (c0 + c2 v) + (c3 v) w
+static void f12mul_line(Fp12& f, const Fp2& c0, const Fp2& c2, const Fp& c3) {
+    Fp12 l; memset(&l, 0, sizeof l);
+    l.c0.c0 = c0; l.c0.c1 = c2; l.c1.c1.c0 = c3;
+    f12mul(f, f, l);
+}
+
+// ------------------------------------------------------------------ G2
+static void g2_dbl_affine(Fp2& x3, Fp2& y3, Fp2& lam, const Fp2& x, const Fp2& y) {
+    Fp2 n, t; f2sqr(n, x); f2dbl(t, n); f2add(n, n, t); f2dbl(t, y); f2inv(t, t); f2mul(lam, n, t);
+    f2sqr(x3, lam); f2sub(x3, x3, x); f2sub(x3, x3, x);
+    f2sub(t, x, x3); f2mul(y3, lam, t); f2sub(y3, y3, y);
+}
+static void g2_add_affine(Fp2& x3, Fp2& y3, Fp2& lam, const Fp2& x1, const Fp2& y1, const Fp2& x2, const Fp2& y2) {
+    Fp2 n, t; f2sub(n, y1, y2); f2sub(t, x1, x2); f2inv(t, t); f2mul(lam, n, t);
+    f2sqr(x3, lam); f2sub(x3, x3, x1); f2sub(x3, x3, x2);
+    f2sub(t, x1, x3); f2mul(y3, lam, t); f2sub(y3, y3, y1);
+}
+// projective (X:Y:Z) helpers just for the subgroup check [r]Q == O (Jacobian)
+struct G2J { Fp2 x, y, z; };
+static void g2j_dbl(G2J& r, const G2J& p) {
+    if (f2zero(p.z)) { r = p; return; }
+    Fp2 a, b, c, d, e, f, t, x3, y3, z3;
+    f2sqr(a, p.x); f2sqr(b, p.y); f2sqr(c, b);
+    f2add(t, p.x, b); f2sqr(t, t); f2sub(t, t, a); f2sub(t, t, c); f2dbl(d, t);
+    f2dbl(e, a); f2add(e, e, a); f2sqr(f, e);
+    f2dbl(t, d); f2sub(x3, f, t);
+    f2sub(t, d, x3); f2mul(y3, e, t); f2dbl(t, c); f2dbl(t, t); f2dbl(t, t); f2sub(y3, y3, t);
+    f2mul(z3, p.y, p.z); f2dbl(z3, z3);
+    r.x = x3; r.y = y3; r.z = z3;
+}
+static void g2j_add_affine(G2J& r, const G2J& p, const G2A& q) {   // q finite
+    if (f2zero(p.z)) { r.x = q.x; r.y = q.y; r.z = F2ONE; return; }
+    Fp2 z1z1, u2, s2, h, hh, i, j, rr, v, t, x3, y3, z3;
+    f2sqr(z1z1, p.z); f2mul(u2, q.x, z1z1); f2mul(s2, q.y, p.z); f2mul(s2, s2, z1z1);
+    f2sub(h, u2, p.x); f2sub(rr, s2, p.y);
+    if (f2zero(h)) { if (f2zero(rr)) { g2j_dbl(r, p); } else { memset(&r, 0, sizeof r); } return; }
+    f2sqr(hh, h); f2dbl(i, hh); f2dbl(i, i); f2mul(j, h, i); f2dbl(rr, rr); f2mul(v, p.x, i);
+    f2sqr(x3, rr); f2sub(x3, x3, j); f2dbl(t, v); f2sub(x3, x3, t);
+    f2sub(t, v, x3); f2mul(y3, rr, t); f2mul(t, p.y, j); f2dbl(t, t); f2sub(y3, y3, t);
+    f2add(z3, p.z, h); f2sqr(z3, z3); f2sub(z3, z3, z1z1); f2sub(z3, z3, hh);
+    r.x = x3; r.y = y3; r.z = z3;
+}
+static const uint64_t FR_MOD64[4] = {0xffffffff00000001ull, 0x53bda402fffe5bfeull, 0x3339d80809a1d805ull, 0x73eda753299d7d48ull};
+static bool g2_in_subgroup(const G2A& q) {
+    if (q.inf) return true;
+    G2J acc; memset(&acc, 0, sizeof acc);
+    for (int i = 254; i >= 0; i--) { g2j_dbl(acc, acc); if ((FR_MOD64[i >> 6] >> (i & 63)) & 1) g2j_add_affine(acc, acc, q); }
+    return f2zero(acc.z);
+}
+
+static bool g_init = false;
+static void init() {
+    if (g_init) return;
+    pack64(P_.l, H_FP_P); pack64(ONE_.l, H_FP_ONE); pack64(R2_.l, H_FP_R2); memset(&ZERO_, 0, sizeof ZERO_);
+    pack64(EXP_PM2, H_FP_PM2); pack64(EXP_PM3D4, H_FP_PM3D4); pack64(EXP_HALF, H_FP_HALF); pack64(EXP_PM1D6, H_FP_PM1D6);
+    F2ONE.c0 = ONE_; F2ONE.c1 = ZERO_; F2ZERO.c0 = ZERO_; F2ZERO.c1 = ZERO_;
+    memset(&F12ONE, 0, sizeof F12ONE); F12ONE.c0.c0 = F2ONE;
+    Fp2 xi; xi.c0 = ONE_; xi.c1 = ONE_;
+    Fp2 gamma; f2pow(gamma, xi, EXP_PM1D6, 384);
+    FROB1[0] = F2ONE; for (int k = 1; k < 6; k++) f2mul(FROB1[k], FROB1[k - 1], gamma);
+    for (int k = 0; k < 6; k++) { Fp2 c, n; f2conj(c, FROB1[k]); f2mul(n, FROB1[k], c); FROB2[k] = n.c0; }   // norm: gamma^(p+1)
+    g_init = true;
+}
+
+int g2_decompress(G2A& out, const uint8_t in[96]) {
+    init();
+    uint8_t b0 = in[0];
+    if (!(b0 & 0x80)) return 3;
+    if (b0 & 0x40) {
+        if (b0 & 0x3f) return 3;
+        for (int i = 1; i < 96; i++) if (in[i]) return 3;
+        memset(&out, 0, sizeof out); out.inf = true; return 0;
+    }
+    uint8_t tmp[48]; memcpy(tmp, in, 48); tmp[0] &= 0x1f;
+    G2A q; q.inf = false;
+    if (!fp_from_be48(q.x.c1, tmp)) return 3;
+    if (!fp_from_be48(q.x.c0, in + 48)) return 3;
+    Fp2 y2, b; f2sqr(y2, q.x); f2mul(y2, y2, q.x);
+    Fp four; fadd(four, ONE_, ONE_); fadd(four, four, four); b.c0 = four; b.c1 = four; f2add(y2, y2, b);
+    if (!f2sqrt(q.y, y2)) return 4;
+    if (f2_lex_largest(q.y) != (bool)((b0 >> 5) & 1)) f2neg(q.y, q.y);
+    if (!g2_in_subgroup(q)) return 5;
+    out = q; return 0;
+}
+void g2_generator(G2A& out) {
+    init();
+    Fp t;
+    pack64(t.l, H_G2_GEN_X0_PLAIN); fto_mont(out.x.c0, t); pack64(t.l, H_G2_GEN_X1_PLAIN); fto_mont(out.x.c1, t);
+    pack64(t.l, H_G2_GEN_Y0_PLAIN); fto_mont(out.y.c0, t); pack64(t.l, H_G2_GEN_Y1_PLAIN); fto_mont(out.y.c1, t);
+    out.inf = false;
+}
+// Walk |x| once for a fixed Q and keep every line as (c0 = lam*xT - yT, c1 = -lam); see host_bls.hpp.
+void g2_prepare(G2Prepared& out, const G2A& q) {
+    init();
+    out.n = 0; out.inf = q.inf;
+    if (q.inf) return;
+    Fp2 tx = q.x, ty = q.y;
+    bool started = false;
+    for (int i = 63; i >= 0; i--) {
+        bool bit = (BLS_X_ABS >> i) & 1;
+        if (!started) { started = bit; continue; }
+        Fp2 lam, x3, y3;
+        g2_dbl_affine(x3, y3, lam, tx, ty);
+        Line& l = out.lines[out.n++]; f2mul(l.c0, lam, tx); f2sub(l.c0, l.c0, ty); f2neg(l.c1, lam);
+        tx = x3; ty = y3;
+        if (bit) {
+            g2_add_affine(x3, y3, lam, tx, ty, q.x, q.y);
+            Line& m = out.lines[out.n++]; f2mul(m.c0, lam, tx); f2sub(m.c0, m.c0, ty); f2neg(m.c1, lam);
+            tx = x3; ty = y3;
+        }
+    }
+}
+// f^|x|
+static void f12pow_x(Fp12& r, const Fp12& a) {
+    Fp12 acc = a;
+    for (int i = 62; i >= 0; i--) { f12sqr(acc, acc); if ((BLS_X_ABS >> i) & 1) f12mul(acc, acc, a); }
+    r = acc;
+}
+// a^x for unitary a and negative x: conj(a^|x|)
+static inline void f12pow_negx(Fp12& r, const Fp12& a) { f12pow_x(r, a); f12conj(r, r); }
+
+bool verify_pairings(const G1A& a1, const G2Prepared& q1, const G1A& b1, const G2Prepared& q2) {
+    init();
+    // pairs with an infinite member contribute 1
+    const G1A* P[2]; const G2Prepared* Q[2]; int np = 0;
+    G1A na1 = a1; if (!na1.inf) fneg(na1.y, a1.y);
+    if (!na1.inf && !q1.inf) { P[np] = &na1; Q[np] = &q1; np++; }
+    if (!b1.inf && !q2.inf) { P[np] = &b1; Q[np] = &q2; np++; }
+    if (np == 0) return true;
+    Fp12 f = F12ONE;
+    int li = 0; bool started = false;
+    for (int i = 63; i >= 0; i--) {
+        bool bit = (BLS_X_ABS >> i) & 1;
+        if (!started) { started = bit; continue; }
+        f12sqr(f, f);
+        for (int k = 0; k < np; k++) { const Line& l = Q[k]->lines[li]; Fp2 c2; f2mulfp(c2, l.c1, P[k]->x); f12mul_line(f, l.c0, c2, P[k]->y); }
+        li++;
+        if (bit) {
+            for (int k = 0; k < np; k++) { const Line& l = Q[k]->lines[li]; Fp2 c2; f2mulfp(c2, l.c1, P[k]->x); f12mul_line(f, l.c0, c2, P[k]->y); }
+            li++;
+        }
+    }
+    // (x < 0: f is the inverse of the true Miller value; irrelevant for an == 1 test)
+    // easy part: f^((p^6-1)(p^2+1))
+    Fp12 t, u; f12conj(t, f); f12inv(u, f); f12mul(f, t, u);
+    f12frob2(t, f); f12mul(f, t, f);
+    // hard part: f^((x-1)^2 (x+p)(x^2+p^2-1) + 3), a cube of the canonical exponent (harmless: gcd(3, r) = 1)
+    Fp12 a, b, c, fc;
+    f12conj(fc, f);
+    f12pow_negx(a, f); f12mul(a, a, fc);                      // f^(x-1)
+    f12pow_negx(t, a); f12conj(u, a); f12mul(a, t, u);        // ^(x-1)
+    f12pow_negx(t, a); f12frob(u, a); f12mul(b, t, u);        // ^(x+p)
+    f12pow_negx(t, b); f12pow_negx(t, t); f12frob2(u, b); f12mul(c, t, u); f12conj(u, b); f12mul(c, c, u);   // ^(x^2+p^2-1)
+    f12sqr(t, f); f12mul(t, t, f); f12mul(c, c, t);           // * f^3
+    return f12isone(c);
+}
+
+}}  // namespace

@@ -1,0 +1,264 @@
+// poly.cuh -- per-blob scalar-field work of the KZG path: blob validation, the Fiat-Shamir challenge,
+// barycentric evaluation with a batched inversion, and the quotient polynomial.
+//
+// Replaces (file:line in /root/reference):
+//   Blob::from_slice            src/blob.rs:26-37      (k_blob_check: every element < r)
+//   Blob::challenge             src/blob.rs:78-97      (k_challenge: SHA-256 over domain | degree | blob | commitment)
+//   Polynomial::evaluate        src/kzg/poly.rs:10-33  (k_eval_prod / k_eval_inv / k_eval_finish)
+//   Polynomial::prove (quotient) src/kzg/poly.rs:45-66 (k_eval_finish with WANT_Q)
+// kateth divides per term (8,192 Euclidean inversions per proof).  Here all 4,096 denominators of a blob are
+// inverted with ONE inversion: per-thread products, a product tree over the CTA in shared memory, the root
+// inverted in a separate kernel where 32 blobs share a warp (one inversion per lane), then the tree is walked
+// back down.  Field elements are unique, so the results are bit-identical to the per-term divisions.
+//
+// Domain mixing: blob elements f_i stay in canonical (non-Montgomery) form; multiplying a canonical value by a
+// Montgomery-form value with the Montgomery product yields a canonical value, so y and the quotient come out
+// canonical -- exactly what the output encoding and the MSM's digit recoding need -- with no conversions.
+#pragma once
+#include "field.cuh"
+#include "sha256.cuh"
+#include "msm.cuh"
+
+namespace kb200 {
+
+// ---- roots of unity in bit-reversed order (src/math.rs:7-29, 72-74), Montgomery form, built once ----
+__device__ __forceinline__ uint32_t brp12(uint32_t i) { return __brev(i) >> 20; }
+__global__ void k_roots(Fr* roots_brp) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= KB_N) return;
+    Fr w; fr_set(w, c_k.fr_omega);
+    Fr r; fr_pow_u32(r, w, brp12(i));
+    roots_brp[i] = r;
+}
+
+// ---- Blob::from_slice: status[b] = 2 (InvalidFieldElement) if any element >= r ----
+__global__ void k_blob_check(const uint32_t* __restrict__ blobs, int n, int32_t* __restrict__ status) {
+    size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= (size_t)n * KB_N) return;
+    const uint4* p = reinterpret_cast<const uint4*>(blobs + gid * 8);
+    uint4 a = __ldg(p), b = __ldg(p + 1);
+    Fr v;
+    v.l[7] = bswap32(a.x); v.l[6] = bswap32(a.y); v.l[5] = bswap32(a.z); v.l[4] = bswap32(a.w);
+    v.l[3] = bswap32(b.x); v.l[2] = bswap32(b.y); v.l[1] = bswap32(b.z); v.l[0] = bswap32(b.w);
+    if (fr_plain_geq_r(v)) status[gid >> 12] = KB_INVALID_FIELD_ELEMENT;
+}
+// 32-byte big-endian scalars (z or y): status 7 (NotInFiniteField) if >= r; out = canonical limbs
+__global__ void k_scalar_check(const uint32_t* __restrict__ in, int n, Fr* __restrict__ out, int32_t* __restrict__ status) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Fr v; fr_load_be(v, in + (size_t)i * 8);
+    if (fr_plain_geq_r(v)) { if (status[i] == 0) status[i] = KB_SCALAR_NOT_IN_FIELD; }
+    out[i] = v;
+}
+
+// ---- Blob::challenge: z = SHA-256("FSBLOBVERIFY_V1_" | u128_be(4096) | blob | compress(C)) mod r, canonical ----
+__global__ void k_challenge(const uint32_t* __restrict__ blobs, const uint32_t* __restrict__ comm48, int n, const int32_t* __restrict__ status,
+                            Fr* __restrict__ z_out) {
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= n) return;
+    if (status[b] != 0) { Fr zz; fr_zero(zz); z_out[b] = zz; return; }
+    const uint4* bp = reinterpret_cast<const uint4*>(blobs + (size_t)b * (KB_N * 8));
+    uint32_t h[8], w[16];
+    sha256_init(h);
+    // block 0: domain tag, degree, first 32 bytes of the blob
+    w[0] = 0x4653424c; w[1] = 0x4f425645; w[2] = 0x52494659; w[3] = 0x5f56315f;   // "FSBLOBVERIFY_V1_"
+    w[4] = 0; w[5] = 0; w[6] = 0; w[7] = KB_N;
+    uint4 c0 = __ldg(bp), c1 = __ldg(bp + 1);
+    w[8] = bswap32(c0.x); w[9] = bswap32(c0.y); w[10] = bswap32(c0.z); w[11] = bswap32(c0.w);
+    w[12] = bswap32(c1.x); w[13] = bswap32(c1.y); w[14] = bswap32(c1.z); w[15] = bswap32(c1.w);
+    sha256_block(h, w);
+    // blocks 1..2047: blob bytes [64k-32, 64k+32)
+#pragma unroll 1
+    for (int k = 1; k < 2048; k++) {
+        const uint4* p = bp + (4 * k - 2);
+        uint4 v0 = __ldg(p), v1 = __ldg(p + 1), v2 = __ldg(p + 2), v3 = __ldg(p + 3);
+        w[0] = bswap32(v0.x); w[1] = bswap32(v0.y); w[2] = bswap32(v0.z); w[3] = bswap32(v0.w);
+        w[4] = bswap32(v1.x); w[5] = bswap32(v1.y); w[6] = bswap32(v1.z); w[7] = bswap32(v1.w);
+        w[8] = bswap32(v2.x); w[9] = bswap32(v2.y); w[10] = bswap32(v2.z); w[11] = bswap32(v2.w);
+        w[12] = bswap32(v3.x); w[13] = bswap32(v3.y); w[14] = bswap32(v3.z); w[15] = bswap32(v3.w);
+        sha256_block(h, w);
+    }
+    // block 2048: last 32 blob bytes + first 32 bytes of the commitment
+    {
+        const uint4* p = bp + (4 * 2048 - 2);
+        uint4 v0 = __ldg(p), v1 = __ldg(p + 1);
+        const uint32_t* cp = comm48 + (size_t)b * 12;
+        w[0] = bswap32(v0.x); w[1] = bswap32(v0.y); w[2] = bswap32(v0.z); w[3] = bswap32(v0.w);
+        w[4] = bswap32(v1.x); w[5] = bswap32(v1.y); w[6] = bswap32(v1.z); w[7] = bswap32(v1.w);
+#pragma unroll
+        for (int k = 0; k < 8; k++) w[8 + k] = bswap32(cp[k]);
+        sha256_block(h, w);
+        // block 2049: last 16 commitment bytes, padding, bit length (131152 * 8 = 1049216 = 0x100280)
+#pragma unroll
+        for (int k = 0; k < 4; k++) w[k] = bswap32(cp[8 + k]);
+        w[4] = 0x80000000u;
+#pragma unroll
+        for (int k = 5; k < 15; k++) w[k] = 0;
+        w[15] = 131152u * 8u;
+        sha256_block(h, w);
+    }
+    Fr z;
+#pragma unroll
+    for (int k = 0; k < 8; k++) z.l[7 - k] = h[k];
+    fr_reduce_256(z);
+    z_out[b] = z;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Evaluation, phase 1.  CTA per blob, EV_THREADS threads, EV_PER = 4096/EV_THREADS denominators per thread
+// (element index i = k*EV_THREADS + tid).  d_i = z - w_i; if some d_m == 0 (z in the domain, poly.rs:14-18) the
+// index m is recorded and that factor is replaced by 1.  Writes the product of all 4096 factors.
+// ---------------------------------------------------------------------------------------------------------
+#define EV_THREADS 512
+#define EV_PER 8
+__device__ __forceinline__ void cta_tree_up(Fr* tree, const Fr& leaf, int tid) {
+    // tree[EV_THREADS + tid] = leaf; internal node n has children 2n, 2n+1; root at 1
+    tree[EV_THREADS + tid] = leaf;
+    __syncthreads();
+#pragma unroll 1
+    for (int width = EV_THREADS / 2; width >= 1; width >>= 1) {
+        if (tid < width) { Fr a = tree[2 * (width + tid)], b = tree[2 * (width + tid) + 1], r; fr_mul(r, a, b); tree[width + tid] = r; }
+        __syncthreads();
+    }
+}
+__global__ void __launch_bounds__(EV_THREADS) k_eval_prod(const Fr* __restrict__ z_canon, const Fr* __restrict__ roots, int n,
+                                                           Fr* __restrict__ prod_out, int32_t* __restrict__ indomain_out) {
+    __shared__ Fr tree[2 * EV_THREADS];
+    __shared__ int s_m;
+    const int b = blockIdx.x, tid = threadIdx.x;
+    if (tid == 0) s_m = -1;
+    __syncthreads();
+    Fr z; { Fr zc = z_canon[b]; fr_to_mont(z, zc); }
+    Fr local; fr_set(local, c_k.fr_one);
+#pragma unroll 1
+    for (int k = 0; k < EV_PER; k++) {
+        int i = k * EV_THREADS + tid;
+        Fr d; fr_sub(d, z, roots[i]);
+        if (fr_is_zero(d)) s_m = i; else fr_mul(local, local, d);
+    }
+    cta_tree_up(tree, local, tid);
+    if (tid == 0) { prod_out[b] = tree[1]; indomain_out[b] = s_m; }
+}
+// phase 2: one thread per blob inverts the product (32 blobs per warp, one Fermat inversion per lane)
+__global__ void k_eval_inv(Fr* __restrict__ prod, int n) {
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= n) return;
+    Fr p = prod[b], r; fr_inv(r, p); prod[b] = r;
+}
+// phase 3: walk the tree down, recover 1/d_i, evaluate; optionally emit the quotient.
+//   y (canonical)  = (z^N - 1)/N * sum_i f_i * w_i / (z - w_i)                      [poly.rs:23-32]
+//   q_i (canonical) = (f_i - y)/(w_i - z) = (y - f_i) * inv_i                        [poly.rs:45-49]
+//   z == w_m:  y = f_m;  q_m = sum_{j!=m} (f_j - y) w_j / (w_m (w_m - w_j)) = -w_m^-1 * sum_{j!=m} q_j w_j   [poly.rs:50-63]
+template <bool WANT_Q>
+__global__ void __launch_bounds__(EV_THREADS, 1) k_eval_finish(const uint32_t* __restrict__ blobs, const Fr* __restrict__ z_canon,
+                                                             const Fr* __restrict__ roots, const Fr* __restrict__ prod_inv,
+                                                             const int32_t* __restrict__ indomain, const int32_t* __restrict__ status, int n,
+                                                             Fr* __restrict__ y_out, uint32_t* __restrict__ q_out) {
+    __shared__ Fr tree[2 * EV_THREADS];
+    __shared__ Fr s_y;
+    const int b = blockIdx.x, tid = threadIdx.x;
+    if (status[b] != 0) return;
+    const int m = indomain[b];
+    Fr z; { Fr zc = z_canon[b]; fr_to_mont(z, zc); }
+    Fr one; fr_set(one, c_k.fr_one);
+    // recompute the factors and the per-thread prefix products
+    Fr pre[EV_PER];            // pre[k] = product of this thread's factors 0..k-1
+    Fr local = one;
+#pragma unroll
+    for (int k = 0; k < EV_PER; k++) {
+        int i = k * EV_THREADS + tid;
+        Fr d; fr_sub(d, z, roots[i]);
+        pre[k] = local;
+        if (i != m) fr_mul(local, local, d);
+    }
+    cta_tree_up(tree, local, tid);
+    // down-sweep: tree[n] becomes the inverse of the product under node n
+    if (tid == 0) tree[1] = prod_inv[b];
+    __syncthreads();
+#pragma unroll 1
+    for (int width = 1; width < EV_THREADS; width <<= 1) {
+        if (tid < width) {
+            int nd = width + tid;
+            Fr inv = tree[nd], l = tree[2 * nd], r = tree[2 * nd + 1], il, ir;
+            fr_mul(il, inv, r); fr_mul(ir, inv, l);
+            tree[2 * nd] = il; tree[2 * nd + 1] = ir;
+        }
+        __syncthreads();
+    }
+    Fr run = tree[EV_THREADS + tid];          // inverse of this thread's product
+    __syncthreads();
+    // back-substitute: inv[k] = run * pre[k]; run *= d_k   (k descending)
+    Fr (&inv)[EV_PER] = pre;      // inv[k] overwrites pre[k] in place (register budget)
+    Fr acc; fr_zero(acc);
+#pragma unroll
+    for (int k = EV_PER - 1; k >= 0; k--) {
+        int i = k * EV_THREADS + tid;
+        Fr w = roots[i];
+        if (i == m) { fr_zero(inv[k]); continue; }
+        Fr d; fr_sub(d, z, w);
+        fr_mul(inv[k], run, inv[k]);
+        fr_mul(run, run, d);
+        // term = f_i * (w_i * inv_i): canonical f times Montgomery value -> canonical
+        Fr f; fr_load_be(f, blobs + ((size_t)b * KB_N + i) * 8);
+        Fr t; fr_mul(t, w, inv[k]); fr_mul(t, f, t);
+        fr_add(acc, acc, t);
+    }
+    // CTA sum of acc
+    tree[tid] = acc;
+    __syncthreads();
+#pragma unroll 1
+    for (int stride = EV_THREADS / 2; stride >= 1; stride >>= 1) {
+        if (tid < stride) { Fr a = tree[tid], c = tree[tid + stride]; fr_add(a, a, c); tree[tid] = a; }
+        __syncthreads();
+    }
+    if (tid == 0) {
+        Fr y;
+        if (m >= 0) {
+            fr_load_be(y, blobs + ((size_t)b * KB_N + m) * 8);
+        } else {
+            Fr zn = z;
+#pragma unroll 1
+            for (int k = 0; k < 12; k++) fr_sqr(zn, zn);       // z^4096
+            fr_sub(zn, zn, one);
+            Fr ninv; fr_set(ninv, c_k.fr_ninv);
+            fr_mul(zn, zn, ninv);                               // (z^N - 1)/N, Montgomery
+            Fr s = tree[0];
+            fr_mul(y, s, zn);                                   // canonical
+        }
+        s_y = y; y_out[b] = y;
+    }
+    if (!WANT_Q) return;
+    __syncthreads();
+    Fr y = s_y;
+    Fr qsum; fr_zero(qsum);
+#pragma unroll
+    for (int k = 0; k < EV_PER; k++) {
+        int i = k * EV_THREADS + tid;
+        if (i == m) continue;
+        Fr f; fr_load_be(f, blobs + ((size_t)b * KB_N + i) * 8);
+        Fr q; fr_sub(q, y, f); fr_mul(q, q, inv[k]);            // canonical
+        uint4* dst = reinterpret_cast<uint4*>(q_out + ((size_t)b * KB_N + i) * 8);
+        dst[0] = make_uint4(q.l[0], q.l[1], q.l[2], q.l[3]); dst[1] = make_uint4(q.l[4], q.l[5], q.l[6], q.l[7]);
+        if (m >= 0) { Fr t; fr_mul(t, q, roots[i]); fr_add(qsum, qsum, t); }
+    }
+    if (m >= 0) {          // uniform across the CTA
+        __syncthreads();
+        tree[tid] = qsum;
+        __syncthreads();
+#pragma unroll 1
+        for (int stride = EV_THREADS / 2; stride >= 1; stride >>= 1) {
+            if (tid < stride) { Fr a = tree[tid], c = tree[tid + stride]; fr_add(a, a, c); tree[tid] = a; }
+            __syncthreads();
+        }
+        if (tid == 0) {
+            // w_m^-1 = w^(4096 - e) where w_m = w^e, e = brp(m)
+            uint32_t e = brp12((uint32_t)m);
+            Fr winv = roots[brp12((KB_N - e) & (KB_N - 1))];
+            Fr q = tree[0], nq; fr_mul(q, q, winv); fr_neg(nq, q);
+            uint4* dst = reinterpret_cast<uint4*>(q_out + ((size_t)b * KB_N + m) * 8);
+            dst[0] = make_uint4(nq.l[0], nq.l[1], nq.l[2], nq.l[3]); dst[1] = make_uint4(nq.l[4], nq.l[5], nq.l[6], nq.l[7]);
+        }
+    }
+}
+
+}  // namespace kb200

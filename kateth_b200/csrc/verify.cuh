@@ -1,0 +1,158 @@
+// verify.cuh -- the verification side: G1 decompression + subgroup check, and the random-linear-combination sums
+// of batch verification.
+//
+// Replaces (file:line in /root/reference):
+//   P1::decompress                    src/bls.rs:505-531        (k_g1_decompress)
+//   Setup::verify_proof_batch         src/kzg/setup.rs:115-161  (k_batch_r, k_rlc, k_rlc_finish, k_rlc_combine) up to,
+//                                                               but not including, the two-pairing check (host)
+//   Setup::verify_proof_inner         src/kzg/setup.rs:84-94    (same kernels in "raw" mode, weights = 1)
+// kateth's quirks are reproduced: r = SHA-256("RCKZGBATCH___V1_" | u128_be(4096) | u128_be(n)) mod r depends on n
+// only, and rpowers = [r, r, r^2, r^3, ...] because Fr::pow(x, 0) returns x (src/bls.rs:169-187).
+//
+// Per GPU the result is one 320-byte record {A, B, C as affine Montgomery points, s}:
+//   A = sum w_i pi_i,  B = sum w_i z_i pi_i,  C = sum w_i C_i,  s = sum w_i y_i        (w_i = rpowers[i])
+// Records of several GPUs are exchanged with one all-gather, then k_rlc_combine forms the pairing operands
+//   lhs = sum_g A_g            rhs = sum_g C_g - (sum_g s_g) * G1 + sum_g B_g
+// and the host checks e(lhs, [tau]_2) == e(rhs, G2).
+#pragma once
+#include "poly.cuh"
+
+namespace kb200 {
+
+struct RlcRecord { G1Affine a, b, c; Fr s; };   // 3*96 + 32 = 320 bytes
+static_assert(sizeof(RlcRecord) == 320, "record layout");
+
+// in48: n compressed points; out: affine Montgomery; status[i] set to 3/4/5 on failure (kept if already non-zero)
+__global__ void __launch_bounds__(64) k_g1_decompress(const uint32_t* __restrict__ in48, int n, G1Affine* __restrict__ out, int32_t* __restrict__ status) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t w[12];
+    for (int k = 0; k < 12; k++) w[k] = in48[(size_t)i * 12 + k];
+    G1Affine p;
+    int st = g1_uncompress(p, w);
+    if (st == KB_OK && !g1_in_subgroup(p)) st = KB_G1_NOT_IN_GROUP;
+    if (st != KB_OK) { fp_zero(p.x); fp_zero(p.y); if (status[i] == 0) status[i] = st; }
+    out[i] = p;
+}
+
+// r (Montgomery) for a batch of n_total proofs
+__global__ void k_batch_r(uint32_t n_total, Fr* r_mont) {
+    uint32_t h[8], w[16];
+    sha256_init(h);
+    w[0] = 0x52434b5a; w[1] = 0x47424154; w[2] = 0x43485f5f; w[3] = 0x5f56315f;   // "RCKZGBATCH___V1_"
+    w[4] = 0; w[5] = 0; w[6] = 0; w[7] = KB_N;
+    w[8] = 0; w[9] = 0; w[10] = 0; w[11] = n_total;
+    w[12] = 0x80000000u; w[13] = 0; w[14] = 0; w[15] = 48 * 8;
+    sha256_block(h, w);
+    Fr v;
+    for (int k = 0; k < 8; k++) v.l[7 - k] = h[k];
+    fr_reduce_256(v);
+    Fr m; fr_to_mont(m, v);
+    *r_mont = m;
+}
+
+#define RLC_THREADS 64
+// grid (ceil(n/RLC_THREADS), 3).  which = blockIdx.y: 0 -> w_i*pi_i, 1 -> (w_i z_i)*pi_i, 2 -> w_i*C_i.
+// raw != 0: weights are 1 (single-proof check, src/kzg/setup.rs:84-94 rearranged to avoid the G2 scalar mul:
+//   e(pi, [tau]_2) == e(C - y G1 + z pi, G2)).
+__global__ void __launch_bounds__(RLC_THREADS) k_rlc(const G1Affine* __restrict__ proofs, const G1Affine* __restrict__ comms,
+                                                      const Fr* __restrict__ z_canon, const Fr* __restrict__ y_canon, int n, uint32_t index_offset,
+                                                      const Fr* __restrict__ r_mont, int raw, G1* __restrict__ partials, Fr* __restrict__ s_partials) {
+    __shared__ G1 sm[RLC_THREADS / 2];
+    __shared__ Fr sms[RLC_THREADS];
+    const int tid = threadIdx.x, which = blockIdx.y;
+    const int i = blockIdx.x * RLC_THREADS + tid;
+    G1 acc; g1_set_inf(acc);
+    Fr s; fr_zero(s);
+    if (i < n) {
+        Fr wgt;    // Montgomery
+        if (raw) fr_set(wgt, c_k.fr_one);
+        else {
+            uint32_t gi = index_offset + (uint32_t)i;
+            Fr r = *r_mont;
+            fr_pow_u32(wgt, r, gi == 0 ? 1u : gi);     // Fr::pow(r, 0) == r quirk
+        }
+        Fr k;      // canonical scalar
+        if (which == 1) { Fr z = z_canon[i]; fr_mul(k, z, wgt); }
+        else fr_from_mont(k, wgt);
+        G1Affine p = (which == 2) ? comms[i] : proofs[i];
+        g1_mul(acc, p, k);
+        if (which == 0) { Fr y = y_canon[i]; fr_mul(s, y, wgt); }
+    }
+#pragma unroll 1
+    for (int stride = RLC_THREADS / 2; stride >= 1; stride >>= 1) {
+        if (tid >= stride && tid < 2 * stride) sm[tid - stride] = acc;
+        __syncthreads();
+        if (tid < stride) g1_add(acc, sm[tid]);
+        __syncthreads();
+    }
+    if (tid == 0) partials[(size_t)which * gridDim.x + blockIdx.x] = acc;
+    if (which == 0) {
+        sms[tid] = s;
+        __syncthreads();
+#pragma unroll 1
+        for (int stride = RLC_THREADS / 2; stride >= 1; stride >>= 1) {
+            if (tid < stride) { Fr a = sms[tid], c = sms[tid + stride]; fr_add(a, a, c); sms[tid] = a; }
+            __syncthreads();
+        }
+        if (tid == 0) s_partials[blockIdx.x] = sms[0];
+    }
+}
+// grid 3 CTAs of RLC_FIN_THREADS: CTA `which` reduces its row of partials, normalises, writes the record field.
+#define RLC_FIN_THREADS 128
+__global__ void __launch_bounds__(RLC_FIN_THREADS) k_rlc_finish(const G1* __restrict__ partials, const Fr* __restrict__ s_partials, int nparts,
+                                                                 RlcRecord* __restrict__ rec) {
+    __shared__ G1 sm[RLC_FIN_THREADS / 2];
+    __shared__ Fr sms[RLC_FIN_THREADS];
+    const int tid = threadIdx.x, which = blockIdx.x;
+    G1 acc; g1_set_inf(acc);
+    for (int k = tid; k < nparts; k += RLC_FIN_THREADS) { G1 t = partials[(size_t)which * nparts + k]; g1_add(acc, t); }
+#pragma unroll 1
+    for (int stride = RLC_FIN_THREADS / 2; stride >= 1; stride >>= 1) {
+        if (tid >= stride && tid < 2 * stride) sm[tid - stride] = acc;
+        __syncthreads();
+        if (tid < stride) g1_add(acc, sm[tid]);
+        __syncthreads();
+    }
+    if (tid == 0) {
+        G1Affine a; g1_to_affine(a, acc);
+        if (which == 0) rec->a = a; else if (which == 1) rec->b = a; else rec->c = a;
+    }
+    if (which == 0) {
+        Fr s; fr_zero(s);
+        for (int k = tid; k < nparts; k += RLC_FIN_THREADS) { Fr t = s_partials[k]; fr_add(s, s, t); }
+        sms[tid] = s;
+        __syncthreads();
+#pragma unroll 1
+        for (int stride = RLC_FIN_THREADS / 2; stride >= 1; stride >>= 1) {
+            if (tid < stride) { Fr a = sms[tid], c = sms[tid + stride]; fr_add(a, a, c); sms[tid] = a; }
+            __syncthreads();
+        }
+        if (tid == 0) rec->s = sms[0];
+    }
+}
+// Combine the records of all ranks into the two G1 pairing operands, as plain (non-Montgomery) affine coordinates:
+// out[0..11] = lhs.x, [12..23] = lhs.y, [24..35] = rhs.x, [36..47] = rhs.y, out[48] = lhs is infinity, out[49] = rhs is infinity.
+__global__ void k_rlc_combine(const RlcRecord* __restrict__ recs, int nrec, uint32_t* __restrict__ out) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    G1 A, B, C; g1_set_inf(A); g1_set_inf(B); g1_set_inf(C);
+    Fr s; fr_zero(s);
+    for (int g = 0; g < nrec; g++) {
+        RlcRecord r = recs[g];
+        g1_madd_signed(A, r.a, false); g1_madd_signed(B, r.b, false); g1_madd_signed(C, r.c, false);
+        fr_add(s, s, r.s);
+    }
+    // rhs = C - s*G1 + B = C + s*(-G1) + B
+    G1Affine ng; fp_set(ng.x, c_k.g1_gen_x); fp_set(ng.y, c_k.g1_neg_gen_y);
+    G1 t; g1_mul(t, ng, s);
+    g1_add(C, t); g1_add(C, B);
+    G1Affine la, ra; g1_to_affine(la, A); g1_to_affine(ra, C);
+    Fp v;
+    fp_from_mont(v, la.x); for (int k = 0; k < 12; k++) out[k] = v.l[k];
+    fp_from_mont(v, la.y); for (int k = 0; k < 12; k++) out[12 + k] = v.l[k];
+    fp_from_mont(v, ra.x); for (int k = 0; k < 12; k++) out[24 + k] = v.l[k];
+    fp_from_mont(v, ra.y); for (int k = 0; k < 12; k++) out[36 + k] = v.l[k];
+    out[48] = g1a_is_inf(la) ? 1u : 0u; out[49] = g1a_is_inf(ra) ? 1u : 0u;
+}
+
+}  // namespace kb200

@@ -1,0 +1,286 @@
+"""ctypes binding of include/kateth_b200.h and the `Setup` mirror class (see package docstring)."""
+import ctypes as C
+import os
+
+BYTES_PER_BLOB = 131072
+RECORD_BYTES = 320
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+_STATUS_NAMES = {
+    1: "Blob(InvalidLen)", 2: "Blob(InvalidFieldElement)", 3: "Bls(ECGroup(InvalidEncoding))", 4: "Bls(ECGroup(NotOnCurve))",
+    5: "Bls(ECGroup(NotInGroup))", 6: "Bls(FiniteField(InvalidEncoding))", 7: "Bls(FiniteField(NotInFiniteField))",
+    -1: "CUDA", -2: "Io", -3: "Serde", -10: "InvalidLenG1Lagrange", -11: "InvalidLenG2Monomial", -20: "BadArgument",
+}
+
+
+class KzgError(Exception):
+    """Mirror of kateth's kzg::Error / LoadSetupError (src/kzg/mod.rs:15-31, src/kzg/setup.rs:20-28)."""
+
+    def __init__(self, status, detail=""):
+        super().__init__("%s (status %d)%s" % (_STATUS_NAMES.get(status, "?"), status, (": " + detail) if detail else ""))
+        self.status = status
+
+
+def lib_path():
+    return os.path.join(_HERE, "libkateth_b200.so")
+
+
+_lib = None
+
+
+class _Info(C.Structure):
+    _fields_ = [("window_bits", C.c_int), ("windows", C.c_int), ("table_bytes", C.c_uint64), ("kernel_launches", C.c_uint64),
+                ("device", C.c_int), ("sm_count", C.c_int), ("setup_seconds", C.c_double)]
+
+
+# every symbol include/kateth_b200.h declares (tests/test_abi.py checks the header against this list and the .so)
+SYMBOLS = [
+    "kb200_setup_load_json", "kb200_setup_load_raw", "kb200_setup_free", "kb200_set_stream", "kb200_last_error",
+    "kb200_blob_to_commitment", "kb200_blob_to_commitment_device", "kb200_compute_blob_proof", "kb200_compute_blob_proof_device",
+    "kb200_compute_proof", "kb200_compute_proof_device", "kb200_verify_proof", "kb200_verify_proof_batch", "kb200_verify_blob_proof",
+    "kb200_verify_blob_proof_batch", "kb200_verify_blob_proof_batch_device", "kb200_verify_blob_proof_batch_partial_device",
+    "kb200_verify_batch_finish_device", "kb200_last_pairing_operands", "kb200_get_info", "kb200_test_fp_mul", "kb200_test_fr_mul",
+    "kb200_test_g1_decompress", "kb200_test_mac_peak", "kb200_test_host_pairing",
+]
+
+
+def lib():
+    """Load libkateth_b200.so.  Fails loudly if it has not been built (python -c 'import __graft_entry__ as g; g.build()')."""
+    global _lib
+    if _lib is None:
+        p = lib_path()
+        if not os.path.exists(p):
+            raise RuntimeError("libkateth_b200.so is not built (%s); run __graft_entry__.build(). There is no CPU fallback." % p)
+        _lib = C.CDLL(p)
+        _lib.kb200_last_error.restype = C.c_char_p
+        for name in SYMBOLS:
+            if name not in ("kb200_last_error", "kb200_setup_free"):
+                getattr(_lib, name).restype = C.c_int
+        _lib.kb200_setup_free.restype = None
+        _lib.kb200_setup_free.argtypes = [C.c_void_p]
+    return _lib
+
+
+def _vp(x):
+    return C.c_void_p(int(x))
+
+
+def _check(st):
+    if st != 0:
+        raise KzgError(st, lib().kb200_last_error().decode() if st < 0 else "")
+
+
+class Setup:
+    """kateth::kzg::Setup<4096, 65> (src/kzg/setup.rs:37-276) backed by the GPU engine."""
+
+    def __init__(self, handle):
+        self._h = handle
+
+    # -- Setup::load_json (src/kzg/setup.rs:46-82)
+    @classmethod
+    def load_json(cls, path, device=0, window_bits=0):
+        h = C.c_void_p()
+        _check(lib().kb200_setup_load_json(os.fsencode(path), int(device), int(window_bits), C.byref(h)))
+        return cls(h)
+
+    def close(self):
+        if self._h:
+            lib().kb200_setup_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_stream(self, cuda_stream_ptr):
+        _check(lib().kb200_set_stream(self._h, _vp(cuda_stream_ptr)))
+
+    def info(self):
+        i = _Info()
+        _check(lib().kb200_get_info(self._h, C.byref(i)))
+        return {k: getattr(i, k) for k, _ in _Info._fields_}
+
+    # -- Setup::blob_to_commitment (src/kzg/setup.rs:167-171), returns the compressed commitment
+    def blob_to_commitment(self, blob):
+        blob = bytes(blob)
+        if len(blob) != BYTES_PER_BLOB:
+            raise KzgError(1)
+        out = C.create_string_buffer(48)
+        _check(lib().kb200_blob_to_commitment(self._h, blob, C.c_size_t(1), out, None))
+        return out.raw
+
+    # -- Setup::blob_proof (src/kzg/setup.rs:177-183)
+    def blob_proof(self, blob, commitment):
+        blob, commitment = bytes(blob), bytes(commitment)
+        if len(blob) != BYTES_PER_BLOB:
+            raise KzgError(1)
+        if len(commitment) != 48:      # &Bytes48 in kateth: unrepresentable; the vector harness maps it to an error
+            raise KzgError(3)
+        out = C.create_string_buffer(48)
+        _check(lib().kb200_compute_blob_proof(self._h, blob, commitment, C.c_size_t(1), out, None))
+        return out.raw
+
+    # -- Setup::proof (src/kzg/setup.rs:185-194) -> (proof, y)
+    def proof(self, blob, z):
+        blob, z = bytes(blob), bytes(z)
+        if len(blob) != BYTES_PER_BLOB:
+            raise KzgError(1)
+        if len(z) != 32:
+            raise KzgError(6)
+        out, y = C.create_string_buffer(48), C.create_string_buffer(32)
+        _check(lib().kb200_compute_proof(self._h, blob, z, C.c_size_t(1), out, y, None))
+        return out.raw, y.raw
+
+    # -- Setup::verify_proof (src/kzg/setup.rs:96-113): order proof, commitment, point, eval
+    def verify_proof(self, proof, commitment, z, y):
+        proof, commitment, z, y = bytes(proof), bytes(commitment), bytes(z), bytes(y)
+        if len(proof) != 48 or len(commitment) != 48:
+            raise KzgError(3)
+        if len(z) != 32 or len(y) != 32:
+            raise KzgError(6)
+        ok = C.c_int(0)
+        _check(lib().kb200_verify_proof(self._h, proof, commitment, z, y, C.byref(ok)))
+        return bool(ok.value)
+
+    # -- Setup::verify_blob_proof (src/kzg/setup.rs:208-221)
+    def verify_blob_proof(self, blob, commitment, proof):
+        blob, commitment, proof = bytes(blob), bytes(commitment), bytes(proof)
+        if len(blob) != BYTES_PER_BLOB:
+            raise KzgError(1)
+        if len(commitment) != 48 or len(proof) != 48:
+            raise KzgError(3)
+        ok = C.c_int(0)
+        _check(lib().kb200_verify_blob_proof(self._h, blob, commitment, proof, C.byref(ok)))
+        return bool(ok.value)
+
+    # -- Setup::verify_blob_proof_batch (src/kzg/setup.rs:247-275)
+    def verify_blob_proof_batch(self, blobs, commitments, proofs):
+        assert len(blobs) == len(commitments) == len(proofs)   # kateth: assert_eq! (panics)
+        for b in blobs:
+            if len(b) != BYTES_PER_BLOB:
+                raise KzgError(1)
+        for c in list(commitments) + list(proofs):
+            if len(c) != 48:
+                raise KzgError(3)
+        n = len(blobs)
+        ok = C.c_int(0)
+        _check(lib().kb200_verify_blob_proof_batch(self._h, b"".join(bytes(b) for b in blobs), b"".join(bytes(c) for c in commitments),
+                                                   b"".join(bytes(p) for p in proofs), C.c_size_t(n), C.byref(ok), None))
+        return bool(ok.value)
+
+    def last_pairing_operands(self):
+        a, b = C.create_string_buffer(48), C.create_string_buffer(48)
+        _check(lib().kb200_last_pairing_operands(self._h, a, b))
+        return a.raw, b.raw
+
+    # ---------------- batch / resident-data extensions (the throughput surface) ----------------
+    def blob_to_commitment_many(self, blobs_concat, n):
+        out, st = C.create_string_buffer(48 * n), (C.c_int32 * n)()
+        rc = lib().kb200_blob_to_commitment(self._h, blobs_concat, C.c_size_t(n), out, st)
+        if rc < 0:
+            _check(rc)
+        return out.raw, list(st)
+
+    def blob_proof_many(self, blobs_concat, commitments_concat, n):
+        out, st = C.create_string_buffer(48 * n), (C.c_int32 * n)()
+        rc = lib().kb200_compute_blob_proof(self._h, blobs_concat, commitments_concat, C.c_size_t(n), out, st)
+        if rc < 0:
+            _check(rc)
+        return out.raw, list(st)
+
+    def proof_many(self, blobs_concat, z_concat, n):
+        out, y, st = C.create_string_buffer(48 * n), C.create_string_buffer(32 * n), (C.c_int32 * n)()
+        rc = lib().kb200_compute_proof(self._h, blobs_concat, z_concat, C.c_size_t(n), out, y, st)
+        if rc < 0:
+            _check(rc)
+        return out.raw, y.raw, list(st)
+
+    def verify_proof_batch(self, proofs_concat, commitments_concat, z_concat, y_concat, n):
+        ok = C.c_int(0)
+        _check(lib().kb200_verify_proof_batch(self._h, proofs_concat, commitments_concat, z_concat, y_concat, C.c_size_t(n), C.byref(ok), None))
+        return bool(ok.value)
+
+    def verify_blob_proof_batch_concat(self, blobs_concat, commitments_concat, proofs_concat, n):
+        ok = C.c_int(0)
+        _check(lib().kb200_verify_blob_proof_batch(self._h, blobs_concat, commitments_concat, proofs_concat, C.c_size_t(n), C.byref(ok), None))
+        return bool(ok.value)
+
+    # device-pointer calls (integers = device addresses, e.g. torch.Tensor.data_ptr())
+    def blob_to_commitment_device(self, d_blobs, n, d_out48, d_status):
+        return lib().kb200_blob_to_commitment_device(self._h, _vp(d_blobs), C.c_size_t(n), _vp(d_out48), _vp(d_status))
+
+    def blob_proof_device(self, d_blobs, d_comm48, n, d_out48, d_status):
+        return lib().kb200_compute_blob_proof_device(self._h, _vp(d_blobs), _vp(d_comm48), C.c_size_t(n), _vp(d_out48), _vp(d_status))
+
+    def proof_device(self, d_blobs, d_z32, n, d_out48, d_y32, d_status):
+        return lib().kb200_compute_proof_device(self._h, _vp(d_blobs), _vp(d_z32), C.c_size_t(n), _vp(d_out48), _vp(d_y32), _vp(d_status))
+
+    def verify_blob_proof_batch_device(self, d_blobs, d_comm48, d_proofs48, n, d_status):
+        ok = C.c_int(0)
+        _check(lib().kb200_verify_blob_proof_batch_device(self._h, _vp(d_blobs), _vp(d_comm48), _vp(d_proofs48), C.c_size_t(n), C.byref(ok), _vp(d_status)))
+        return bool(ok.value)
+
+    def verify_partial_device(self, d_blobs, d_comm48, d_proofs48, n_local, index_offset, n_total, d_record, d_status):
+        return lib().kb200_verify_blob_proof_batch_partial_device(self._h, _vp(d_blobs), _vp(d_comm48), _vp(d_proofs48), C.c_size_t(n_local),
+                                                                  C.c_size_t(index_offset), C.c_size_t(n_total), _vp(d_record), _vp(d_status))
+
+    def verify_finish_device(self, d_records, n_records):
+        ok = C.c_int(0)
+        _check(lib().kb200_verify_batch_finish_device(self._h, _vp(d_records), C.c_size_t(n_records), C.byref(ok)))
+        return bool(ok.value)
+
+
+def shard_bounds(n_total, world_size, rank):
+    """Contiguous shard [lo, hi) of rank `rank`."""
+    return n_total * rank // world_size, n_total * (rank + 1) // world_size
+
+
+class BatchVerifier:
+    """verify_blob_kzg_proof_batch sharded over the ranks of a torch.distributed process group: every rank computes the
+    320-byte partial record of its contiguous shard on its GPU, ONE all_gather (NCCL over NVLink) exchanges the
+    records, and every rank finishes (sum of records -> two-pairing check on the host)."""
+
+    def __init__(self, setup, group=None):
+        self.setup, self.group = setup, group
+
+    def verify(self, d_blobs, d_comm48, d_proofs48, n_local, index_offset, n_total, d_status, record_tensor, gathered_tensor):
+        import torch.distributed as dist
+        rc = self.setup.verify_partial_device(d_blobs, d_comm48, d_proofs48, n_local, index_offset, n_total, record_tensor.data_ptr(), d_status)
+        if rc < 0:
+            _check(rc)
+        dist.all_gather_into_tensor(gathered_tensor, record_tensor, group=self.group)
+        world = gathered_tensor.numel() // RECORD_BYTES
+        return rc, self.setup.verify_finish_device(gathered_tensor.data_ptr(), world)
+
+
+class test_hooks:
+    @staticmethod
+    def fp_mul(a_u32, b_u32):
+        import numpy as np
+        a = np.ascontiguousarray(a_u32, dtype=np.uint32); b = np.ascontiguousarray(b_u32, dtype=np.uint32)
+        out = np.empty_like(a)
+        _check(lib().kb200_test_fp_mul(a.ctypes.data_as(C.c_void_p), b.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p), C.c_size_t(a.shape[0])))
+        return out
+
+    @staticmethod
+    def fr_mul(a_u32, b_u32):
+        import numpy as np
+        a = np.ascontiguousarray(a_u32, dtype=np.uint32); b = np.ascontiguousarray(b_u32, dtype=np.uint32)
+        out = np.empty_like(a)
+        _check(lib().kb200_test_fr_mul(a.ctypes.data_as(C.c_void_p), b.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p), C.c_size_t(a.shape[0])))
+        return out
+
+    @staticmethod
+    def g1_decompress(setup, points48):
+        n = len(points48)
+        st, out = (C.c_int32 * n)(), C.create_string_buffer(48 * n)
+        _check(lib().kb200_test_g1_decompress(setup._h, b"".join(points48), C.c_size_t(n), st, out))
+        return list(st), [out.raw[48 * i:48 * i + 48] for i in range(n)]
+
+    @staticmethod
+    def mac_peak(iters=4096):
+        a, b = C.c_double(0), C.c_double(0)
+        _check(lib().kb200_test_mac_peak(int(iters), C.byref(a), C.byref(b)))
+        return a.value, b.value

@@ -1,0 +1,213 @@
+"""GPU parity tests (run with -m gpu on a B200): the CUDA engine, called through the C ABI, against
+  (1) the CPU oracle on the same seeded inputs,
+  (2) the 253 sha-pinned consensus-spec-tests vectors (every handler kateth tests, src/kzg/setup.rs:319-463),
+  (3) size-independent properties at larger batch sizes.
+Bit-exact is the bar everywhere: 48-byte compressed G1, 32-byte scalars, booleans, error classes."""
+import hashlib, os, random, sys
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "tools"))
+import reconstruct_vectors as RV
+
+pytestmark = pytest.mark.gpu
+R = RV.R
+P = 0x1a0111ea397fe69a4b1ba7b6434bacd764774b84f38512bf6730d2a0f6b0f6241eabfffeb153ffffb9feffffffffaaab
+
+
+def rand_blob(seed):
+    """Canonical field elements: SHA-256 counter stream, top bit cleared, rejected if >= r."""
+    out = bytearray()
+    ctr = 0
+    while len(out) < 131072:
+        h = bytearray(hashlib.sha256(b"kb200-blob" + seed.to_bytes(8, "little") + ctr.to_bytes(8, "little")).digest())
+        ctr += 1
+        h[0] &= 0x7f
+        if int.from_bytes(h, "big") < R:
+            out += h
+    return bytes(out)
+
+
+def limbs32(v, n):
+    return [(v >> (32 * i)) & 0xffffffff for i in range(n)]
+
+
+# ---------------------------------------------------------------- K1: field products vs the oracle
+def test_fp_mul_bit_exact():
+    import kateth_b200 as K
+    from oracle import oracle as O
+    rng = random.Random(1)
+    edge = [0, 1, 2, P - 1, P - 2, (P - 1) // 2, 2 ** 380, 2 ** 381 - 1 - (2 ** 381 - 1 >= P) * (2 ** 381 - P), 0xffffffff, 2 ** 64 - 1]
+    vals = [(a, b) for a in edge for b in edge] + [(rng.randrange(P), rng.randrange(P)) for _ in range(20000)]
+    a = np.array([limbs32(x, 12) for x, _ in vals], dtype=np.uint32)
+    b = np.array([limbs32(y, 12) for _, y in vals], dtype=np.uint32)
+    got = K.test_hooks.fp_mul(a, b)
+    exp = O.fp_mul_raw(a.view(np.uint64), b.view(np.uint64)).view(np.uint32)
+    assert np.array_equal(got, exp)
+    # and against plain integers: a*b/2^384 mod p
+    rinv = pow(2 ** 384, -1, P)
+    for k in range(0, len(vals), 997):
+        x, y = vals[k]
+        assert sum(int(got[k][i]) << (32 * i) for i in range(12)) == x * y * rinv % P
+
+
+def test_fr_mul_bit_exact():
+    import kateth_b200 as K
+    from oracle import oracle as O
+    rng = random.Random(2)
+    edge = [0, 1, 2, R - 1, R - 2, (R - 1) // 2, 2 ** 254, 0xffffffff, 2 ** 64 - 1]
+    vals = [(a, b) for a in edge for b in edge] + [(rng.randrange(R), rng.randrange(R)) for _ in range(20000)]
+    a = np.array([limbs32(x, 8) for x, _ in vals], dtype=np.uint32)
+    b = np.array([limbs32(y, 8) for _, y in vals], dtype=np.uint32)
+    got = K.test_hooks.fr_mul(a, b)
+    exp = O.fr_mul_raw(a.view(np.uint64), b.view(np.uint64)).view(np.uint32)
+    assert np.array_equal(got, exp)
+
+
+# ---------------------------------------------------------------- golden commitments / proofs
+GOLD_COMM = {
+    0: "c00000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000",
+    1: "a572cbea904d67468808c8eb50a9450c9721db309128012543902d0ac358a62ae28f75bb8f1c7c42c39a8c5529bf0f4e",
+    2: "a421e229565952cfff4ef3517100a97da1d4fe57956fa50a442f92af03b1bf37adacc8ad4ed209b31287ea5bb94d9d06",
+    5: "b7f1d3a73197d7942695638c4fa9ac0fc3688c4f9774b905a14e3a3f171bac586c55e83ff97a1aeffb3af00adb22c6bb",
+    6: "93efc82d2017e9c57834a1246463e64774e56183bb247c8fc9dd98c56817e878d97b05f5c8d900acf1fbbbca6f146556",
+}
+
+
+def test_golden_commitments(engine_setup):
+    vb = RV.valid_blobs()
+    for i, hexv in GOLD_COMM.items():
+        assert engine_setup.blob_to_commitment(vb[i]).hex() == hexv, i
+
+
+def test_golden_blob_proof_and_in_domain_proofs(engine_setup):
+    vb = RV.valid_blobs()
+    c = engine_setup.blob_to_commitment(vb[2])
+    assert engine_setup.blob_proof(vb[2], c).hex() == "a2aeea08a9cd37fb0b089b1938bbe7eedd4ea6120dc70f45d59ad077008d08be115b858350b1eff645148fe4470b65c8"
+    # r1 at z = 1 (in the domain, brp index 0) and z = omega (brp index 2048)
+    p, y = engine_setup.proof(vb[2], RV.FE_VALID[1])
+    assert p.hex() == "b0c829a8d2d3405304fecbea193e6c67f7c3912a6adc7c3737ad3f8a3b750425c1531a7426f03033a3994bc82a10609f"
+    assert y.hex() == "1824b159acc5056f998c4fefecbc4ff55884b7fa0003480200000001fffffffe"
+    p, y = engine_setup.proof(vb[2], RV.FE_VALID[5])
+    assert p.hex() == "a444d6bb5aadc3ceb615b50d6606bd54bfe529f59247987cd1ab848d19de599a9052f1835fb0d0d44cf70183e19a68c9"
+    assert y.hex() == "6d928e13fe443e957d82e3e71d48cb65d51028eb4483e719bf8efcdf12f7c321"
+
+
+# ---------------------------------------------------------------- all 253 vectors through the engine
+def test_all_253_vectors_through_engine():
+    counts, bad, missing = RV.check_all("engine")
+    assert sum(counts.values()) == 253
+    assert not bad, bad[:5]
+    assert not missing
+
+
+# ---------------------------------------------------------------- random blobs vs the oracle, same seeded inputs
+def test_random_blobs_match_oracle(engine_setup, oracle_setup):
+    n = 6
+    blobs = [rand_blob(100 + i) for i in range(n)]
+    cat = b"".join(blobs)
+    comm, st = engine_setup.blob_to_commitment_many(cat, n)
+    assert st == [0] * n
+    for i in range(n):
+        assert comm[48 * i:48 * i + 48] == oracle_setup.blob_to_commitment(blobs[i])
+    proofs, st = engine_setup.blob_proof_many(cat, comm, n)
+    assert st == [0] * n
+    for i in range(2):
+        assert proofs[48 * i:48 * i + 48] == oracle_setup.blob_proof(blobs[i], comm[48 * i:48 * i + 48])
+    # challenge/evaluation and the RLC operands of the pairing check are diffed too (intermediate sums)
+    cs = [comm[48 * i:48 * i + 48] for i in range(n)]
+    ps = [proofs[48 * i:48 * i + 48] for i in range(n)]
+    assert engine_setup.verify_blob_proof_batch(blobs, cs, ps) is True
+    lhs, rhs = engine_setup.last_pairing_operands()
+    assert (lhs, rhs) == oracle_setup.verify_blob_proof_batch_sums(blobs, cs, ps)
+    # proof at random points
+    zs = [RV.fe(int.from_bytes(hashlib.sha256(b"z%d" % i).digest(), "big")) for i in range(n)]
+    pr, ys, st = engine_setup.proof_many(cat, b"".join(zs), n)
+    assert st == [0] * n
+    for i in range(2):
+        assert (pr[48 * i:48 * i + 48], ys[32 * i:32 * i + 32]) == oracle_setup.proof(blobs[i], zs[i])
+    assert engine_setup.verify_proof_batch(pr, comm, b"".join(zs), ys, n) is True
+    for i in range(n):
+        assert engine_setup.verify_proof(pr[48 * i:48 * i + 48], cs[i], zs[i], ys[32 * i:32 * i + 32]) is True
+
+
+# ---------------------------------------------------------------- properties at batch scale
+def test_batch_properties(engine_setup, oracle_setup):
+    import kateth_b200 as K
+    n = 300                                    # > 148 SMs: exercises the one-CTA-per-blob shape and ragged tails
+    base = [rand_blob(1000 + i) for i in range(3)]
+    # linearity: commit(a) + commit(b) == commit(a + b mod r)
+    from oracle import oracle as O
+    a_int = [int.from_bytes(base[0][32 * k:32 * k + 32], "big") for k in range(4096)]
+    b_int = [int.from_bytes(base[1][32 * k:32 * k + 32], "big") for k in range(4096)]
+    sum_blob = b"".join(RV.fe(x + y) for x, y in zip(a_int, b_int))
+    blobs = [base[i % 3] for i in range(n - 1)] + [sum_blob]
+    cat = b"".join(blobs)
+    comm, st = engine_setup.blob_to_commitment_many(cat, n)
+    assert st == [0] * n
+    cs = [comm[48 * i:48 * i + 48] for i in range(n)]
+    for i in range(n - 1):
+        assert cs[i] == cs[i % 3]            # same blob -> same commitment, whatever CTA computed it
+    assert O.g1_add(cs[0], cs[1]) == cs[n - 1]
+    proofs, st = engine_setup.blob_proof_many(cat, comm, n)
+    assert st == [0] * n
+    ps = [proofs[48 * i:48 * i + 48] for i in range(n)]
+    assert ps[0] == oracle_setup.blob_proof(base[0], cs[0])
+    assert engine_setup.verify_blob_proof_batch_concat(cat, comm, proofs, n) is True
+    # one corrupted proof flips the verdict
+    bad = bytearray(proofs); bad[48 * 137:48 * 138] = O.g1_add(ps[137], RV.G1)
+    assert engine_setup.verify_blob_proof_batch_concat(cat, comm, bytes(bad), n) is False
+    # one bad blob makes the whole call an error, with per-item status
+    badcat = bytearray(cat); badcat[131072 * 5 + 32 * 77:131072 * 5 + 32 * 78] = RV.be32(R)
+    c2, st2 = engine_setup.blob_to_commitment_many(bytes(badcat), 8)
+    assert st2 == [0, 0, 0, 0, 0, 2, 0, 0] and c2[48 * 4:48 * 5] == cs[4]
+    with pytest.raises(K.KzgError) as e:
+        engine_setup.verify_blob_proof_batch_concat(bytes(badcat), comm, proofs, n)
+    assert e.value.status == 2
+
+
+def test_sharded_partials_equal_single_call(engine_setup):
+    """The multi-GPU path emulated on one GPU: shards with index offsets + finish == single call."""
+    import torch
+    n = 10
+    blobs = [rand_blob(2000 + i) for i in range(n)]
+    cat = b"".join(blobs)
+    comm, _ = engine_setup.blob_to_commitment_many(cat, n)
+    proofs, _ = engine_setup.blob_proof_many(cat, comm, n)
+    assert engine_setup.verify_blob_proof_batch_concat(cat, comm, proofs, n) is True
+    single = engine_setup.last_pairing_operands()
+    dev = torch.device("cuda:0")
+    d_b = torch.frombuffer(bytearray(cat), dtype=torch.uint8).to(dev)
+    d_c = torch.frombuffer(bytearray(comm), dtype=torch.uint8).to(dev)
+    d_p = torch.frombuffer(bytearray(proofs), dtype=torch.uint8).to(dev)
+    recs = torch.zeros(3 * 320, dtype=torch.uint8, device=dev)
+    st = torch.zeros(n, dtype=torch.int32, device=dev)
+    bounds = [(0, 3), (3, 4), (4, 10)]
+    for g, (lo, hi) in enumerate(bounds):
+        rc = engine_setup.verify_partial_device(d_b.data_ptr() + lo * 131072, d_c.data_ptr() + lo * 48, d_p.data_ptr() + lo * 48, hi - lo, lo, n,
+                                                recs.data_ptr() + g * 320, st.data_ptr() + 4 * lo)
+        assert rc == 0
+    assert engine_setup.verify_finish_device(recs.data_ptr(), 3) is True
+    assert engine_setup.last_pairing_operands() == single
+
+
+def test_g1_decompress_classes(engine_setup):
+    import kateth_b200 as K
+    pts = [RV.G1, RV.INF, RV.INVALID_G1[2], RV.INVALID_G1[3], bytes([0x17]) + RV.G1[1:], b"\xe0" + bytes(47), b"\x9a" + b"\xff" * 47]
+    st, re = K.test_hooks.g1_decompress(engine_setup, pts)
+    assert st == [0, 0, 5, 4, 3, 3, 3]
+    assert re[0] == RV.G1 and re[1] == RV.INF
+
+
+def test_other_window_width_gives_same_bytes():
+    """The window width is a tuning knob, not a semantic one."""
+    import kateth_b200 as K
+    s = K.Setup.load_json(os.path.join(ROOT, "tests/golden/trusted_setup_4096.json"), window_bits=9)
+    try:
+        vb = RV.valid_blobs()
+        for i, hexv in GOLD_COMM.items():
+            assert s.blob_to_commitment(vb[i]).hex() == hexv
+        assert s.info()["window_bits"] == 9
+    finally:
+        s.close()
