@@ -1,0 +1,333 @@
+#!/usr/bin/env python3
+"""bench.py -- blobs/s of kateth's EIP-4844 hot path on B200 (commit + blob-proof + batch-verify), see DESIGN.md "Measurement".
+
+  python bench.py --gpus N --steps K --warmup W            the sm_100a engine (libkateth_b200.so, through its C ABI)
+  python bench.py --impl reference --gpus N ...            kateth's CPU path as restated by oracle/ (kateth itself is Rust
+                                                           over blst: neither toolchain nor crate exists here), all host threads
+
+One "step" = one pass of the hot path over one batch of synthetic canonical-field-element blobs:
+    blob_to_commitment (4096-point MSM)  ->  compute_blob_kzg_proof (challenge, barycentric evaluation, quotient, 4096-point MSM)
+    ->  verify_blob_kzg_proof_batch (challenge, evaluation, G1 decompression, RLC sums, [all-gather of the 320-byte partials],
+    host two-pairing check).
+`value` times the step with inputs resident in HBM; `e2e` times the same step through the host-buffer C-ABI calls with the
+blobs in pinned host memory (H2D of the blobs and D2H of commitments/proofs/verdict inside the timed region).
+Under torchrun every rank owns `--blobs` blobs (weak scaling); the only collective is the all-gather of the batch-verify records.
+Prints ONE JSON line on rank 0.
+"""
+import argparse, json, os, subprocess, sys, threading, time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+SETUP_JSON = os.path.join(ROOT, "tests", "golden", "trusted_setup_4096.json")
+BLOB = 131072
+R_MOD = 0x73eda753299d7d483339d80809a1d80553bda402fffe5bfeffffffff00000001
+# SURVEY.md 8(d) fixed yardstick: one 4096-point, 255-bit MSM = 2.80e8 MAC32 (32x32->64 multiply-accumulates);
+# an Fp product = 300 MAC32.  The table MSM gathers 4096 * windows affine points of 96 bytes.
+MAC32_PER_MSM = 2.80e8
+METRIC = "blobs/sec commit+prove+batch-verify"
+
+
+def synth_blobs(n, seed):
+    """n blobs of canonical field elements, uniform in [0, r): 256 random bits, top bit cleared, rejected if >= r
+    (mirrors the distribution of Blob::random, /root/reference/src/blob.rs:66-76).  Returns uint8 [n*131072]."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    a = rng.integers(0, 256, size=(n * 4096, 32), dtype=np.uint8)
+    a[:, 0] &= 0x7f
+    rb = np.frombuffer(R_MOD.to_bytes(32, "big"), dtype=np.uint8)
+    while True:
+        # lexicographic a >= r on big-endian bytes: top byte > 0x73 fails, == 0x73 needs the full comparison
+        bad = list(np.nonzero(a[:, 0] > rb[0])[0])
+        bad += [i for i in np.nonzero(a[:, 0] == rb[0])[0] if bytes(a[i]) >= bytes(rb)]
+        if not bad:
+            break
+        fresh = rng.integers(0, 256, size=(len(bad), 32), dtype=np.uint8)
+        fresh[:, 0] &= 0x7f
+        a[bad] = fresh
+    return a.reshape(-1)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, pw, reasons = [], None, [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx = float(f[2]); pw.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "power_w_max": max(pw) if pw else None, "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+def env_ranks():
+    return int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+# ------------------------------------------------------------------------------------------------ CPU legs (oracle/)
+def cpu_leg(blobs_u8, n, threads):
+    """kateth's CPU path (oracle restatement: Pippenger MSMs, per-term inversions, naive lincombs in batch verify) on n blobs
+    with `threads` host threads, sharded over blobs.  Returns seconds for commit+prove and for batch-verify."""
+    from oracle import oracle as O
+    s = cpu_leg.setup = getattr(cpu_leg, "setup", None) or O.Setup.load_json(SETUP_JSON)
+    cat = bytes(blobs_u8[: n * BLOB])
+    t0 = time.perf_counter()
+    comm, proofs = s.commit_prove_many(cat, n, 2, threads)
+    t1 = time.perf_counter()
+    ok = s.verify_many(cat, comm, proofs, n, threads)
+    t2 = time.perf_counter()
+    assert ok, "oracle batch verification of its own proofs failed"
+    return t1 - t0, t2 - t1, comm, proofs
+
+
+def run_reference(args):
+    rank, world, _ = env_ranks()
+    if rank != 0:
+        return
+    threads = host_threads()
+    n = max(threads, 8) if args.ref_blobs <= 0 else args.ref_blobs        # one blob per thread per step: a few seconds per step
+    blobs = synth_blobs(n, 0x4b5a4700 + 3)
+    times = []
+    for it in range(args.warmup + args.steps):
+        a, b, _, _ = cpu_leg(blobs, n, threads)
+        if it >= args.warmup:
+            times.append(a + b)
+    dt = sum(times) / len(times)
+    val = n / dt
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "blobs/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64 limbs (Fr 4x64, Fp 6x64 Montgomery)",
+            "data": "synthetic canonical field elements, uniform in [0, r)",
+            "config": {"workload": "commit + compute_blob_kzg_proof + verify_blob_kzg_proof_batch, 4096-element blobs (BASELINE configs[2]+[3] shape)",
+                       "blobs_per_step": n, "note": "kateth is Rust over blst (no toolchain, crate absent): this is oracle/'s C restatement of its algorithm"},
+            "cpu_baseline": {"value": val, "unit": "blobs/s", "cores": threads, "kind": "port", "sample": "%d blobs per step, %d threads" % (n, threads)},
+            "e2e": {"value": val, "unit": "blobs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ the sm_100a engine
+def run_engine(args):
+    import torch
+    import torch.distributed as dist
+    import kateth_b200 as K
+    rank, world, local = env_ranks()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the engine has no CPU fallback (use --impl reference for the CPU path)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    n = args.blobs
+    s = K.Setup.load_json(SETUP_JSON, device=local, window_bits=args.window_bits)
+    s.set_stream(torch.cuda.current_stream().cuda_stream)
+    info0 = s.info()
+    peak_wide, peak_fp = K.test_hooks.mac_peak(16384) if rank == 0 else (0.0, 0.0)
+
+    h_blobs = torch.from_numpy(synth_blobs(n, 0x4b5a4700 + 3 + 1000 * rank)).pin_memory()
+    h_comm = torch.empty(n * 48, dtype=torch.uint8).pin_memory()
+    h_proof = torch.empty(n * 48, dtype=torch.uint8).pin_memory()
+    d_blobs = h_blobs.to(dev)
+    d_comm = torch.empty(n * 48, dtype=torch.uint8, device=dev)
+    d_proof = torch.empty(n * 48, dtype=torch.uint8, device=dev)
+    d_status = torch.zeros(n, dtype=torch.int32, device=dev)
+    d_rec = torch.zeros(K.RECORD_BYTES, dtype=torch.uint8, device=dev)
+    d_all = torch.zeros(world * K.RECORD_BYTES, dtype=torch.uint8, device=dev)
+
+    def check(rc, what):
+        if rc != 0:
+            raise SystemExit("bench.py: %s returned status %d (%s)" % (what, rc, K.lib().kb200_last_error().decode()))
+
+    def finish():
+        if world > 1:
+            dist.all_gather_into_tensor(d_all, d_rec)          # the ONLY data-path collective: 320 bytes per rank over NVLink
+            ok = s.verify_finish_device(d_all.data_ptr(), world)
+        else:
+            ok = s.verify_finish_device(d_rec.data_ptr(), 1)
+        if not ok:
+            raise SystemExit("bench.py: batch verification of the engine's own proofs returned false")
+
+    stage_ev = []
+
+    def step_resident(record):
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)] if record else None
+        if record: ev[0].record()
+        check(s.blob_to_commitment_device(d_blobs.data_ptr(), n, d_comm.data_ptr(), d_status.data_ptr()), "blob_to_commitment")
+        if record: ev[1].record()
+        check(s.blob_proof_device(d_blobs.data_ptr(), d_comm.data_ptr(), n, d_proof.data_ptr(), d_status.data_ptr()), "compute_blob_proof")
+        if record: ev[2].record()
+        check(s.verify_partial_device(d_blobs.data_ptr(), d_comm.data_ptr(), d_proof.data_ptr(), n, rank * n, world * n, d_rec.data_ptr(),
+                                      d_status.data_ptr()), "verify_blob_proof_batch(partial)")
+        finish()
+        if record: ev[3].record(); stage_ev.append(ev)
+
+    def step_e2e():
+        check(s.blob_to_commitment_host(h_blobs.data_ptr(), n, h_comm.data_ptr()), "blob_to_commitment(host)")
+        check(s.blob_proof_host(h_blobs.data_ptr(), h_comm.data_ptr(), n, h_proof.data_ptr()), "compute_blob_proof(host)")
+        check(s.verify_partial_host(h_blobs.data_ptr(), h_comm.data_ptr(), h_proof.data_ptr(), n, rank * n, world * n, d_rec.data_ptr()),
+              "verify_blob_proof_batch(host, partial)")
+        finish()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup, *a):
+        for _ in range(warmup):
+            fn(*([False] * len(a)))
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn(*a)
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    sampler = ClockSampler(local)
+    # ---- resident arm
+    for _ in range(args.warmup):
+        step_resident(False)
+    barrier()
+    s.set_profiling(True)
+    l0 = s.info()["kernel_launches"]
+    if rank == 0: sampler.start()
+    ms_res = timed(step_resident, args.steps, 0, True)
+    clocks = sampler.stop() if rank == 0 else None
+    launches = s.info()["kernel_launches"] - l0
+    prof = s.msm_profile()
+    s.set_profiling(False)
+    # ---- end-to-end arm (host buffers)
+    e2e_steps = max(1, min(args.steps, args.e2e_steps))
+    ms_e2e = timed(step_e2e, e2e_steps, 1)
+    # parity guard inside the bench: the host-buffer path and the resident path must agree byte for byte
+    if not (torch.equal(h_comm, d_comm.cpu()) and torch.equal(h_proof, d_proof.cpu())):
+        raise SystemExit("bench.py: host-buffer and resident outputs differ")
+    return dict(rank=rank, world=world, n=n, s=s, ms_res=ms_res, ms_e2e=ms_e2e, e2e_steps=e2e_steps, clocks=clocks, launches=launches, prof=prof,
+                stage_ev=stage_ev, info=info0, peak=(peak_wide, peak_fp), h_blobs=h_blobs, h_comm=h_comm, h_proof=h_proof)
+
+
+def load_peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        return None
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="engine", choices=["engine", "reference"])
+    ap.add_argument("--blobs", type=int, default=4096, help="blobs per GPU per step (BASELINE configs[2]: 4096)")
+    ap.add_argument("--window-bits", type=int, default=int(os.environ.get("KB200_WINDOW_BITS", "0")))
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--ref-blobs", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    r = run_engine(args)
+    rank, world, n, s = r["rank"], r["world"], r["n"], r["s"]
+    if rank != 0:
+        s.close()
+        return
+    import torch
+    total = n * world
+    ms_step = r["ms_res"] / args.steps
+    value = total / (ms_step * 1e-3)
+    ms_e2e = r["ms_e2e"] / r["e2e_steps"]
+    # per-stage device times (rank 0), averaged over the timed steps
+    st = [[ev[i].elapsed_time(ev[i + 1]) for i in range(3)] for ev in r["stage_ev"]]
+    stage = [sum(x[i] for x in st) / len(st) for i in range(3)]
+    # roofline of the dominant kernel (k_msm): SURVEY 8(d) yardstick MAC32 per MSM x MSMs per launch / CUDA-event launch duration
+    prof, info = r["prof"], r["info"]
+    peak_wide, peak_fp = r["peak"]
+    msm_ms = prof["ms"] / max(1, prof["launches"])
+    msms_per_launch = prof["msms"] / max(1, prof["launches"])
+    achieved = MAC32_PER_MSM * msms_per_launch / (msm_ms * 1e-3) / 1e12 if msm_ms > 0 else 0.0
+    peaks = load_peaks()
+    hbm_peak = peaks["hbm_gbs"] if peaks else 6650.0
+    gather_bytes = 4096.0 * info["windows"] * 96 * msms_per_launch
+    roofline = {"bound": "imad", "achieved": achieved, "peak": peak_wide, "unit": "TMAC32/s", "frac": achieved / peak_wide if peak_wide else None,
+                "traffic": None, "kernel": "k_msm", "launch_ms": msm_ms, "msms_per_launch": msms_per_launch, "share_of_step": prof["ms"] / r["ms_res"],
+                "peak_source": "K0 mad.wide.u32 microbenchmark measured in this run (fp_mul chain: %.2f TMAC32/s); no integer peak in MEASURED_PEAKS.json" % peak_fp,
+                "algorithmic": "2.80e8 MAC32 per 4096-point MSM (SURVEY 8d: signed-digit c=13 Pippenger, 10 Fp mul per mixed add, 300 MAC32 per Fp mul)",
+                "hbm": {"achieved": gather_bytes / (msm_ms * 1e-3) / 1e9 if msm_ms > 0 else 0.0, "peak": hbm_peak, "unit": "GB/s",
+                        "frac": (gather_bytes / (msm_ms * 1e-3) / 1e9 / hbm_peak) if msm_ms > 0 else None,
+                        "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650 GB/s",
+                        "algorithmic": "4096 x %d windows x 96-byte table points gathered per MSM" % info["windows"]}}
+    cpu_baseline = None
+    if world == 1 and not args.no_cpu_baseline:
+        threads = host_threads()
+        m = max(threads, 8)
+        a, b, comm, proofs = cpu_leg(r["h_blobs"].numpy(), m, threads)
+        # the bench doubles as a parity check: the oracle's bytes for the sample must equal the engine's
+        if comm != bytes(r["h_comm"].numpy()[: 48 * m]) or proofs != bytes(r["h_proof"].numpy()[: 48 * m]):
+            raise SystemExit("bench.py: engine output differs from the oracle on the CPU-baseline sample")
+        cpu_baseline = {"value": m / (a + b), "unit": "blobs/s", "cores": threads, "kind": "port",
+                        "sample": "first %d blobs of the step's batch, %d threads (commit+prove %.2f s, batch-verify %.2f s); outputs equal the engine's" % (m, threads, a, b)}
+    line = {"metric": METRIC, "value": value, "unit": "blobs/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32 limbs (Fp 12x32, Fr 8x32 Montgomery, IMAD.WIDE)",
+            "data": "synthetic canonical field elements, uniform in [0, r)",
+            "config": {"workload": "commit + compute_blob_kzg_proof + verify_blob_kzg_proof_batch over %d blobs per GPU (BASELINE configs[2] size; configs[3] sharding)" % n,
+                       "blobs_per_gpu": n, "global_blobs": total, "window_bits": info["window_bits"], "windows": info["windows"],
+                       "table_gb": round(info["table_bytes"] / 2 ** 30, 2), "parallelism": "blob shards x%d, replicated tables, 1 all-gather of 320 B" % world,
+                       "l2": "inputs (%d MiB of blobs + multi-GB table) exceed the 126 MB L2; no flush needed" % (n * BLOB >> 20)},
+            "stages_ms": {"commit": stage[0], "prove": stage[1], "verify": stage[2]},
+            "stage_blobs_per_s_per_gpu": {"commit": n / stage[0] * 1e3, "prove": n / stage[1] * 1e3, "verify": n / stage[2] * 1e3},
+            "e2e": {"value": total / (ms_e2e * 1e-3), "unit": "blobs/s", "h2d_bytes_per_step": 3 * n * BLOB + 3 * n * 48, "d2h_bytes_per_step": 2 * n * 48 + 200 + 8 * n,
+                    "ms_per_step": ms_e2e, "steps": r["e2e_steps"], "api": "kb200_blob_to_commitment + kb200_compute_blob_proof + kb200_verify_blob_proof_batch_partial (pinned host buffers)"},
+            "gpu_launches": int(r["launches"]), "roofline": roofline, "cpu_baseline": cpu_baseline, "clocks": r["clocks"],
+            "setup_seconds": info["setup_seconds"]}
+    print(json.dumps(line), flush=True)
+    s.close()
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -102,6 +102,9 @@ int kb200_verify_blob_proof_batch_device(kb200_setup* s, const void* d_blobs, co
  *      one all-gather (NCCL over NVLink, done by the caller), and any rank finishes.  d_record: device memory. ---- */
 int kb200_verify_blob_proof_batch_partial_device(kb200_setup* s, const void* d_blobs, const void* d_commitments48, const void* d_proofs48,
                                                  size_t n_local, size_t index_offset, size_t n_total, void* d_record, int32_t* d_status);
+/* Same with the shard's inputs in host memory (n_local <= 4096); the record is still written to device memory. */
+int kb200_verify_blob_proof_batch_partial(kb200_setup* s, const uint8_t* blobs, const uint8_t* commitments48, const uint8_t* proofs48, size_t n_local,
+                                          size_t index_offset, size_t n_total, void* d_record, int32_t* status);
 /* d_records: n_records x KB200_RECORD_BYTES in device memory. */
 int kb200_verify_batch_finish_device(kb200_setup* s, const void* d_records, size_t n_records, int* ok);
 /* The two compressed G1 operands of the final pairing check of the last finish call (for diffing intermediate sums). */
@@ -116,6 +119,10 @@ typedef struct {
     double setup_seconds;
 } kb200_info;
 int kb200_get_info(kb200_setup* s, kb200_info* info);
+/* CUDA-event timing of the dominant kernel (the fixed-base MSM) for roofline reporting: switch on, run, read the summed
+ * device time, launch count and number of 4096-point MSMs covered since the last read. */
+int kb200_set_profiling(kb200_setup* s, int on);
+int kb200_get_msm_profile(kb200_setup* s, double* ms_total, uint64_t* launches, uint64_t* msms);
 
 /* ---- unit-test hooks (device field arithmetic against the oracle; not part of the kateth surface) ---- */
 int kb200_test_fp_mul(const uint32_t* a, const uint32_t* b, uint32_t* out, size_t n); /* n x 12 limbs, Montgomery */

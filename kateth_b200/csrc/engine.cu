@@ -58,6 +58,11 @@ struct kb200_setup {
         records, combine;
     uint8_t last_lhs[48], last_rhs[48];
     bool have_last = false;
+    // optional CUDA-event timing of the dominant kernel (k_msm), for bench.py's roofline
+    bool prof = false;
+    std::vector<cudaEvent_t> prof_ev;   // pairs (start, stop)
+    size_t prof_used = 0;
+    uint64_t prof_items = 0;            // MSMs (4096-point) covered by the recorded launches
 };
 
 #define LAUNCH(s, kern, grid, block, ...)                   \
@@ -256,9 +261,26 @@ extern "C" void kb200_setup_free(kb200_setup* s) {
     DBuf* bufs[] = {&s->blobs, &s->c48, &s->p48, &s->zy32, &s->out48, &s->out32, &s->st_blob, &s->st_a, &s->st_b, &s->status, &s->z, &s->y, &s->prod,
                     &s->indom, &s->q, &s->partials, &s->aff_c, &s->aff_p, &s->rlc_part, &s->rlc_s, &s->rmont, &s->records, &s->combine};
     for (DBuf* b : bufs) b->release();
+    for (cudaEvent_t e : s->prof_ev) cudaEventDestroy(e);
     delete s;
 }
 extern "C" int kb200_set_stream(kb200_setup* s, void* stream) { if (!s) return KB200_E_ARG; s->stream = (cudaStream_t)stream; return 0; }
+extern "C" int kb200_set_profiling(kb200_setup* s, int on) {
+    if (!s) return KB200_E_ARG;
+    s->prof = on != 0; s->prof_used = 0; s->prof_items = 0;
+    return 0;
+}
+// total device time (ms) of the k_msm launches since the last call / set_profiling, their count and the MSMs they covered
+extern "C" int kb200_get_msm_profile(kb200_setup* s, double* ms_total, uint64_t* launches, uint64_t* msms) {
+    if (!s || !ms_total || !launches || !msms) return KB200_E_ARG;
+    CU(cudaSetDevice(s->device));
+    CU(cudaStreamSynchronize(s->stream));
+    double tot = 0;
+    for (size_t i = 0; i + 1 < s->prof_used; i += 2) { float ms = 0; CU(cudaEventElapsedTime(&ms, s->prof_ev[i], s->prof_ev[i + 1])); tot += ms; }
+    *ms_total = tot; *launches = s->prof_used / 2; *msms = s->prof_items;
+    s->prof_used = 0; s->prof_items = 0;
+    return 0;
+}
 extern "C" int kb200_get_info(kb200_setup* s, kb200_info* info) {
     if (!s || !info) return KB200_E_ARG;
     info->window_bits = s->tab.c; info->windows = s->tab.nwin; info->table_bytes = s->table_bytes; info->kernel_launches = s->launches;
@@ -281,7 +303,14 @@ template <int FMT>
 static int run_msm(kb200_setup* s, const uint32_t* d_scalars, size_t n, const int32_t* d_status, uint32_t* d_out48) {
     int S = pick_slices(s, n);
     if (int rc = s->partials.ensure(n * S * sizeof(G1))) return rc;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (s->prof) {
+        if (s->prof_used + 2 > s->prof_ev.size()) { cudaEvent_t a, b; CU(cudaEventCreate(&a)); CU(cudaEventCreate(&b)); s->prof_ev.push_back(a); s->prof_ev.push_back(b); }
+        e0 = s->prof_ev[s->prof_used]; e1 = s->prof_ev[s->prof_used + 1]; s->prof_used += 2; s->prof_items += n;
+        CU(cudaEventRecord(e0, s->stream));
+    }
     LAUNCH(s, (k_msm<FMT>), (unsigned)(n * S), MSM_THREADS, s->tab, d_scalars, d_status, s->partials.as<G1>(), S);
+    if (e1) CU(cudaEventRecord(e1, s->stream));
     LAUNCH(s, k_msm_finish, blocks(n, 32), 32, s->partials.as<G1>(), S, (int)n, d_status, d_out48, (G1Affine*)nullptr);
     return 0;
 }
@@ -577,6 +606,21 @@ extern "C" int kb200_verify_blob_proof_batch(kb200_setup* s, const uint8_t* blob
     if (e_comm) return e_comm;
     if (e_proof) return e_proof;
     return finish_records(s, s->records.as<RlcRecord>(), nch, ok);
+}
+// host-buffer shard of a multi-GPU batch: inputs in (pinned) host memory, the 320-byte record stays on the device
+extern "C" int kb200_verify_blob_proof_batch_partial(kb200_setup* s, const uint8_t* blobs, const uint8_t* comm48, const uint8_t* proofs48, size_t n,
+                                                     size_t index_offset, size_t n_total, void* d_record, int32_t* status) {
+    if (!s || !d_record || (n && (!blobs || !comm48 || !proofs48))) return KB200_E_ARG;
+    CU(cudaSetDevice(s->device));
+    if (n > CHUNK) { snprintf(g_err, sizeof g_err, "partial: at most %zu blobs per call", CHUNK); return KB200_E_ARG; }
+    if (int rc = h2d(s, s->blobs, blobs, n * KB_BLOB_BYTES)) return rc;
+    if (int rc = h2d(s, s->c48, comm48, n * 48)) return rc;
+    if (int rc = h2d(s, s->p48, proofs48, n * 48)) return rc;
+    if (int rc = s->status.ensure(n ? n * 4 : 16)) return rc;
+    int e = kb200_verify_blob_proof_batch_partial_device(s, s->blobs.p, s->c48.p, s->p48.p, n, index_offset, n_total, d_record, s->status.as<int32_t>());
+    if (e < 0) return e;
+    if (status && n) if (int rc = d2h(s, status, s->status.p, n * 4)) return rc;
+    return e;
 }
 // points given directly: mirrors the private Setup::verify_proof_batch (raw = 0) and verify_proof_inner (raw = 1)
 static int verify_points(kb200_setup* s, const uint8_t* proofs48, const uint8_t* comm48, const uint8_t* z32, const uint8_t* y32, size_t n, int raw, int* ok,

@@ -39,7 +39,7 @@ SYMBOLS = [
     "kb200_blob_to_commitment", "kb200_blob_to_commitment_device", "kb200_compute_blob_proof", "kb200_compute_blob_proof_device",
     "kb200_compute_proof", "kb200_compute_proof_device", "kb200_verify_proof", "kb200_verify_proof_batch", "kb200_verify_blob_proof",
     "kb200_verify_blob_proof_batch", "kb200_verify_blob_proof_batch_device", "kb200_verify_blob_proof_batch_partial_device",
-    "kb200_verify_batch_finish_device", "kb200_last_pairing_operands", "kb200_get_info", "kb200_test_fp_mul", "kb200_test_fr_mul",
+    "kb200_verify_blob_proof_batch_partial", "kb200_verify_batch_finish_device", "kb200_set_profiling", "kb200_get_msm_profile", "kb200_last_pairing_operands", "kb200_get_info", "kb200_test_fp_mul", "kb200_test_fr_mul",
     "kb200_test_g1_decompress", "kb200_test_mac_peak", "kb200_test_host_pairing",
 ]
 
@@ -225,6 +225,32 @@ class Setup:
     def verify_partial_device(self, d_blobs, d_comm48, d_proofs48, n_local, index_offset, n_total, d_record, d_status):
         return lib().kb200_verify_blob_proof_batch_partial_device(self._h, _vp(d_blobs), _vp(d_comm48), _vp(d_proofs48), C.c_size_t(n_local),
                                                                   C.c_size_t(index_offset), C.c_size_t(n_total), _vp(d_record), _vp(d_status))
+
+    def verify_partial_host(self, blobs, comm48, proofs48, n_local, index_offset, n_total, d_record):
+        """blobs / comm48 / proofs48: integer host addresses (e.g. pinned torch tensors' data_ptr()) or bytes."""
+        conv = lambda x: x if isinstance(x, (bytes, bytearray)) else _vp(x)
+        return lib().kb200_verify_blob_proof_batch_partial(self._h, conv(blobs), conv(comm48), conv(proofs48), C.c_size_t(n_local),
+                                                           C.c_size_t(index_offset), C.c_size_t(n_total), _vp(d_record), None)
+
+    def set_profiling(self, on=True):
+        _check(lib().kb200_set_profiling(self._h, 1 if on else 0))
+
+    def msm_profile(self):
+        ms, l, m = C.c_double(0), C.c_uint64(0), C.c_uint64(0)
+        _check(lib().kb200_get_msm_profile(self._h, C.byref(ms), C.byref(l), C.byref(m)))
+        return {"ms": ms.value, "launches": l.value, "msms": m.value}
+
+    # host-buffer batch calls on raw addresses (pinned host memory): the end-to-end path of bench.py
+    def blob_to_commitment_host(self, blobs_ptr, n, out48_ptr, status_ptr=0):
+        return lib().kb200_blob_to_commitment(self._h, _vp(blobs_ptr), C.c_size_t(n), _vp(out48_ptr), _vp(status_ptr) if status_ptr else None)
+
+    def blob_proof_host(self, blobs_ptr, comm48_ptr, n, out48_ptr, status_ptr=0):
+        return lib().kb200_compute_blob_proof(self._h, _vp(blobs_ptr), _vp(comm48_ptr), C.c_size_t(n), _vp(out48_ptr), _vp(status_ptr) if status_ptr else None)
+
+    def verify_blob_proof_batch_host(self, blobs_ptr, comm48_ptr, proofs48_ptr, n):
+        ok = C.c_int(0)
+        _check(lib().kb200_verify_blob_proof_batch(self._h, _vp(blobs_ptr), _vp(comm48_ptr), _vp(proofs48_ptr), C.c_size_t(n), C.byref(ok), None))
+        return bool(ok.value)
 
     def verify_finish_device(self, d_records, n_records):
         ok = C.c_int(0)
