@@ -291,9 +291,11 @@ def main():
     peaks = load_peaks()
     hbm_peak = peaks["hbm_gbs"] if peaks else 6650.0
     gather_bytes = 4096.0 * info["windows"] * 96 * msms_per_launch
-    roofline = {"bound": "imad", "achieved": achieved, "peak": peak_wide, "unit": "TMAC32/s", "frac": achieved / peak_wide if peak_wide else None,
+    executed = 4096.0 * info["windows"] * 3000.0 * msms_per_launch / (msm_ms * 1e-3) / 1e12 if msm_ms > 0 else 0.0
+    roofline = {"bound": "imad", "achieved": achieved, "executed": executed, "executed_frac": executed / peak_wide if peak_wide else None, "peak": peak_wide, "unit": "TMAC32/s", "frac": achieved / peak_wide if peak_wide else None,
                 "traffic": None, "kernel": "k_msm", "launch_ms": msm_ms, "msms_per_launch": msms_per_launch, "share_of_step": prof["ms"] / r["ms_res"],
-                "peak_source": "K0 mad.wide.u32 microbenchmark measured in this run (fp_mul chain: %.2f TMAC32/s); no integer peak in MEASURED_PEAKS.json" % peak_fp,
+                "peak_source": "K0 IMAD.WIDE.U32 microbenchmark measured in this run (half the 32-bit IMAD rate on sm_100a; Fp-product chain: %.2f TMAC32/s); no integer peak in MEASURED_PEAKS.json" % peak_fp,
+                "executed_note": "executed = 4096 x windows x 3000 MAC32 (XYZZ mixed additions actually issued) per MSM; achieved = SURVEY 8d yardstick",
                 "algorithmic": "2.80e8 MAC32 per 4096-point MSM (SURVEY 8d: signed-digit c=13 Pippenger, 10 Fp mul per mixed add, 300 MAC32 per Fp mul)",
                 "hbm": {"achieved": gather_bytes / (msm_ms * 1e-3) / 1e9 if msm_ms > 0 else 0.0, "peak": hbm_peak, "unit": "GB/s",
                         "frac": (gather_bytes / (msm_ms * 1e-3) / 1e9 / hbm_peak) if msm_ms > 0 else None,

@@ -125,7 +125,8 @@ __global__ void __launch_bounds__(256) k_mac_wide(uint64_t* out, int iters, uint
 #pragma unroll 1
     for (int it = 0; it < iters; it++) {
 #pragma unroll
-        for (int k = 0; k < 16; k++) asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc[k]) : "r"(a), "r"(b));
+        for (int k = 0; k < 16; k++)   // multiplicand taken from another chain so the product is not loop-invariant (ptxas would hoist it)
+            asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc[k]) : "r"((uint32_t)acc[(k + 5) & 15] ^ a), "r"(b));
     }
     uint64_t s = 0;
 #pragma unroll
