@@ -60,7 +60,8 @@ typedef struct kb200_setup kb200_setup;
 /* ---- Setup::load_json (/root/reference/src/kzg/setup.rs:46-82) ----
  * Parses {"g1_lagrange": [4096 x "0x" + 96 hex], "g2_monomial": [65 x "0x" + 192 hex]}, validates every point
  * (curve + subgroup; G1 on the GPU, G2 on the host), bit-reverses the Lagrange points, builds the roots-of-unity
- * table and the fixed-base window table on `device`.  window_bits: 0 = default (13 -> 32 GB table), else 8..14. */
+ * table and the fixed-base window table on `device`.  window_bits: 0 = default (13 -> 28.6 GiB table), else 4..15
+ * (15 -> 17 windows, 107 GiB).  The top window is unsigned; the others hold signed-digit magnitudes. */
 int kb200_setup_load_json(const char* path, int device, int window_bits, kb200_setup** out);
 /* Same from decoded bytes: n_g1 x 48 bytes, n_g2 x 96 bytes. */
 int kb200_setup_load_raw(const uint8_t* g1_lagrange48, size_t n_g1, const uint8_t* g2_monomial96, size_t n_g2, int device, int window_bits,

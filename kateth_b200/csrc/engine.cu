@@ -116,21 +116,38 @@ __global__ void k_test_compress(const G1Affine* in, int n, const int32_t* status
     if (status[i] != 0) { for (int k = 0; k < 12; k++) w[k] = 0; } else g1_compress(w, in[i]);
     for (int k = 0; k < 12; k++) out48[(size_t)i * 12 + k] = w[k];
 }
-// K0: integer multiply-add peak.  (a) 16 independent mad.wide.u32 chains per thread; (b) a chain of Fp products.
+// K0: integer multiplier peak.  (a) four independent carry chains of six IMAD.WIDE.U32.X per thread (the instruction the
+// Montgomery products are made of; SASS checked: nothing but IMAD.WIDE in the loop); (b) a chain of Fp products.
+__device__ __forceinline__ void k0_chain6(uint64_t (&t)[6], uint32_t a, uint32_t b) {
+    asm volatile(
+        "{\n\t.reg .u32 l0,h0,l1,h1,l2,h2,l3,h3,l4,h4,l5,h5;\n\t"
+        "mov.b64 {l0,h0}, %0;\n\tmov.b64 {l1,h1}, %1;\n\tmov.b64 {l2,h2}, %2;\n\tmov.b64 {l3,h3}, %3;\n\tmov.b64 {l4,h4}, %4;\n\tmov.b64 {l5,h5}, %5;\n\t"
+        "mad.lo.cc.u32 l0, %6, %7, l0;\n\tmadc.hi.cc.u32 h0, %6, %7, h0;\n\t"
+        "madc.lo.cc.u32 l1, %6, %7, l1;\n\tmadc.hi.cc.u32 h1, %6, %7, h1;\n\t"
+        "madc.lo.cc.u32 l2, %6, %7, l2;\n\tmadc.hi.cc.u32 h2, %6, %7, h2;\n\t"
+        "madc.lo.cc.u32 l3, %6, %7, l3;\n\tmadc.hi.cc.u32 h3, %6, %7, h3;\n\t"
+        "madc.lo.cc.u32 l4, %6, %7, l4;\n\tmadc.hi.cc.u32 h4, %6, %7, h4;\n\t"
+        "madc.lo.cc.u32 l5, %6, %7, l5;\n\tmadc.hi.u32 h5, %6, %7, h5;\n\t"
+        "mov.b64 %0, {l0,h0};\n\tmov.b64 %1, {l1,h1};\n\tmov.b64 %2, {l2,h2};\n\tmov.b64 %3, {l3,h3};\n\tmov.b64 %4, {l4,h4};\n\tmov.b64 %5, {l5,h5};\n\t}"
+        : "+l"(t[0]), "+l"(t[1]), "+l"(t[2]), "+l"(t[3]), "+l"(t[4]), "+l"(t[5]) : "r"(a), "r"(b));
+}
 __global__ void __launch_bounds__(256) k_mac_wide(uint64_t* out, int iters, uint32_t seed) {
-    uint64_t acc[16];
+    uint64_t t[4][6];
     uint32_t a = seed + threadIdx.x, b = seed * 2654435761u + blockIdx.x;
 #pragma unroll
-    for (int k = 0; k < 16; k++) acc[k] = k;
+    for (int c = 0; c < 4; c++)
+#pragma unroll
+        for (int k = 0; k < 6; k++) t[c][k] = threadIdx.x + k + c;
 #pragma unroll 1
     for (int it = 0; it < iters; it++) {
 #pragma unroll
-        for (int k = 0; k < 16; k++)   // multiplicand taken from another chain so the product is not loop-invariant (ptxas would hoist it)
-            asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc[k]) : "r"((uint32_t)acc[(k + 5) & 15] ^ a), "r"(b));
+        for (int c = 0; c < 4; c++) k0_chain6(t[c], a + c, b);
     }
     uint64_t s = 0;
 #pragma unroll
-    for (int k = 0; k < 16; k++) s ^= acc[k];
+    for (int c = 0; c < 4; c++)
+#pragma unroll
+        for (int k = 0; k < 6; k++) s ^= t[c][k];
     out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 __global__ void __launch_bounds__(256) k_mac_fpmul(Fp* out, int iters, uint32_t seed) {
@@ -204,16 +221,36 @@ static int build_setup(kb200_setup* s, const uint8_t* g1, const uint8_t* g2, int
     // roots of unity, bit-reversed (src/kzg/setup.rs:74-75)
     CU(cudaMalloc(&s->d_roots, KB_N * sizeof(Fr)));
     LAUNCH(s, k_roots, KB_N / 256, 256, s->d_roots);
-    // fixed-base window table
+    // fixed-base window table: nwin = ceil(255 / c) windows; windows below the top hold the 2^(c-1) signed-digit magnitudes, the top
+    // window is unsigned and holds (r >> c*(nwin-1)) + 1 magnitudes (scalars are canonical, so its digit never exceeds that)
     int c = window_bits ? window_bits : 13;
     if (c < 4 || c > 15) { cudaFree(d_pts); return KB200_E_ARG; }
-    int nwin = 255 / c + 1, blast = 255 - c * (nwin - 1), dlast = 1 << blast;
-    size_t rows = (size_t)(nwin - 1) * ((size_t)1 << (c - 1)) + dlast;
+    int nwin = (255 + c - 1) / c;
+    int dlast;
+    {
+        int sh = c * (nwin - 1), limb = sh >> 5, off = sh & 31;
+        uint64_t top = kb200::consts::H_FR_R[limb];
+        if (limb + 1 < 8) top |= (uint64_t)kb200::consts::H_FR_R[limb + 1] << 32;
+        dlast = (int)(top >> off) + 1;
+    }
+    size_t win_rows = (size_t)1 << (c - 1);
+    size_t rows = (size_t)(nwin - 1) * win_rows + dlast;
     size_t bytes = rows * KB_N * sizeof(G1Affine);
+    // build scratch (Z and prefix products) is bounded to ~16 GiB: windows are built in groups, the top window alone
+    size_t row_bytes = (size_t)KB_N * sizeof(G1Affine);
+    int group = (int)(((size_t)16 << 30) / (win_rows * row_bytes));
+    if (group < 1) group = 1;
+    if (group > nwin - 1) group = nwin - 1;
+    size_t scratch_rows = (size_t)group * win_rows;
+    if ((size_t)dlast > scratch_rows) scratch_rows = dlast;
     uint4* scratch;
     CU(cudaMalloc(&s->d_table, bytes));
-    CU(cudaMalloc(&scratch, bytes));
-    LAUNCH(s, k_table_build, (KB_N * nwin + 127) / 128, 128, s->d_table, scratch, s->d_bases, c, nwin, dlast);
+    CU(cudaMalloc(&scratch, scratch_rows * row_bytes));
+    for (int j0 = 0; j0 < nwin;) {
+        int cnt = (j0 == nwin - 1) ? 1 : ((nwin - 1 - j0 < group) ? nwin - 1 - j0 : group);
+        LAUNCH(s, k_table_build, (KB_N * cnt + 31) / 32, 32, s->d_table, scratch, s->d_bases, c, nwin, dlast, j0, cnt);
+        j0 += cnt;
+    }
     CU(cudaStreamSynchronize(s->stream));
     CU(cudaGetLastError());
     cudaFree(scratch); cudaFree(d_pts);
@@ -718,7 +755,7 @@ extern "C" int kb200_test_mac_peak(int iters, double* tmacs_wide, double* tmacs_
     k_mac_wide<<<grid, block>>>((uint64_t*)buf, 64, 1);   // warm-up
     CU(cudaEventRecord(e0)); k_mac_wide<<<grid, block>>>((uint64_t*)buf, iters, 7); CU(cudaEventRecord(e1)); CU(cudaEventSynchronize(e1));
     CU(cudaEventElapsedTime(&ms, e0, e1));
-    *tmacs_wide = (double)grid * block * iters * 16.0 / (ms * 1e-3) / 1e12;
+    *tmacs_wide = (double)grid * block * iters * 24.0 / (ms * 1e-3) / 1e12;
     int it2 = iters / 16 > 0 ? iters / 16 : 1;
     k_mac_fpmul<<<grid, block>>>((Fp*)buf, 4, 1);
     CU(cudaEventRecord(e0)); k_mac_fpmul<<<grid, block>>>((Fp*)buf, it2, 7); CU(cudaEventRecord(e1)); CU(cudaEventSynchronize(e1));

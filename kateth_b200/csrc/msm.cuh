@@ -26,7 +26,7 @@ struct MsmTable {
     const uint4* data;   // 6 x uint4 per entry
     int c;               // window bits
     int nwin;            // windows
-    int dlast;           // digit magnitudes stored for the last window (2^(255 - c*(nwin-1)))
+    int dlast;           // digit magnitudes stored for the top (unsigned) window: (r >> c*(nwin-1)) + 1
 };
 
 __device__ __forceinline__ void load_affine(G1Affine& p, const uint4* src) {
@@ -52,10 +52,11 @@ __device__ __forceinline__ void store_affine(uint4* dst, const G1Affine& p) {
 // in XYZZ with an explicit Z (ZZ = Z^2, ZZZ = Z^3), X,Y parked in the table slot and (Z, prefix product) in a
 // same-shaped scratch array; one inversion per thread and a backward sweep normalise everything to affine.
 // ---------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) k_table_build(uint4* table, uint4* scratch, const G1Affine* bases, int c, int nwin, int dlast) {
+__global__ void __launch_bounds__(128) k_table_build(uint4* table, uint4* scratch, const G1Affine* bases, int c, int nwin, int dlast, int j0, int jcount) {
     int gid = blockIdx.x * blockDim.x + threadIdx.x;
-    if (gid >= KB_N * nwin) return;
-    int i = gid & (KB_N - 1), j = gid >> 12;
+    if (gid >= KB_N * jcount) return;
+    int i = gid & (KB_N - 1), j = j0 + (gid >> 12);
+    scratch -= ((size_t)j0 << (c - 1)) * KB_N * 6;      // scratch covers windows [j0, j0 + jcount) only
     int D = 1 << (c - 1);
     int nd = (j == nwin - 1) ? dlast : D;
     size_t base_e = ((size_t)j << (c - 1)) * KB_N + i;     // entry index of d = 1
@@ -147,7 +148,7 @@ __global__ void __launch_bounds__(MSM_THREADS) k_msm(MsmTable tab, const uint32_
 #pragma unroll
                 for (int k = 0; k < 7; k++) s[k] = __funnelshift_r(s[k], s[k + 1], c);
                 s[7] >>= c;
-                bool neg = d > D;                                  // never true in the last window (d <= dlast <= D)
+                bool neg = d > D && j != nwin - 1;                 // the top window is unsigned (its digits are bounded by r >> c*(nwin-1))
                 carry = neg ? 1u : 0u;
                 uint32_t mag = neg ? ((1u << c) - d) : d;
                 if (mag != 0) {

@@ -200,14 +200,30 @@ def test_g1_decompress_classes(engine_setup):
     assert re[0] == RV.G1 and re[1] == RV.INF
 
 
-def test_other_window_width_gives_same_bytes():
-    """The window width is a tuning knob, not a semantic one."""
+@pytest.mark.parametrize("wb", [9, 15])
+def test_other_window_width_gives_same_bytes(wb, oracle_setup):
+    """The window width is a tuning knob, not a semantic one.  15 is bench.py's throughput configuration (17 windows, the
+    top one unsigned and 15 bits wide, 107 GiB table); 9 exercises a 3-bit top window."""
     import kateth_b200 as K
-    s = K.Setup.load_json(os.path.join(ROOT, "tests/golden/trusted_setup_4096.json"), window_bits=9)
+    s = K.Setup.load_json(os.path.join(ROOT, "tests/golden/trusted_setup_4096.json"), window_bits=wb)
     try:
         vb = RV.valid_blobs()
         for i, hexv in GOLD_COMM.items():
             assert s.blob_to_commitment(vb[i]).hex() == hexv
-        assert s.info()["window_bits"] == 9
+        assert s.info()["window_bits"] == wb
+        # r - 1 everywhere, then scalars whose top window is maximal with and without a carry coming in
+        hi = [R - 1, R - 2 ** 240, (R >> 240 << 240) + 2 ** 239 + 5, (R >> 240 << 240) + 2 ** 239 - 5, 2 ** 254, 2 ** 240 - 1]
+        blob = b"".join(RV.fe(hi[k % len(hi)] - (k // len(hi))) for k in range(4096))
+        c = s.blob_to_commitment(blob)
+        assert c == oracle_setup.blob_to_commitment(blob)
+        blobs = [rand_blob(3000 + i) for i in range(3)] + [blob]
+        cat = b"".join(blobs)
+        comm, st = s.blob_to_commitment_many(cat, 4)
+        proofs, st2 = s.blob_proof_many(cat, comm, 4)
+        assert st == [0] * 4 and st2 == [0] * 4
+        for i in range(4):
+            assert comm[48 * i:48 * i + 48] == oracle_setup.blob_to_commitment(blobs[i])
+        assert proofs[:48] == oracle_setup.blob_proof(blobs[0], comm[:48])
+        assert s.verify_blob_proof_batch_concat(cat, comm, proofs, 4) is True
     finally:
         s.close()

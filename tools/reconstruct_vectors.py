@@ -122,7 +122,7 @@ def get_backend(name):
     if name == "engine":
         import kateth_b200 as K
         from oracle import oracle as O  # only add_one() of the *generator recipe* (an input, not a checked output)
-        s = K.Setup.load_json(os.path.join(ROOT, "tests/golden/trusted_setup_4096.json"))
+        s = K.Setup.load_json(os.path.join(ROOT, "tests/golden/trusted_setup_4096.json"), window_bits=int(os.environ.get("KB200_WINDOW_BITS", "0")))
         return s, K.KzgError, O.g1_add
     raise SystemExit("unknown backend")
 
