@@ -128,7 +128,8 @@ int kb200_get_msm_profile(kb200_setup* s, double* ms_total, uint64_t* launches, 
 /* ---- unit-test hooks (device field arithmetic against the oracle; not part of the kateth surface) ---- */
 int kb200_test_fp_mul(const uint32_t* a, const uint32_t* b, uint32_t* out, size_t n); /* n x 12 limbs, Montgomery */
 int kb200_test_fr_mul(const uint32_t* a, const uint32_t* b, uint32_t* out, size_t n); /* n x 8 limbs */
-int kb200_test_g1_decompress(kb200_setup* s, const uint8_t* in48, size_t n, int32_t* status, uint8_t* recompressed48);
+/* by_order != 0: subgroup membership by the [r]P == infinity definition instead of the endomorphism test */
+int kb200_test_g1_decompress(kb200_setup* s, const uint8_t* in48, size_t n, int32_t* status, uint8_t* recompressed48, int by_order);
 int kb200_test_mac_peak(int iters, double* tmacs_wide, double* tmacs_lohi);            /* K0: IMAD microbenchmark */
 /* host pairing alone: e(a1, [tau]_2) == e(b1, G2) for plain little-endian affine coordinates (12 x u32 each) */
 int kb200_test_host_pairing(kb200_setup* s, const uint32_t* a_xy24, int a_inf, const uint32_t* b_xy24, int b_inf, int* ok);

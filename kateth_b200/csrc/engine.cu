@@ -47,6 +47,7 @@ struct kb200_setup {
     cudaStream_t stream = 0;
     G1Affine* d_bases = nullptr;     // g1_lagrange_brp, affine Montgomery   (src/kzg/setup.rs:39)
     Fr* d_roots = nullptr;           // roots_of_unity_brp, Montgomery       (src/kzg/setup.rs:41)
+    G1Affine* d_neg_g_pow = nullptr; // 2^(8w) * (-G1), w = 0..31 (verify.cuh, k_rlc_combine)
     uint4* d_table = nullptr;        // fixed-base window table (msm.cuh)
     MsmTable tab{};
     uint64_t table_bytes = 0;
@@ -202,7 +203,7 @@ static int build_setup(kb200_setup* s, const uint8_t* g1, const uint8_t* g2, int
     CU(cudaMalloc(&d_in, KB_N * 48)); CU(cudaMalloc(&d_pts, KB_N * sizeof(G1Affine))); CU(cudaMalloc(&d_st, KB_N * 4));
     CU(cudaMemcpy(d_in, g1, KB_N * 48, cudaMemcpyHostToDevice));
     CU(cudaMemset(d_st, 0, KB_N * 4));
-    LAUNCH(s, k_g1_decompress, KB_N / 64, 64, d_in, KB_N, d_pts, d_st);
+    LAUNCH(s, k_g1_decompress, KB_N / 64, 64, d_in, (const uint32_t*)nullptr, KB_N, d_pts, (G1Affine*)nullptr, d_st, (int32_t*)nullptr, 0);
     std::vector<int32_t> st(KB_N);
     CU(cudaMemcpy(st.data(), d_st, KB_N * 4, cudaMemcpyDeviceToHost));
     cudaFree(d_in); cudaFree(d_st);
@@ -221,6 +222,8 @@ static int build_setup(kb200_setup* s, const uint8_t* g1, const uint8_t* g2, int
     // roots of unity, bit-reversed (src/kzg/setup.rs:74-75)
     CU(cudaMalloc(&s->d_roots, KB_N * sizeof(Fr)));
     LAUNCH(s, k_roots, KB_N / 256, 256, s->d_roots);
+    CU(cudaMalloc(&s->d_neg_g_pow, 32 * sizeof(G1Affine)));
+    LAUNCH(s, k_neg_g_table, 1, 32, s->d_neg_g_pow);
     // fixed-base window table: nwin = ceil(255 / c) windows; windows below the top hold the 2^(c-1) signed-digit magnitudes, the top
     // window is unsigned and holds (r >> c*(nwin-1)) + 1 magnitudes (scalars are canonical, so its digit never exceeds that)
     int c = window_bits ? window_bits : 13;
@@ -295,6 +298,7 @@ extern "C" void kb200_setup_free(kb200_setup* s) {
     cudaSetDevice(s->device);
     if (s->d_bases) cudaFree(s->d_bases);
     if (s->d_roots) cudaFree(s->d_roots);
+    if (s->d_neg_g_pow) cudaFree(s->d_neg_g_pow);
     if (s->d_table) cudaFree(s->d_table);
     DBuf* bufs[] = {&s->blobs, &s->c48, &s->p48, &s->zy32, &s->out48, &s->out32, &s->st_blob, &s->st_a, &s->st_b, &s->status, &s->z, &s->y, &s->prod,
                     &s->indom, &s->q, &s->partials, &s->aff_c, &s->aff_p, &s->rlc_part, &s->rlc_s, &s->rmont, &s->records, &s->combine};
@@ -413,7 +417,7 @@ extern "C" int kb200_compute_blob_proof_device(kb200_setup* s, const void* d_blo
     CU(cudaMemsetAsync(s->st_blob.p, 0, n * 4, s->stream));
     CU(cudaMemsetAsync(s->st_a.p, 0, n * 4, s->stream));
     LAUNCH(s, k_blob_check, blocks(n * KB_N, 256), 256, (const uint32_t*)d_blobs, (int)n, s->st_blob.as<int32_t>());
-    LAUNCH(s, k_g1_decompress, blocks(n, 64), 64, (const uint32_t*)d_comm48, (int)n, s->aff_c.as<G1Affine>(), s->st_a.as<int32_t>());
+    LAUNCH(s, k_g1_decompress, blocks(n, 64), 64, (const uint32_t*)d_comm48, (const uint32_t*)nullptr, (int)n, s->aff_c.as<G1Affine>(), (G1Affine*)nullptr, s->st_a.as<int32_t>(), (int32_t*)nullptr, 0);
     LAUNCH(s, k_merge_status, blocks(n, 256), 256, s->st_blob.as<int32_t>(), s->st_a.as<int32_t>(), (const int32_t*)nullptr, (int)n, d_status);
     LAUNCH(s, k_challenge, blocks(n, 32), 32, (const uint32_t*)d_blobs, (const uint32_t*)d_comm48, (int)n, d_status, s->z.as<Fr>());
     if (int rc = prove_tail(s, (const uint32_t*)d_blobs, n, d_status, (uint32_t*)d_out48)) return rc;
@@ -471,7 +475,7 @@ static void compress_plain(uint8_t out[48], const uint32_t* xy24, bool inf) {
 }
 static int finish_records(kb200_setup* s, const RlcRecord* d_records, size_t nrec, int* ok) {
     if (int rc = s->combine.ensure(64 * 4)) return rc;
-    LAUNCH(s, k_rlc_combine, 1, 32, d_records, (int)nrec, s->combine.as<uint32_t>());
+    LAUNCH(s, k_rlc_combine, 1, 32, d_records, (int)nrec, s->d_neg_g_pow, s->combine.as<uint32_t>());
     uint32_t h[50];
     CU(cudaMemcpyAsync(h, s->combine.p, sizeof h, cudaMemcpyDeviceToHost, s->stream));
     CU(cudaStreamSynchronize(s->stream));
@@ -502,8 +506,8 @@ static int verify_prepare(kb200_setup* s, const uint32_t* d_blobs, const uint32_
     CU(cudaMemsetAsync(s->st_a.p, 0, n * 4, s->stream));
     CU(cudaMemsetAsync(s->st_b.p, 0, n * 4, s->stream));
     LAUNCH(s, k_blob_check, blocks(n * KB_N, 256), 256, d_blobs, (int)n, s->st_blob.as<int32_t>());
-    LAUNCH(s, k_g1_decompress, blocks(n, 64), 64, d_c48, (int)n, s->aff_c.as<G1Affine>(), s->st_a.as<int32_t>());
-    LAUNCH(s, k_g1_decompress, blocks(n, 64), 64, d_p48, (int)n, s->aff_p.as<G1Affine>(), s->st_b.as<int32_t>());
+    LAUNCH(s, k_g1_decompress, blocks(2 * n, 64), 64, d_c48, d_p48, (int)n, s->aff_c.as<G1Affine>(), s->aff_p.as<G1Affine>(), s->st_a.as<int32_t>(),
+           s->st_b.as<int32_t>(), 0);
     LAUNCH(s, k_merge_status, blocks(n, 256), 256, s->st_blob.as<int32_t>(), s->st_a.as<int32_t>(), s->st_b.as<int32_t>(), (int)n, d_status);
     LAUNCH(s, k_challenge, blocks(n, 32), 32, d_blobs, d_c48, (int)n, d_status, s->z.as<Fr>());
     if (int rc = run_eval<false>(s, d_blobs, n, d_status)) return rc;
@@ -679,8 +683,8 @@ static int verify_points(kb200_setup* s, const uint8_t* proofs48, const uint8_t*
     if (int rc = s->prod.ensure(n * 4)) return rc;   // 4th status class (y)
     CU(cudaMemsetAsync(s->prod.p, 0, n * 4, s->stream));
     // kateth's order in verify_proof: proof, commitment, point, eval (src/kzg/setup.rs:103-110)
-    LAUNCH(s, k_g1_decompress, blocks(n, 64), 64, s->p48.as<uint32_t>(), (int)n, s->aff_p.as<G1Affine>(), s->st_blob.as<int32_t>());
-    LAUNCH(s, k_g1_decompress, blocks(n, 64), 64, s->c48.as<uint32_t>(), (int)n, s->aff_c.as<G1Affine>(), s->st_a.as<int32_t>());
+    LAUNCH(s, k_g1_decompress, blocks(2 * n, 64), 64, s->p48.as<uint32_t>(), s->c48.as<uint32_t>(), (int)n, s->aff_p.as<G1Affine>(), s->aff_c.as<G1Affine>(),
+           s->st_blob.as<int32_t>(), s->st_a.as<int32_t>(), 0);
     LAUNCH(s, k_scalar_check, blocks(n, 128), 128, s->zy32.as<uint32_t>(), (int)n, s->z.as<Fr>(), s->st_b.as<int32_t>());
     LAUNCH(s, k_scalar_check, blocks(n, 128), 128, s->out32.as<uint32_t>(), (int)n, s->y.as<Fr>(), s->prod.as<int32_t>());
     std::vector<int32_t> h[4];
@@ -732,7 +736,7 @@ extern "C" int kb200_test_fr_mul(const uint32_t* a, const uint32_t* b, uint32_t*
     CU(cudaMemcpy(out, dout, n * 32, cudaMemcpyDeviceToHost));
     cudaFree(da); cudaFree(db); cudaFree(dout); return 0;
 }
-extern "C" int kb200_test_g1_decompress(kb200_setup* s, const uint8_t* in48, size_t n, int32_t* status, uint8_t* re48) {
+extern "C" int kb200_test_g1_decompress(kb200_setup* s, const uint8_t* in48, size_t n, int32_t* status, uint8_t* re48, int by_order) {
     if (!s || !in48 || !status || !re48) return KB200_E_ARG;
     CU(cudaSetDevice(s->device));
     if (int rc = h2d(s, s->c48, in48, n * 48)) return rc;
@@ -740,7 +744,7 @@ extern "C" int kb200_test_g1_decompress(kb200_setup* s, const uint8_t* in48, siz
     if (int rc = s->status.ensure(n * 4)) return rc;
     if (int rc = s->out48.ensure(n * 48)) return rc;
     CU(cudaMemsetAsync(s->status.p, 0, n * 4, s->stream));
-    LAUNCH(s, k_g1_decompress, blocks(n, 64), 64, s->c48.as<uint32_t>(), (int)n, s->aff_c.as<G1Affine>(), s->status.as<int32_t>());
+    LAUNCH(s, k_g1_decompress, blocks(n, 64), 64, s->c48.as<uint32_t>(), (const uint32_t*)nullptr, (int)n, s->aff_c.as<G1Affine>(), (G1Affine*)nullptr, s->status.as<int32_t>(), (int32_t*)nullptr, by_order);
     LAUNCH(s, k_test_compress, blocks(n, 64), 64, s->aff_c.as<G1Affine>(), (int)n, s->status.as<int32_t>(), s->out48.as<uint32_t>());
     if (int rc = d2h(s, status, s->status.p, n * 4)) return rc;
     return d2h(s, re48, s->out48.p, n * 48);

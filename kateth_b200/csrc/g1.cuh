@@ -154,8 +154,39 @@ __device__ __noinline__ int g1_uncompress(G1Affine& r, const uint32_t* in12) {
     fp_cneg(y, y, fp_plain_gt_half(t) != want);
     r.x = xm; r.y = y; return KB_OK;
 }
-// subgroup membership by definition: [r]P == infinity   (blst_p1_affine_in_g1)
+// acc = [|x|] base, |x| = 0xd201000000010000 (the BLS parameter; bits 63, 62, 60, 57, 48, 16), MSB-first double-and-add.
+// AFFINE = true: base is the affine point (bx, by); false: base is the XYZZ point *bz.
+template <bool AFFINE>
+__device__ __noinline__ void g1_mul_bls_x(G1& acc, const Fp& bx, const Fp& by, const G1* bz) {
+    const uint64_t X = 0xd201000000010000ull;
+    if (AFFINE) { acc.x = bx; acc.y = by; fp_set(acc.zz, c_k.fp_one); fp_set(acc.zzz, c_k.fp_one); } else acc = *bz;
+#pragma unroll 1
+    for (int i = 62; i >= 0; i--) {
+        g1_dbl(acc);
+        if ((X >> i) & 1) { if (AFFINE) g1_madd(acc, bx, by); else g1_add(acc, *bz); }
+    }
+}
+// Subgroup membership (blst_p1_affine_in_g1).  With beta the cube root of unity below and phi(x, y) = (beta x, y), G1 is the
+// eigenspace phi(P) = [-x^2]P (r = x^4 - x^2 + 1, so lambda = -x^2 satisfies lambda^2 + lambda + 1 = 0 mod r); a point of the
+// curve is in G1 iff that holds (Scott, "A note on group membership tests for G1, G2 and GT on BLS pairing-friendly curves",
+// 2021 -- the test blst uses).  126 doublings + 10 additions instead of the 255 + 128 of [r]P == infinity; checked against the
+// definition on random curve points, cofactor-cleared points and small-order torsion points (tests/test_gpu_parity.py).
 __device__ __noinline__ bool g1_in_subgroup(const G1Affine& p) {
+    if (g1a_is_inf(p)) return true;
+    G1 t1, t2;
+    g1_mul_bls_x<true>(t1, p.x, p.y, nullptr);
+    if (g1_is_inf(t1)) return false;
+    g1_mul_bls_x<false>(t2, p.x, p.y, &t1);          // t2 = [x^2]P
+    if (g1_is_inf(t2)) return false;
+    // phi(P) == -t2  <=>  beta*x*ZZ == X  and  y*ZZZ == -Y
+    Fp bx, l, ry;
+    fp_set(bx, c_k.fp_beta); fp_mul(bx, bx, p.x); fp_mul(l, bx, t2.zz);
+    if (!fp_eq(l, t2.x)) return false;
+    fp_mul(l, p.y, t2.zzz); fp_neg(ry, t2.y);
+    return fp_eq(l, ry);
+}
+// the definition, kept for the unit test that pins the fast test: [r]P == infinity
+__device__ __noinline__ bool g1_in_subgroup_by_order(const G1Affine& p) {
     if (g1a_is_inf(p)) return true;
     Fr k; fr_set(k, c_k.fr_mod);
     G1 t; g1_mul(t, p, k);

@@ -22,15 +22,21 @@ namespace kb200 {
 struct RlcRecord { G1Affine a, b, c; Fr s; };   // 3*96 + 32 = 320 bytes
 static_assert(sizeof(RlcRecord) == 320, "record layout");
 
-// in48: n compressed points; out: affine Montgomery; status[i] set to 3/4/5 on failure (kept if already non-zero)
-__global__ void __launch_bounds__(64) k_g1_decompress(const uint32_t* __restrict__ in48, int n, G1Affine* __restrict__ out, int32_t* __restrict__ status) {
+// Two arrays of n compressed points each (the second may be null) in ONE launch, one thread per point: out = affine
+// Montgomery; status[i] set to 3/4/5 on failure (kept if already non-zero).  by_order != 0 uses the [r]P definition of
+// subgroup membership instead of the endomorphism test (unit test only).
+__global__ void __launch_bounds__(64) k_g1_decompress(const uint32_t* __restrict__ in_a, const uint32_t* __restrict__ in_b, int n,
+                                                      G1Affine* __restrict__ out_a, G1Affine* __restrict__ out_b, int32_t* __restrict__ st_a,
+                                                      int32_t* __restrict__ st_b, int by_order) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+    if (i >= (in_b ? 2 * n : n)) return;
+    const uint32_t* in48 = in_a; G1Affine* out = out_a; int32_t* status = st_a;
+    if (i >= n) { i -= n; in48 = in_b; out = out_b; status = st_b; }
     uint32_t w[12];
     for (int k = 0; k < 12; k++) w[k] = in48[(size_t)i * 12 + k];
     G1Affine p;
     int st = g1_uncompress(p, w);
-    if (st == KB_OK && !g1_in_subgroup(p)) st = KB_G1_NOT_IN_GROUP;
+    if (st == KB_OK && !(by_order ? g1_in_subgroup_by_order(p) : g1_in_subgroup(p))) st = KB_G1_NOT_IN_GROUP;
     if (st != KB_OK) { fp_zero(p.x); fp_zero(p.y); if (status[i] == 0) status[i] = st; }
     out[i] = p;
 }
@@ -131,28 +137,60 @@ __global__ void __launch_bounds__(RLC_FIN_THREADS) k_rlc_finish(const G1* __rest
         if (tid == 0) rec->s = sms[0];
     }
 }
+// neg_g_pow[w] = 2^(8w) * (-G1), affine, w = 0..31: fixed-base table for the [s](-G1) term of the combine step (built at setup)
+__global__ void k_neg_g_table(G1Affine* __restrict__ neg_g_pow) {
+    int w = threadIdx.x;
+    if (w >= 32) return;
+    G1Affine ng; fp_set(ng.x, c_k.g1_gen_x); fp_set(ng.y, c_k.g1_neg_gen_y);
+    G1 t; g1_from_affine(t, ng);
+#pragma unroll 1
+    for (int k = 0; k < 8 * w; k++) g1_dbl(t);
+    G1Affine a; g1_to_affine(a, t);
+    neg_g_pow[w] = a;
+}
 // Combine the records of all ranks into the two G1 pairing operands, as plain (non-Montgomery) affine coordinates:
 // out[0..11] = lhs.x, [12..23] = lhs.y, [24..35] = rhs.x, [36..47] = rhs.y, out[48] = lhs is infinity, out[49] = rhs is infinity.
-__global__ void k_rlc_combine(const RlcRecord* __restrict__ recs, int nrec, uint32_t* __restrict__ out) {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    G1 A, B, C; g1_set_inf(A); g1_set_inf(B); g1_set_inf(C);
+//   lhs = sum_g A_g        rhs = sum_g C_g + [sum_g s_g](-G1) + sum_g B_g
+// One warp: lane w multiplies the fixed point 2^(8w)(-G1) by byte w of s (8 double-and-add steps), the warp tree-sums the 32
+// terms, lane 0 adds the records, lanes 0 and 1 normalise one operand each.
+__global__ void __launch_bounds__(32) k_rlc_combine(const RlcRecord* __restrict__ recs, int nrec, const G1Affine* __restrict__ neg_g_pow,
+                                                    uint32_t* __restrict__ out) {
+    __shared__ G1 sm[16];
+    const int lane = threadIdx.x;
     Fr s; fr_zero(s);
-    for (int g = 0; g < nrec; g++) {
-        RlcRecord r = recs[g];
-        g1_madd_signed(A, r.a, false); g1_madd_signed(B, r.b, false); g1_madd_signed(C, r.c, false);
-        fr_add(s, s, r.s);
+    for (int g = 0; g < nrec; g++) { Fr t = recs[g].s; fr_add(s, s, t); }
+    const uint32_t digit = (s.l[lane >> 2] >> (8 * (lane & 3))) & 0xffu;
+    G1 acc; g1_set_inf(acc);
+    {
+        G1Affine base = neg_g_pow[lane];
+#pragma unroll 1
+        for (int i = 7; i >= 0; i--) { g1_dbl(acc); if ((digit >> i) & 1) g1_madd(acc, base.x, base.y); }
     }
-    // rhs = C - s*G1 + B = C + s*(-G1) + B
-    G1Affine ng; fp_set(ng.x, c_k.g1_gen_x); fp_set(ng.y, c_k.g1_neg_gen_y);
-    G1 t; g1_mul(t, ng, s);
-    g1_add(C, t); g1_add(C, B);
-    G1Affine la, ra; g1_to_affine(la, A); g1_to_affine(ra, C);
-    Fp v;
-    fp_from_mont(v, la.x); for (int k = 0; k < 12; k++) out[k] = v.l[k];
-    fp_from_mont(v, la.y); for (int k = 0; k < 12; k++) out[12 + k] = v.l[k];
-    fp_from_mont(v, ra.x); for (int k = 0; k < 12; k++) out[24 + k] = v.l[k];
-    fp_from_mont(v, ra.y); for (int k = 0; k < 12; k++) out[36 + k] = v.l[k];
-    out[48] = g1a_is_inf(la) ? 1u : 0u; out[49] = g1a_is_inf(ra) ? 1u : 0u;
+#pragma unroll 1
+    for (int stride = 16; stride >= 1; stride >>= 1) {
+        if (lane >= stride && lane < 2 * stride) sm[lane - stride] = acc;
+        __syncwarp();
+        if (lane < stride) g1_add(acc, sm[lane]);
+        __syncwarp();
+    }
+    if (lane == 0) {
+        G1 A, B; g1_set_inf(A); g1_set_inf(B);
+        for (int g = 0; g < nrec; g++) {
+            RlcRecord r = recs[g];
+            g1_madd_signed(A, r.a, false); g1_madd_signed(B, r.b, false); g1_madd_signed(acc, r.c, false);
+        }
+        g1_add(acc, B);
+        sm[0] = A; sm[1] = acc;
+    }
+    __syncwarp();
+    if (lane < 2) {
+        G1 t = sm[lane];
+        G1Affine a; g1_to_affine(a, t);
+        Fp v;
+        fp_from_mont(v, a.x); for (int k = 0; k < 12; k++) out[24 * lane + k] = v.l[k];
+        fp_from_mont(v, a.y); for (int k = 0; k < 12; k++) out[24 * lane + 12 + k] = v.l[k];
+        out[48 + lane] = g1a_is_inf(a) ? 1u : 0u;
+    }
 }
 
 }  // namespace kb200

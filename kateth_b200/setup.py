@@ -299,10 +299,10 @@ class test_hooks:
         return out
 
     @staticmethod
-    def g1_decompress(setup, points48):
+    def g1_decompress(setup, points48, by_order=False):
         n = len(points48)
         st, out = (C.c_int32 * n)(), C.create_string_buffer(48 * n)
-        _check(lib().kb200_test_g1_decompress(setup._h, b"".join(points48), C.c_size_t(n), st, out))
+        _check(lib().kb200_test_g1_decompress(setup._h, b"".join(points48), C.c_size_t(n), st, out, 1 if by_order else 0))
         return list(st), [out.raw[48 * i:48 * i + 48] for i in range(n)]
 
     @staticmethod

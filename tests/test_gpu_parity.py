@@ -227,3 +227,59 @@ def test_other_window_width_gives_same_bytes(wb, oracle_setup):
         assert s.verify_blob_proof_batch_concat(cat, comm, proofs, 4) is True
     finally:
         s.close()
+
+
+# ---------------------------------------------------------------- subgroup test: endomorphism criterion == [r]P definition
+def _ec_add(P, Q):
+    if P is None: return Q
+    if Q is None: return P
+    x1, y1 = P; x2, y2 = Q
+    if x1 == x2:
+        if (y1 + y2) % P_MOD == 0: return None
+        l = 3 * x1 * x1 * pow(2 * y1, -1, P_MOD) % P_MOD
+    else:
+        l = (y2 - y1) * pow(x2 - x1, -1, P_MOD) % P_MOD
+    x3 = (l * l - x1 - x2) % P_MOD
+    return x3, (l * (x1 - x3) - y1) % P_MOD
+
+
+def _ec_mul(k, pt):
+    acc = None
+    while k:
+        if k & 1: acc = _ec_add(acc, pt)
+        pt = _ec_add(pt, pt); k >>= 1
+    return acc
+
+
+P_MOD = P
+
+
+def _compress(pt):
+    if pt is None:
+        return RV.INF
+    x, y = pt
+    b = bytearray(x.to_bytes(48, "big")); b[0] |= 0x80
+    if y > (P_MOD - 1) // 2: b[0] |= 0x20
+    return bytes(b)
+
+
+def test_subgroup_check_matches_definition(engine_setup):
+    """k_g1_decompress uses phi(P) == [-x^2]P (g1.cuh); it must agree with [r]P == infinity on points of the curve that are
+    outside G1 (random points, small-order torsion points) and inside it (cofactor-cleared points)."""
+    import kateth_b200 as K
+    H_COF = 0x396c8c005555e1568c00aaab0000aaab
+    rng = random.Random(7)
+    pts = []
+    while len(pts) < 40:
+        x = rng.randrange(P_MOD); a = (x ** 3 + 4) % P_MOD; y = pow(a, (P_MOD + 1) // 4, P_MOD)
+        if y * y % P_MOD == a:
+            pts.append((x, y))
+    cleared = [_ec_mul(H_COF, q) for q in pts[:6]]                       # in G1
+    torsion = [_ec_mul(R * (H_COF // q), pts[10 + k]) for k, q in enumerate((3, 11, 121, 10177))]   # order divides q: not in G1
+    allp = pts + cleared + [t for t in torsion if t is not None]
+    enc = [_compress(q) for q in allp]
+    st_fast, re_fast = K.test_hooks.g1_decompress(engine_setup, enc)
+    st_def, re_def = K.test_hooks.g1_decompress(engine_setup, enc, by_order=True)
+    assert st_fast == st_def
+    assert st_fast[:40] == [5] * 40 and st_fast[40:46] == [0] * 6 and all(s == 5 for s in st_fast[46:])
+    assert re_fast[40:46] == enc[40:46]
