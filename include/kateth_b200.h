@@ -123,6 +123,10 @@ int kb200_get_info(kb200_setup* s, kb200_info* info);
 /* CUDA-event timing of the dominant kernel (the fixed-base MSM) for roofline reporting: switch on, run, read the summed
  * device time, launch count and number of 4096-point MSMs covered since the last read. */
 int kb200_set_profiling(kb200_setup* s, int on);
+/* Shape of the fixed-base MSM: 0 = automatic (batch-affine summation, msm_ba.cuh, once the batch fills the GPU with one
+ * CTA per blob; XYZZ accumulation with several CTAs per blob below that), 1 = always XYZZ (k_msm), 2 = always batch-affine
+ * (k_msm_ba).  Both produce the same bytes; the switch exists for the parity tests and for profiling. */
+int kb200_set_msm_mode(kb200_setup* s, int mode);
 int kb200_get_msm_profile(kb200_setup* s, double* ms_total, uint64_t* launches, uint64_t* msms);
 
 /* ---- unit-test hooks (device field arithmetic against the oracle; not part of the kateth surface) ---- */

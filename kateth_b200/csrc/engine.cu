@@ -12,6 +12,7 @@
 
 #include "../../include/kateth_b200.h"
 #include "verify.cuh"
+#include "msm_ba.cuh"
 #include "host_bls.hpp"
 
 using namespace kb200;
@@ -56,7 +57,11 @@ struct kb200_setup {
     double setup_seconds = 0;
     // workspace (per chunk)
     DBuf blobs, c48, p48, zy32, out48, out32, st_blob, st_a, st_b, status, z, y, prod, indom, q, partials, aff_c, aff_p, rlc_part, rlc_s, rmont,
-        records, combine;
+        records, combine, dig, scr_pts, scr_pre;
+    // batch-affine MSM (msm_ba.cuh): 0 = automatic (batches that fill the GPU), 1 = always k_msm, 2 = always k_msm_ba
+    int msm_mode = 0, ba_grid = 0;
+    unsigned int* d_counter = nullptr;
+    BaOffset ba_off{};
     uint8_t last_lhs[48], last_rhs[48];
     bool have_last = false;
     // optional CUDA-event timing of the dominant kernel (k_msm), for bench.py's roofline
@@ -258,6 +263,16 @@ static int build_setup(kb200_setup* s, const uint8_t* g1, const uint8_t* g2, int
     CU(cudaGetLastError());
     cudaFree(scratch); cudaFree(d_pts);
     s->tab.data = s->d_table; s->tab.c = c; s->tab.nwin = nwin; s->tab.dlast = dlast;
+    {   // batch-affine MSM: signed-digit offset, persistent grid, work counter
+        memset(&s->ba_off, 0, sizeof s->ba_off);
+        for (int j = 0; j < nwin - 1; j++) { int bit = c * j + c - 1; s->ba_off.l[bit >> 5] |= 1u << (bit & 31); }
+        int occ = 0;
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_msm_ba, BA_THREADS, 0));
+        if (occ < 1) occ = 1;
+        s->ba_grid = occ * s->sm_count;
+        CU(cudaMalloc(&s->d_counter, sizeof(unsigned int)));
+        if (const char* e = getenv("KB200_MSM_MODE")) { int m = atoi(e); if (m >= 0 && m <= 2) s->msm_mode = m; }
+    }
     s->table_bytes = bytes;
     s->setup_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     return 0;
@@ -300,13 +315,19 @@ extern "C" void kb200_setup_free(kb200_setup* s) {
     if (s->d_roots) cudaFree(s->d_roots);
     if (s->d_neg_g_pow) cudaFree(s->d_neg_g_pow);
     if (s->d_table) cudaFree(s->d_table);
+    if (s->d_counter) cudaFree(s->d_counter);
     DBuf* bufs[] = {&s->blobs, &s->c48, &s->p48, &s->zy32, &s->out48, &s->out32, &s->st_blob, &s->st_a, &s->st_b, &s->status, &s->z, &s->y, &s->prod,
-                    &s->indom, &s->q, &s->partials, &s->aff_c, &s->aff_p, &s->rlc_part, &s->rlc_s, &s->rmont, &s->records, &s->combine};
+                    &s->indom, &s->q, &s->partials, &s->aff_c, &s->aff_p, &s->rlc_part, &s->rlc_s, &s->rmont, &s->records, &s->combine, &s->dig, &s->scr_pts, &s->scr_pre};
     for (DBuf* b : bufs) b->release();
     for (cudaEvent_t e : s->prof_ev) cudaEventDestroy(e);
     delete s;
 }
 extern "C" int kb200_set_stream(kb200_setup* s, void* stream) { if (!s) return KB200_E_ARG; s->stream = (cudaStream_t)stream; return 0; }
+extern "C" int kb200_set_msm_mode(kb200_setup* s, int mode) {
+    if (!s || mode < 0 || mode > 2) return KB200_E_ARG;
+    s->msm_mode = mode;
+    return 0;
+}
 extern "C" int kb200_set_profiling(kb200_setup* s, int on) {
     if (!s) return KB200_E_ARG;
     s->prof = on != 0; s->prof_used = 0; s->prof_items = 0;
@@ -344,14 +365,33 @@ static inline int blocks(size_t n, int t) { return (int)((n + t - 1) / t); }
 template <int FMT>
 static int run_msm(kb200_setup* s, const uint32_t* d_scalars, size_t n, const int32_t* d_status, uint32_t* d_out48) {
     int S = pick_slices(s, n);
+    const bool ba = s->msm_mode == 2 || (s->msm_mode == 0 && S == 1);
+    if (ba) S = 1;
     if (int rc = s->partials.ensure(n * S * sizeof(G1))) return rc;
+    unsigned grid = 0;
+    if (ba) {
+        const size_t K1 = (size_t)BA_UB * s->tab.nwin / 2;
+        grid = (unsigned)((n < (size_t)s->ba_grid) ? n : (size_t)s->ba_grid);
+        if (int rc = s->dig.ensure(n * KB_N * (size_t)s->tab.nwin * 4)) return rc;
+        if (int rc = s->scr_pts.ensure((size_t)s->ba_grid * K1 * 6 * BA_THREADS * sizeof(uint4))) return rc;
+        if (int rc = s->scr_pre.ensure((size_t)s->ba_grid * K1 * 3 * BA_THREADS * sizeof(uint4))) return rc;
+    }
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (s->prof) {
         if (s->prof_used + 2 > s->prof_ev.size()) { cudaEvent_t a, b; CU(cudaEventCreate(&a)); CU(cudaEventCreate(&b)); s->prof_ev.push_back(a); s->prof_ev.push_back(b); }
         e0 = s->prof_ev[s->prof_used]; e1 = s->prof_ev[s->prof_used + 1]; s->prof_used += 2; s->prof_items += n;
         CU(cudaEventRecord(e0, s->stream));
     }
-    LAUNCH(s, (k_msm<FMT>), (unsigned)(n * S), MSM_THREADS, s->tab, d_scalars, d_status, s->partials.as<G1>(), S);
+    if (ba) {
+        CU(cudaMemsetAsync(s->d_counter, 0, sizeof(unsigned int), s->stream));
+        LAUNCH(s, (k_msm_recode<FMT>), blocks(n * KB_N, 256), 256, s->tab, s->ba_off, d_scalars, d_status, s->dig.as<uint32_t>(), (int)n);
+        BaArgs a;
+        a.tab = s->tab; a.dig = s->dig.as<uint32_t>(); a.scr_pts = s->scr_pts.as<uint4>(); a.scr_pre = s->scr_pre.as<uint4>();
+        a.partials = s->partials.as<G1>(); a.status = d_status; a.counter = s->d_counter; a.n = (int)n;
+        LAUNCH(s, k_msm_ba, grid, BA_THREADS, a);
+    } else {
+        LAUNCH(s, (k_msm<FMT>), (unsigned)(n * S), MSM_THREADS, s->tab, d_scalars, d_status, s->partials.as<G1>(), S);
+    }
     if (e1) CU(cudaEventRecord(e1, s->stream));
     LAUNCH(s, k_msm_finish, blocks(n, 32), 32, s->partials.as<G1>(), S, (int)n, d_status, d_out48, (G1Affine*)nullptr);
     return 0;

@@ -1,0 +1,278 @@
+// msm_ba.cuh -- the throughput shape of the fixed-base MSM: batch-affine summation of the gathered table points.
+//
+// Same job as k_msm (msm.cuh): replaces P1::lincomb_pippenger (/root/reference/src/bls.rs:416-437) behind
+// Blob::commitment (src/blob.rs:48-53) and Polynomial::prove (src/kzg/poly.rs:68).  k_msm adds every gathered table
+// point into an XYZZ accumulator (8M + 2S = 10 Fp products per point).  All 4096 * W points of one MSM only have to be
+// SUMMED, so here they are first added pairwise in AFFINE coordinates, where an addition costs 1S + 2M once the
+// inverse of (x2 - x1) is known, and the inverses of a whole batch come from one shared inversion (3 products per
+// element for the prefix/suffix products + one binary-GCD inversion per batch, fp_bgcd.cuh: ~10 products' worth of
+// multiplier work).  Per thread and unit (8 bases x W windows = 8W gathered points):
+//     round 1: 4W pairs of table points        -> 4W affine sums
+//     round 2: 2W pairs of round-1 sums        -> 2W
+//     round 3:  W pairs                        ->  W
+//     then W mixed additions into the thread's XYZZ accumulator,
+// i.e. (6*7W + 3*10 + 10*W) / 8W = 6.7 products per gathered point at W = 17 instead of 10.  The sums of a round live in
+// a per-CTA scratch area in HBM, interleaved by thread so every access is a coalesced 512-byte warp transaction; the
+// table points are simply gathered twice (once for the denominators, once for the additions).
+// Exceptional pairs (an operand at infinity = zero digit, P == Q, P == -Q) are detected from the x coordinates in both
+// passes and take a slow path with the complete formulas (doubling shares the batch inversion with denominator 2y),
+// so the 48-byte result is the same group element whatever the scalars or the setup are.
+//
+// The scalars are recoded once per MSM by k_msm_recode into 32-bit table row references (signed digits: adding
+// 2^(c-1) to every window below the top one turns the unsigned window value v into the signed digit v - 2^(c-1)).
+#pragma once
+#include "msm.cuh"
+#include "fp_bgcd.cuh"
+
+namespace kb200 {
+
+#define BA_THREADS 128
+#define BA_UNITS 4                 // units per thread; BA_UNITS * BA_UB * BA_THREADS = 4096 bases per CTA (one blob)
+#define BA_UB 8                    // bases per unit per thread
+#define BA_ZERO 0xffffffffu        // digit 0: nothing to add
+
+struct BaOffset { uint32_t l[8]; };     // sum_{j < nwin-1} 2^(c-1) * 2^(c*j)
+
+// One out-of-line copy of the Montgomery product for everything in this kernel.  The batch-affine kernel has its warps
+// in different phases (prefix products, inversion, additions, final accumulation) at the same time; with the 400-
+// instruction product inlined at every call site the instruction working set is > 100 KB and the warps stall on
+// instruction fetch (ncu: no_instructions 28 %).  Arguments and result travel in registers (by-value structs: no stack).
+__device__ __noinline__ Fp fp_mulc(Fp a, Fp b) { Fp r; fp_mul(r, a, b); return r; }
+#define BA_MUL(r, a, b) r = fp_mulc(a, b)
+#define BA_SQR(r, a) r = fp_mulc(a, a)
+
+// g1_madd / g1_add (g1.cuh) on the shared product
+__device__ __noinline__ void ba_madd(G1& acc, const Fp& x2, const Fp& y2) {
+    if (fp_is_zero(x2)) return;                                     // (0,0): nothing to add
+    if (g1_is_inf(acc)) { acc.x = x2; acc.y = y2; fp_set(acc.zz, c_k.fp_one); fp_set(acc.zzz, c_k.fp_one); return; }
+    Fp p, r, pp, ppp, q, t;
+    BA_MUL(p, x2, acc.zz); fp_sub(p, p, acc.x);
+    BA_MUL(r, y2, acc.zzz); fp_sub(r, r, acc.y);
+    if (fp_is_zero(p)) { G1 tmp = acc; g1_madd_rare(&tmp, &x2, &y2, fp_is_zero(r)); acc = tmp; return; }
+    BA_SQR(pp, p); BA_MUL(ppp, p, pp); BA_MUL(q, acc.x, pp);
+    BA_SQR(t, r); fp_sub(t, t, ppp); fp_sub(t, t, q); fp_sub(acc.x, t, q);
+    fp_sub(q, q, acc.x); BA_MUL(q, r, q); BA_MUL(t, acc.y, ppp); fp_sub(acc.y, q, t);
+    BA_MUL(acc.zz, acc.zz, pp); BA_MUL(acc.zzz, acc.zzz, ppp);
+}
+__device__ __noinline__ void ba_add(G1& acc, const G1& b) {
+    if (g1_is_inf(b)) return;
+    if (g1_is_inf(acc)) { acc = b; return; }
+    Fp u1, u2, s1, s2, p, r, pp, ppp, q, t;
+    BA_MUL(u1, acc.x, b.zz); BA_MUL(u2, b.x, acc.zz);
+    BA_MUL(s1, acc.y, b.zzz); BA_MUL(s2, b.y, acc.zzz);
+    fp_sub(p, u2, u1); fp_sub(r, s2, s1);
+    if (fp_is_zero(p)) {
+        if (fp_is_zero(r)) g1_dbl(acc); else g1_set_inf(acc);
+        return;
+    }
+    BA_SQR(pp, p); BA_MUL(ppp, p, pp); BA_MUL(q, u1, pp);
+    BA_SQR(t, r); fp_sub(t, t, ppp); fp_sub(t, t, q); fp_sub(acc.x, t, q);
+    fp_sub(q, q, acc.x); BA_MUL(q, r, q); BA_MUL(t, s1, ppp); fp_sub(acc.y, q, t);
+    BA_MUL(acc.zz, acc.zz, b.zz); BA_MUL(acc.zz, acc.zz, pp);
+    BA_MUL(acc.zzz, acc.zzz, b.zzz); BA_MUL(acc.zzz, acc.zzz, ppp);
+}
+// inversion on the shared product (fp_inv_bgcd, fp_bgcd.cuh)
+__device__ __noinline__ Fp ba_inv(Fp a) {
+    Fp r3 = {{0xd94ca1e0u, 0xed48ac6bu, 0x03a7adf8u, 0x315f831eu, 0x615e29ddu, 0x9a53352au, 0x921e1761u, 0x34c04e5eu, 0x65724728u, 0x2512d435u, 0x91755d4du, 0x0aa63460u}};
+    Fp t;
+    if (bg_inverse(t.l, a.l)) return fp_mulc(t, r3);
+    Fp r; fp_inv(r, a); return r;
+}
+
+// digits: dig[((item * BA_UNITS + u) * NP + p) * BA_THREADS + t],  NP = BA_UB * nwin,  p = j * BA_UB + b,
+// for base i = (u * BA_UB + b) * BA_THREADS + t and window j.  Value: bit 31 = negative, low bits = table row
+// (j << (c-1)) + |d| - 1, or BA_ZERO.
+template <int FMT>
+__global__ void __launch_bounds__(256) k_msm_recode(MsmTable tab, BaOffset off, const uint32_t* __restrict__ scalars, const int32_t* __restrict__ status,
+                                                    uint32_t* __restrict__ dig, int n) {
+    size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int item = (int)(gid >> 12), i = (int)(gid & (KB_N - 1));
+    if (item >= n) return;
+    if (status != nullptr && status[item] != 0) return;
+    uint32_t s[8];
+    {
+        const uint4* sp = reinterpret_cast<const uint4*>(scalars + gid * 8);
+        uint4 a = __ldg(sp), b = __ldg(sp + 1);
+        if (FMT == 0) {
+            s[7] = bswap32(a.x); s[6] = bswap32(a.y); s[5] = bswap32(a.z); s[4] = bswap32(a.w);
+            s[3] = bswap32(b.x); s[2] = bswap32(b.y); s[1] = bswap32(b.z); s[0] = bswap32(b.w);
+        } else {
+            s[0] = a.x; s[1] = a.y; s[2] = a.z; s[3] = a.w; s[4] = b.x; s[5] = b.y; s[6] = b.z; s[7] = b.w;
+        }
+    }
+    {   // s += off  (s < r < 2^255 and off < 2^255: no carry out)
+        uint32_t cy = 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) { uint64_t t = (uint64_t)s[k] + off.l[k] + cy; s[k] = (uint32_t)t; cy = (uint32_t)(t >> 32); }
+    }
+    const int c = tab.c, nwin = tab.nwin;
+    const uint32_t mask = (1u << c) - 1, D = 1u << (c - 1);
+    const int t = i & (BA_THREADS - 1), ub = i >> 7, u = ub >> 3, b = ub & (BA_UB - 1);
+    const int NP = BA_UB * nwin;
+    uint32_t* out = dig + (((size_t)item * BA_UNITS + u) * NP + b) * BA_THREADS + t;
+#pragma unroll 1
+    for (int j = 0; j < nwin; j++) {
+        uint32_t v = s[0] & mask;
+#pragma unroll
+        for (int k = 0; k < 7; k++) s[k] = __funnelshift_r(s[k], s[k + 1], c);
+        s[7] >>= c;
+        uint32_t e;
+        if (j == nwin - 1) {
+            v = s[0] << c | v;       // the top window keeps everything that is left (it is unsigned)
+            e = v ? (((uint32_t)j << (c - 1)) + v - 1) : BA_ZERO;
+        } else {
+            int d = (int)v - (int)D;
+            uint32_t mag = d < 0 ? (uint32_t)(-d) : (uint32_t)d;
+            e = d ? ((((uint32_t)j << (c - 1)) + mag - 1) | (d < 0 ? 0x80000000u : 0u)) : BA_ZERO;
+        }
+        out[(size_t)j * BA_UB * BA_THREADS] = e;
+    }
+}
+
+struct BaArgs {
+    MsmTable tab;
+    const uint32_t* dig;
+    uint4* scr_pts;          // per CTA slot: K1 points, [(slot * K1 + s) * 6 + q] * BA_THREADS + t
+    uint4* scr_pre;          // per CTA slot: K1 prefix products, [(slot * K1 + k) * 3 + q] * BA_THREADS + t
+    G1* partials;            // one XYZZ sum per item
+    const int32_t* status;
+    unsigned int* counter;   // work counter (zeroed before the launch)
+    int n;
+};
+
+// a reference to one operand of a round: table entry (stride 1) or scratch slot (stride BA_THREADS)
+struct BaRef { const uint4* p; int stride; bool neg, zero; };
+
+__device__ __forceinline__ void ba_ld(Fp& r, const uint4* p, int stride) {
+    uint4 a = p[0], b = p[stride], c = p[2 * stride];
+    r.l[0] = a.x; r.l[1] = a.y; r.l[2] = a.z; r.l[3] = a.w; r.l[4] = b.x; r.l[5] = b.y; r.l[6] = b.z; r.l[7] = b.w;
+    r.l[8] = c.x; r.l[9] = c.y; r.l[10] = c.z; r.l[11] = c.w;
+}
+__device__ __forceinline__ void ba_st(uint4* p, const Fp& r) {
+    p[0] = make_uint4(r.l[0], r.l[1], r.l[2], r.l[3]);
+    p[BA_THREADS] = make_uint4(r.l[4], r.l[5], r.l[6], r.l[7]);
+    p[2 * BA_THREADS] = make_uint4(r.l[8], r.l[9], r.l[10], r.l[11]);
+}
+__device__ __forceinline__ void ba_ldx(Fp& x, const BaRef& r) { if (r.zero) fp_zero(x); else ba_ld(x, r.p, r.stride); }
+__device__ __forceinline__ void ba_ldy(Fp& y, const BaRef& r) {
+    if (r.zero) { fp_zero(y); return; }
+    Fp t; ba_ld(t, r.p + 3 * r.stride, r.stride);
+    fp_cneg(y, t, r.neg);
+}
+
+// Denominator of an exceptional pair (an operand at infinity, or x1 == x2): 2*y1 for a doubling, else 1 (nothing to invert).
+__device__ __noinline__ void ba_rare_den(Fp* den, const Fp* x1, const Fp* x2, const BaRef* r1, const BaRef* r2) {
+    fp_set(*den, c_k.fp_one);
+    if (fp_is_zero(*x1) || fp_is_zero(*x2)) return;
+    Fp y1, y2; ba_ldy(y1, *r1); ba_ldy(y2, *r2);
+    if (fp_eq(y1, y2)) fp_dbl(*den, y1);
+}
+// Sum of an exceptional pair; advances the running inverse exactly as the forward pass advanced the running product.
+__device__ __noinline__ void ba_rare_add(Fp* x3, Fp* y3, Fp* inv, const Fp* pk, const Fp* x1, const Fp* y1, const Fp* x2, const Fp* y2) {
+    const bool i1 = fp_is_zero(*x1), i2 = fp_is_zero(*x2);
+    if (i1 && i2) { fp_zero(*x3); fp_zero(*y3); return; }
+    if (i1) { *x3 = *x2; *y3 = *y2; return; }
+    if (i2) { *x3 = *x1; *y3 = *y1; return; }
+    if (!fp_eq(*y1, *y2)) { fp_zero(*x3); fp_zero(*y3); return; }       // P + (-P)
+    Fp den, dinv, lam, t, u;
+    fp_dbl(den, *y1);
+    BA_MUL(dinv, *inv, *pk); BA_MUL(*inv, *inv, den);
+    BA_SQR(t, *x1); fp_dbl(u, t); fp_add(t, t, u);                      // 3 x1^2
+    BA_MUL(lam, t, dinv);
+    BA_SQR(t, lam); fp_sub(t, t, *x1); fp_sub(t, t, *x1);
+    fp_sub(u, *x1, t); BA_MUL(u, lam, u); fp_sub(*y3, u, *y1);
+    *x3 = t;
+}
+
+__global__ void __launch_bounds__(BA_THREADS) k_msm_ba(BaArgs A) {
+    __shared__ G1 sm[BA_THREADS / 2];
+    __shared__ unsigned int s_item;
+    const int tid = threadIdx.x;
+    const int nwin = A.tab.nwin, c = A.tab.c;
+    const int NP = BA_UB * nwin, K1 = NP / 2;
+    uint4* const pts = A.scr_pts + (size_t)blockIdx.x * K1 * 6 * BA_THREADS + tid;
+    uint4* const pre = A.scr_pre + (size_t)blockIdx.x * K1 * 3 * BA_THREADS + tid;
+    (void)c;
+    for (;;) {
+        if (tid == 0) s_item = atomicAdd(A.counter, 1u);
+        __syncthreads();
+        const unsigned int item = s_item;
+        __syncthreads();
+        if (item >= (unsigned int)A.n) break;
+        G1 acc; g1_set_inf(acc);
+        if (A.status == nullptr || A.status[item] == 0) {
+#pragma unroll 1
+            for (int u = 0; u < BA_UNITS; u++) {
+                const uint32_t* dg = A.dig + ((size_t)item * BA_UNITS + u) * NP * BA_THREADS + tid;
+                const int base0 = u * BA_UB * BA_THREADS + tid;
+                auto ref = [&](int round, int idx) -> BaRef {
+                    BaRef r;
+                    if (round == 0) {
+                        uint32_t d = dg[(size_t)idx * BA_THREADS];
+                        r.zero = d == BA_ZERO; r.neg = (d >> 31) != 0;
+                        size_t e = (size_t)(d & 0x7fffffffu) * KB_N + (size_t)(base0 + (idx & (BA_UB - 1)) * BA_THREADS);
+                        r.p = A.tab.data + (r.zero ? 0 : e * 6); r.stride = 1;
+                    } else {
+                        r.zero = false; r.neg = false; r.p = pts + (size_t)idx * 6 * BA_THREADS; r.stride = BA_THREADS;
+                    }
+                    return r;
+                };
+#pragma unroll 1
+                for (int round = 0, K = K1; round < 3; round++, K >>= 1) {
+                    // forward: prefix products of the denominators
+                    Fp run; fp_set(run, c_k.fp_one);
+#pragma unroll 1
+                    for (int k = 0; k < K; k++) {
+                        BaRef r1 = ref(round, k), r2 = ref(round, k + K);
+                        Fp x1, x2, d;
+                        ba_ldx(x1, r1); ba_ldx(x2, r2);
+                        ba_st(pre + (size_t)k * 3 * BA_THREADS, run);
+                        fp_sub(d, x2, x1);
+                        if (fp_is_zero(x1) || fp_is_zero(x2) || fp_is_zero(d)) ba_rare_den(&d, &x1, &x2, &r1, &r2);
+                        BA_MUL(run, run, d);
+                    }
+                    Fp inv = ba_inv(run);
+                    // backward: the additions
+#pragma unroll 1
+                    for (int k = K - 1; k >= 0; k--) {
+                        BaRef r1 = ref(round, k), r2 = ref(round, k + K);
+                        Fp x1, y1, x2, y2, pk, d, x3, y3;
+                        ba_ldx(x1, r1); ba_ldy(y1, r1); ba_ldx(x2, r2); ba_ldy(y2, r2);
+                        ba_ld(pk, pre + (size_t)k * 3 * BA_THREADS, BA_THREADS);
+                        fp_sub(d, x2, x1);
+                        if (fp_is_zero(x1) || fp_is_zero(x2) || fp_is_zero(d)) {
+                            ba_rare_add(&x3, &y3, &inv, &pk, &x1, &y1, &x2, &y2);
+                        } else {
+                            Fp dinv, lam, t;
+                            BA_MUL(dinv, inv, pk); BA_MUL(inv, inv, d);
+                            fp_sub(t, y2, y1); BA_MUL(lam, t, dinv);
+                            BA_SQR(x3, lam); fp_sub(x3, x3, x1); fp_sub(x3, x3, x2);
+                            fp_sub(t, x1, x3); BA_MUL(t, lam, t); fp_sub(y3, t, y1);
+                        }
+                        uint4* o = pts + (size_t)k * 6 * BA_THREADS;
+                        ba_st(o, x3); ba_st(o + 3 * BA_THREADS, y3);
+                    }
+                }
+                // the W sums of this unit -> XYZZ accumulator
+#pragma unroll 1
+                for (int k = 0; k < nwin; k++) {
+                    G1Affine pt;
+                    ba_ld(pt.x, pts + (size_t)k * 6 * BA_THREADS, BA_THREADS);
+                    ba_ld(pt.y, pts + (size_t)k * 6 * BA_THREADS + 3 * BA_THREADS, BA_THREADS);
+                    ba_madd(acc, pt.x, pt.y);
+                }
+            }
+        }
+        // CTA tree reduction through shared memory
+#pragma unroll 1
+        for (int stride = BA_THREADS / 2; stride >= 1; stride >>= 1) {
+            if (tid >= stride && tid < 2 * stride) sm[tid - stride] = acc;
+            __syncthreads();
+            if (tid < stride) ba_add(acc, sm[tid]);
+            __syncthreads();
+        }
+        if (tid == 0) A.partials[item] = acc;
+    }
+}
+
+}  // namespace kb200

@@ -200,13 +200,14 @@ def test_g1_decompress_classes(engine_setup):
     assert re[0] == RV.G1 and re[1] == RV.INF
 
 
-@pytest.mark.parametrize("wb", [9, 15])
-def test_other_window_width_gives_same_bytes(wb, oracle_setup):
+@pytest.mark.parametrize("wb,mode", [(9, 1), (15, 1), (9, 2), (13, 2), (15, 2)])
+def test_other_window_width_gives_same_bytes(wb, mode, oracle_setup):
     """The window width is a tuning knob, not a semantic one.  15 is bench.py's throughput configuration (17 windows, the
     top one unsigned and 15 bits wide, 107 GiB table); 9 exercises a 3-bit top window."""
     import kateth_b200 as K
     s = K.Setup.load_json(os.path.join(ROOT, "tests/golden/trusted_setup_4096.json"), window_bits=wb)
     try:
+        s.set_msm_mode(mode)        # 1 = XYZZ accumulation (k_msm), 2 = batch-affine summation (k_msm_ba)
         vb = RV.valid_blobs()
         for i, hexv in GOLD_COMM.items():
             assert s.blob_to_commitment(vb[i]).hex() == hexv
@@ -283,3 +284,46 @@ def test_subgroup_check_matches_definition(engine_setup):
     assert st_fast == st_def
     assert st_fast[:40] == [5] * 40 and st_fast[40:46] == [0] * 6 and all(s == 5 for s in st_fast[46:])
     assert re_fast[40:46] == enc[40:46]
+
+
+# ---------------------------------------------------------------- batch-affine MSM: all vectors, and a degenerate setup
+def test_all_253_vectors_through_batch_affine_msm(monkeypatch):
+    monkeypatch.setenv("KB200_MSM_MODE", "2")
+    counts, bad, missing = RV.check_all("engine")
+    assert sum(counts.values()) == 253
+    assert not bad, bad[:5]
+    assert not missing
+
+
+@pytest.mark.parametrize("mode", [1, 2])
+def test_degenerate_setup_exercises_exceptional_additions(mode, tmp_path):
+    """A setup whose Lagrange points are small multiples of the generator makes gathered table points and partial sums
+    collide all the time (P == Q, P == -Q, infinity): the complete-formula paths of both MSM shapes must still give the
+    group element the oracle's Pippenger gives."""
+    import json
+    import kateth_b200 as K
+    from oracle import oracle as O
+    real = json.load(open(os.path.join(ROOT, "tests/golden/trusted_setup_4096.json")))
+    gx = int.from_bytes(bytes([RV.G1[0] & 0x1f]) + RV.G1[1:], "big")
+    gy = 0x08b3f481e3aaa0f1a09e30ed741d8ae4fcf5e095d5d00af600db18cb2c04b3edd03cc744a2888ae40caa232946c5e7e1
+    mult = [None] + [_ec_mul(k, (gx, gy)) for k in range(1, 8)]
+    pts = ["0x" + _compress(mult[1 + (i * 7 + i // 64) % 7]).hex() for i in range(4096)]
+    path = tmp_path / "degenerate_setup.json"
+    path.write_text(json.dumps({"g1_lagrange": pts, "g2_monomial": real["g2_monomial"]}))
+    s = K.Setup.load_json(str(path), window_bits=9)
+    o = O.Setup.load_json(str(path))
+    try:
+        s.set_msm_mode(mode)
+        rng = random.Random(77)
+        small = [0, 1, 2, 3, 4, R - 1, R - 2, R - 3, 255, 256, 257, R - 256]
+        blobs = [b"".join(RV.fe(rng.choice(small)) for _ in range(4096)),
+                 b"".join(RV.fe(1) for _ in range(4096)),
+                 b"".join(RV.fe(R - 1 if k & 1 else 1) for k in range(4096)),
+                 b"".join(RV.fe(rng.randrange(R)) for _ in range(4096)),
+                 b"".join(RV.fe(rng.randrange(1 << 18)) for _ in range(4096))]
+        comm, st = s.blob_to_commitment_many(b"".join(blobs), len(blobs))
+        assert st == [0] * len(blobs)
+        for i, b in enumerate(blobs):
+            assert comm[48 * i:48 * i + 48] == o.blob_to_commitment(b), i
+    finally:
+        s.close()
