@@ -27,8 +27,9 @@
 namespace kb200 {
 
 #define BA_THREADS 128
-#define BA_UNITS 4                 // units per thread; BA_UNITS * BA_UB * BA_THREADS = 4096 bases per CTA (one blob)
-#define BA_UB 8                    // bases per unit per thread
+#define BA_UB_LOG 5
+#define BA_UB (1 << BA_UB_LOG)     // bases per unit per thread; a unit is reduced by BA_UB_LOG halving rounds
+#define BA_UNITS (KB_N / (BA_THREADS * BA_UB))   // units per thread (one CTA = one blob)
 #define BA_ZERO 0xffffffffu        // digit 0: nothing to add
 
 struct BaOffset { uint32_t l[8]; };     // sum_{j < nwin-1} 2^(c-1) * 2^(c*j)
@@ -107,7 +108,7 @@ __global__ void __launch_bounds__(256) k_msm_recode(MsmTable tab, BaOffset off, 
     }
     const int c = tab.c, nwin = tab.nwin;
     const uint32_t mask = (1u << c) - 1, D = 1u << (c - 1);
-    const int t = i & (BA_THREADS - 1), ub = i >> 7, u = ub >> 3, b = ub & (BA_UB - 1);
+    const int t = i & (BA_THREADS - 1), ub = i >> 7, u = ub >> BA_UB_LOG, b = ub & (BA_UB - 1);
     const int NP = BA_UB * nwin;
     uint32_t* out = dig + (((size_t)item * BA_UNITS + u) * NP + b) * BA_THREADS + t;
 #pragma unroll 1
@@ -142,6 +143,8 @@ struct BaArgs {
 
 // a reference to one operand of a round: table entry (stride 1) or scratch slot (stride BA_THREADS)
 struct BaRef { const uint4* p; int stride; bool neg, zero; };
+// what a thread needs to find the operands of its current unit
+struct BaCtx { const uint4* tab; const uint32_t* dg; uint4* pts; int base0; };
 
 __device__ __forceinline__ void ba_ld(Fp& r, const uint4* p, int stride) {
     uint4 a = p[0], b = p[stride], c = p[2 * stride];
@@ -153,46 +156,79 @@ __device__ __forceinline__ void ba_st(uint4* p, const Fp& r) {
     p[BA_THREADS] = make_uint4(r.l[4], r.l[5], r.l[6], r.l[7]);
     p[2 * BA_THREADS] = make_uint4(r.l[8], r.l[9], r.l[10], r.l[11]);
 }
+__device__ __forceinline__ uint32_t ba_digit(const BaCtx& c, int idx) { return c.dg[(size_t)idx * BA_THREADS]; }
+// operand idx of a round: round 0 reads the table through the digit d, later rounds read scratch slot idx
+__device__ __forceinline__ BaRef ba_ref(const BaCtx& c, int round, int idx, uint32_t d) {
+    BaRef r;
+    if (round == 0) {
+        r.zero = d == BA_ZERO; r.neg = (d >> 31) != 0;
+        size_t e = (size_t)(d & 0x7fffffffu) * KB_N + (size_t)(c.base0 + (idx & (BA_UB - 1)) * BA_THREADS);
+        r.p = c.tab + (r.zero ? 0 : e * 6); r.stride = 1;
+    } else {
+        r.zero = false; r.neg = false; r.p = c.pts + (size_t)idx * 6 * BA_THREADS; r.stride = BA_THREADS;
+    }
+    return r;
+}
 __device__ __forceinline__ void ba_ldx(Fp& x, const BaRef& r) { if (r.zero) fp_zero(x); else ba_ld(x, r.p, r.stride); }
 __device__ __forceinline__ void ba_ldy(Fp& y, const BaRef& r) {
     if (r.zero) { fp_zero(y); return; }
     Fp t; ba_ld(t, r.p + 3 * r.stride, r.stride);
     fp_cneg(y, t, r.neg);
 }
-
-// Denominator of an exceptional pair (an operand at infinity, or x1 == x2): 2*y1 for a doubling, else 1 (nothing to invert).
-__device__ __noinline__ void ba_rare_den(Fp* den, const Fp* x1, const Fp* x2, const BaRef* r1, const BaRef* r2) {
-    fp_set(*den, c_k.fp_one);
-    if (fp_is_zero(*x1) || fp_is_zero(*x2)) return;
-    Fp y1, y2; ba_ldy(y1, *r1); ba_ldy(y2, *r2);
-    if (fp_eq(y1, y2)) fp_dbl(*den, y1);
+// pull a table entry (96 bytes: at most two 128-byte lines) into L2 ahead of its use
+__device__ __forceinline__ void ba_prefetch(const BaRef& r) {
+    if (r.zero || r.stride != 1) return;
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(r.p));
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(r.p + 5));
 }
-// Sum of an exceptional pair; advances the running inverse exactly as the forward pass advanced the running product.
-__device__ __noinline__ void ba_rare_add(Fp* x3, Fp* y3, Fp* inv, const Fp* pk, const Fp* x1, const Fp* y1, const Fp* x2, const Fp* y2) {
-    const bool i1 = fp_is_zero(*x1), i2 = fp_is_zero(*x2);
-    if (i1 && i2) { fp_zero(*x3); fp_zero(*y3); return; }
-    if (i1) { *x3 = *x2; *y3 = *y2; return; }
-    if (i2) { *x3 = *x1; *y3 = *y1; return; }
-    if (!fp_eq(*y1, *y2)) { fp_zero(*x3); fp_zero(*y3); return; }       // P + (-P)
-    Fp den, dinv, lam, t, u;
-    fp_dbl(den, *y1);
-    BA_MUL(dinv, *inv, *pk); BA_MUL(*inv, *inv, den);
-    BA_SQR(t, *x1); fp_dbl(u, t); fp_add(t, t, u);                      // 3 x1^2
-    BA_MUL(lam, t, dinv);
-    BA_SQR(t, lam); fp_sub(t, t, *x1); fp_sub(t, t, *x1);
-    fp_sub(u, *x1, t); BA_MUL(u, lam, u); fp_sub(*y3, u, *y1);
-    *x3 = t;
+
+// Exceptional pairs (an operand at infinity, or x1 == x2) leave the hot loops through these two out-of-line functions;
+// they re-read their operands themselves so that nothing in the hot loops has its address taken.
+// Denominator: 2*y1 for a doubling, else 1 (nothing to invert).
+__device__ __noinline__ Fp ba_rare_den(BaCtx c, int round, int k, int K) {
+    BaRef r1 = ba_ref(c, round, k, round == 0 ? ba_digit(c, k) : 0u), r2 = ba_ref(c, round, k + K, round == 0 ? ba_digit(c, k + K) : 0u);
+    Fp den, x1, x2;
+    fp_set(den, c_k.fp_one);
+    ba_ldx(x1, r1); ba_ldx(x2, r2);
+    if (fp_is_zero(x1) || fp_is_zero(x2)) return den;
+    Fp y1, y2; ba_ldy(y1, r1); ba_ldy(y2, r2);
+    if (fp_eq(x1, x2) && fp_eq(y1, y2)) fp_dbl(den, y1);
+    return den;
+}
+// Sum of an exceptional pair, written to scratch slot k; returns the running inverse advanced exactly as the forward pass
+// advanced the running product.
+__device__ __noinline__ Fp ba_rare_add(BaCtx c, int round, int k, int K, Fp inv, Fp pk) {
+    BaRef r1 = ba_ref(c, round, k, round == 0 ? ba_digit(c, k) : 0u), r2 = ba_ref(c, round, k + K, round == 0 ? ba_digit(c, k + K) : 0u);
+    Fp x1, y1, x2, y2, x3, y3;
+    ba_ldx(x1, r1); ba_ldy(y1, r1); ba_ldx(x2, r2); ba_ldy(y2, r2);
+    const bool i1 = fp_is_zero(x1), i2 = fp_is_zero(x2);
+    if (i1 && i2) { fp_zero(x3); fp_zero(y3); }
+    else if (i1) { x3 = x2; y3 = y2; }
+    else if (i2) { x3 = x1; y3 = y1; }
+    else if (!fp_eq(y1, y2)) { fp_zero(x3); fp_zero(y3); }            // P + (-P)
+    else {
+        Fp den, dinv, lam, t, u;
+        fp_dbl(den, y1);
+        BA_MUL(dinv, inv, pk); BA_MUL(inv, inv, den);
+        BA_SQR(t, x1); fp_dbl(u, t); fp_add(t, t, u);                   // 3 x1^2
+        BA_MUL(lam, t, dinv);
+        BA_SQR(t, lam); fp_sub(t, t, x1); fp_sub(t, t, x1);
+        fp_sub(u, x1, t); BA_MUL(u, lam, u); fp_sub(y3, u, y1);
+        x3 = t;
+    }
+    uint4* o = c.pts + (size_t)k * 6 * BA_THREADS;
+    ba_st(o, x3); ba_st(o + 3 * BA_THREADS, y3);
+    return inv;
 }
 
 __global__ void __launch_bounds__(BA_THREADS) k_msm_ba(BaArgs A) {
     __shared__ G1 sm[BA_THREADS / 2];
     __shared__ unsigned int s_item;
     const int tid = threadIdx.x;
-    const int nwin = A.tab.nwin, c = A.tab.c;
+    const int nwin = A.tab.nwin;
     const int NP = BA_UB * nwin, K1 = NP / 2;
     uint4* const pts = A.scr_pts + (size_t)blockIdx.x * K1 * 6 * BA_THREADS + tid;
     uint4* const pre = A.scr_pre + (size_t)blockIdx.x * K1 * 3 * BA_THREADS + tid;
-    (void)c;
     for (;;) {
         if (tid == 0) s_item = atomicAdd(A.counter, 1u);
         __syncthreads();
@@ -203,54 +239,62 @@ __global__ void __launch_bounds__(BA_THREADS) k_msm_ba(BaArgs A) {
         if (A.status == nullptr || A.status[item] == 0) {
 #pragma unroll 1
             for (int u = 0; u < BA_UNITS; u++) {
-                const uint32_t* dg = A.dig + ((size_t)item * BA_UNITS + u) * NP * BA_THREADS + tid;
-                const int base0 = u * BA_UB * BA_THREADS + tid;
-                auto ref = [&](int round, int idx) -> BaRef {
-                    BaRef r;
-                    if (round == 0) {
-                        uint32_t d = dg[(size_t)idx * BA_THREADS];
-                        r.zero = d == BA_ZERO; r.neg = (d >> 31) != 0;
-                        size_t e = (size_t)(d & 0x7fffffffu) * KB_N + (size_t)(base0 + (idx & (BA_UB - 1)) * BA_THREADS);
-                        r.p = A.tab.data + (r.zero ? 0 : e * 6); r.stride = 1;
-                    } else {
-                        r.zero = false; r.neg = false; r.p = pts + (size_t)idx * 6 * BA_THREADS; r.stride = BA_THREADS;
-                    }
-                    return r;
-                };
+                BaCtx C;
+                C.tab = A.tab.data; C.dg = A.dig + ((size_t)item * BA_UNITS + u) * NP * BA_THREADS + tid; C.pts = pts;
+                C.base0 = u * BA_UB * BA_THREADS + tid;
 #pragma unroll 1
-                for (int round = 0, K = K1; round < 3; round++, K >>= 1) {
-                    // forward: prefix products of the denominators
+                for (int round = 0, K = K1; round < BA_UB_LOG; round++, K >>= 1) {
+                    const bool tab = round == 0;
+                    // ---- forward: prefix products of the denominators.  Operands of pair k+1 are loaded before the
+                    // product of pair k is issued, the digits of pair k+2 before that.
                     Fp run; fp_set(run, c_k.fp_one);
+                    {
+                        uint32_t d1 = tab ? ba_digit(C, 0) : 0u, d2 = tab ? ba_digit(C, K) : 0u;
+                        BaRef r1 = ba_ref(C, round, 0, d1), r2 = ba_ref(C, round, K, d2);
+                        Fp nx1, nx2; ba_ldx(nx1, r1); ba_ldx(nx2, r2);
+                        d1 = (tab && K > 1) ? ba_digit(C, 1) : 0u; d2 = (tab && K > 1) ? ba_digit(C, 1 + K) : 0u;
 #pragma unroll 1
-                    for (int k = 0; k < K; k++) {
-                        BaRef r1 = ref(round, k), r2 = ref(round, k + K);
-                        Fp x1, x2, d;
-                        ba_ldx(x1, r1); ba_ldx(x2, r2);
-                        ba_st(pre + (size_t)k * 3 * BA_THREADS, run);
-                        fp_sub(d, x2, x1);
-                        if (fp_is_zero(x1) || fp_is_zero(x2) || fp_is_zero(d)) ba_rare_den(&d, &x1, &x2, &r1, &r2);
-                        BA_MUL(run, run, d);
+                        for (int k = 0; k < K; k++) {
+                            Fp x1 = nx1, x2 = nx2, d;
+                            if (k + 1 < K) {
+                                r1 = ba_ref(C, round, k + 1, d1); r2 = ba_ref(C, round, k + 1 + K, d2);
+                                ba_ldx(nx1, r1); ba_ldx(nx2, r2);
+                                if (tab && k + 2 < K) { d1 = ba_digit(C, k + 2); d2 = ba_digit(C, k + 2 + K); }
+                            }
+                            ba_st(pre + (size_t)k * 3 * BA_THREADS, run);
+                            fp_sub(d, x2, x1);
+                            if (fp_is_zero(x1) || fp_is_zero(x2) || fp_is_zero(d)) d = ba_rare_den(C, round, k, K);
+                            BA_MUL(run, run, d);
+                        }
                     }
                     Fp inv = ba_inv(run);
-                    // backward: the additions
+                    // ---- backward: the additions.  The table entries of pair k-1 are pulled into L2 while pair k is added.
+                    {
+                        uint32_t d1 = tab ? ba_digit(C, K - 1) : 0u, d2 = tab ? ba_digit(C, 2 * K - 1) : 0u;
 #pragma unroll 1
-                    for (int k = K - 1; k >= 0; k--) {
-                        BaRef r1 = ref(round, k), r2 = ref(round, k + K);
-                        Fp x1, y1, x2, y2, pk, d, x3, y3;
-                        ba_ldx(x1, r1); ba_ldy(y1, r1); ba_ldx(x2, r2); ba_ldy(y2, r2);
-                        ba_ld(pk, pre + (size_t)k * 3 * BA_THREADS, BA_THREADS);
-                        fp_sub(d, x2, x1);
-                        if (fp_is_zero(x1) || fp_is_zero(x2) || fp_is_zero(d)) {
-                            ba_rare_add(&x3, &y3, &inv, &pk, &x1, &y1, &x2, &y2);
-                        } else {
-                            Fp dinv, lam, t;
-                            BA_MUL(dinv, inv, pk); BA_MUL(inv, inv, d);
-                            fp_sub(t, y2, y1); BA_MUL(lam, t, dinv);
-                            BA_SQR(x3, lam); fp_sub(x3, x3, x1); fp_sub(x3, x3, x2);
-                            fp_sub(t, x1, x3); BA_MUL(t, lam, t); fp_sub(y3, t, y1);
+                        for (int k = K - 1; k >= 0; k--) {
+                            BaRef r1 = ba_ref(C, round, k, d1), r2 = ba_ref(C, round, k + K, d2);
+                            Fp x1, y1, x2, y2, pk, d;
+                            ba_ldx(x1, r1); ba_ldx(x2, r2);
+                            ba_ld(pk, pre + (size_t)k * 3 * BA_THREADS, BA_THREADS);
+                            ba_ldy(y1, r1); ba_ldy(y2, r2);
+                            if (tab && k > 0) {
+                                d1 = ba_digit(C, k - 1); d2 = ba_digit(C, k - 1 + K);
+                                ba_prefetch(ba_ref(C, 0, k - 1, d1)); ba_prefetch(ba_ref(C, 0, k - 1 + K, d2));
+                            }
+                            fp_sub(d, x2, x1);
+                            if (fp_is_zero(x1) || fp_is_zero(x2) || fp_is_zero(d)) {
+                                inv = ba_rare_add(C, round, k, K, inv, pk);
+                            } else {
+                                Fp dinv, lam, t, x3, y3;
+                                BA_MUL(dinv, inv, pk); BA_MUL(inv, inv, d);
+                                fp_sub(t, y2, y1); BA_MUL(lam, t, dinv);
+                                BA_SQR(x3, lam); fp_sub(x3, x3, x1); fp_sub(x3, x3, x2);
+                                fp_sub(t, x1, x3); BA_MUL(t, lam, t); fp_sub(y3, t, y1);
+                                uint4* o = pts + (size_t)k * 6 * BA_THREADS;
+                                ba_st(o, x3); ba_st(o + 3 * BA_THREADS, y3);
+                            }
                         }
-                        uint4* o = pts + (size_t)k * 6 * BA_THREADS;
-                        ba_st(o, x3); ba_st(o + 3 * BA_THREADS, y3);
                     }
                 }
                 // the W sums of this unit -> XYZZ accumulator
