@@ -6,12 +6,12 @@
 // SUMMED, so here they are first added pairwise in AFFINE coordinates, where an addition costs 1S + 2M once the
 // inverse of (x2 - x1) is known, and the inverses of a whole batch come from one shared inversion (3 products per
 // element for the prefix/suffix products + one binary-GCD inversion per batch, fp_bgcd.cuh: ~10 products' worth of
-// multiplier work).  Per thread and unit (8 bases x W windows = 8W gathered points):
-//     round 1: 4W pairs of table points        -> 4W affine sums
-//     round 2: 2W pairs of round-1 sums        -> 2W
-//     round 3:  W pairs                        ->  W
+// multiplier work, ~44k integer-ALU instructions).  A thread owns 32 bases x W windows = 32W gathered points and halves
+// them five times:
+//     round 1: 16W pairs of table points -> 16W affine sums;  rounds 2..5: 8W, 4W, 2W, W pairs of the previous sums;
 //     then W mixed additions into the thread's XYZZ accumulator,
-// i.e. (6*7W + 3*10 + 10*W) / 8W = 6.7 products per gathered point at W = 17 instead of 10.  The sums of a round live in
+// i.e. (6 * 31W + 10 * W) / 32W = 6.1 products per gathered point (+ 5 inversions per thread) instead of 10: 2.13e5
+// instead of 3.48e5 Fp products per 4096-point MSM at W = 17.  The sums of a round live in
 // a per-CTA scratch area in HBM, interleaved by thread so every access is a coalesced 512-byte warp transaction; the
 // table points are simply gathered twice (once for the denominators, once for the additions).
 // Exceptional pairs (an operand at infinity = zero digit, P == Q, P == -Q) are detected from the x coordinates in both
@@ -42,20 +42,42 @@ __device__ __noinline__ Fp fp_mulc(Fp a, Fp b) { Fp r; fp_mul(r, a, b); return r
 #define BA_MUL(r, a, b) r = fp_mulc(a, b)
 #define BA_SQR(r, a) r = fp_mulc(a, a)
 
-// g1_madd / g1_add (g1.cuh) on the shared product
-__device__ __noinline__ void ba_madd(G1& acc, const Fp& x2, const Fp& y2) {
+// g1_dbl_affine / g1_dbl / g1_madd / g1_add (g1.cuh) on the shared product.  All inlined into the kernel: nothing in
+// k_msm_ba passes a pointer to a local object to an out-of-line function, so every operand stays in registers.
+__device__ __forceinline__ void ba_dbl_affine(G1& r, const Fp& x, const Fp& y) {
+    Fp u, v, w, s, m, t;
+    fp_dbl(u, y); BA_SQR(v, u); BA_MUL(w, u, v); BA_MUL(s, x, v);
+    BA_SQR(m, x); fp_dbl(t, m); fp_add(m, m, t);
+    BA_SQR(r.x, m); fp_sub(r.x, r.x, s); fp_sub(r.x, r.x, s);
+    fp_sub(t, s, r.x); BA_MUL(t, m, t); BA_MUL(u, w, y); fp_sub(r.y, t, u);
+    r.zz = v; r.zzz = w;
+}
+__device__ __forceinline__ void ba_dbl(G1& p) {
+    if (g1_is_inf(p)) return;
+    Fp u, v, w, s, m, t;
+    fp_dbl(u, p.y); BA_SQR(v, u); BA_MUL(w, u, v); BA_MUL(s, p.x, v);
+    BA_SQR(m, p.x); fp_dbl(t, m); fp_add(m, m, t);
+    BA_MUL(t, w, p.y);
+    BA_SQR(p.x, m); fp_sub(p.x, p.x, s); fp_sub(p.x, p.x, s);
+    fp_sub(s, s, p.x); BA_MUL(s, m, s); fp_sub(p.y, s, t);
+    BA_MUL(p.zz, v, p.zz); BA_MUL(p.zzz, w, p.zzz);
+}
+__device__ __forceinline__ void ba_madd(G1& acc, const Fp& x2, const Fp& y2) {
     if (fp_is_zero(x2)) return;                                     // (0,0): nothing to add
     if (g1_is_inf(acc)) { acc.x = x2; acc.y = y2; fp_set(acc.zz, c_k.fp_one); fp_set(acc.zzz, c_k.fp_one); return; }
     Fp p, r, pp, ppp, q, t;
     BA_MUL(p, x2, acc.zz); fp_sub(p, p, acc.x);
     BA_MUL(r, y2, acc.zzz); fp_sub(r, r, acc.y);
-    if (fp_is_zero(p)) { G1 tmp = acc; g1_madd_rare(&tmp, &x2, &y2, fp_is_zero(r)); acc = tmp; return; }
+    if (fp_is_zero(p)) {
+        if (fp_is_zero(r)) ba_dbl_affine(acc, x2, y2); else g1_set_inf(acc);
+        return;
+    }
     BA_SQR(pp, p); BA_MUL(ppp, p, pp); BA_MUL(q, acc.x, pp);
     BA_SQR(t, r); fp_sub(t, t, ppp); fp_sub(t, t, q); fp_sub(acc.x, t, q);
     fp_sub(q, q, acc.x); BA_MUL(q, r, q); BA_MUL(t, acc.y, ppp); fp_sub(acc.y, q, t);
     BA_MUL(acc.zz, acc.zz, pp); BA_MUL(acc.zzz, acc.zzz, ppp);
 }
-__device__ __noinline__ void ba_add(G1& acc, const G1& b) {
+__device__ __forceinline__ void ba_add(G1& acc, const G1& b) {
     if (g1_is_inf(b)) return;
     if (g1_is_inf(acc)) { acc = b; return; }
     Fp u1, u2, s1, s2, p, r, pp, ppp, q, t;
@@ -63,7 +85,7 @@ __device__ __noinline__ void ba_add(G1& acc, const G1& b) {
     BA_MUL(s1, acc.y, b.zzz); BA_MUL(s2, b.y, acc.zzz);
     fp_sub(p, u2, u1); fp_sub(r, s2, s1);
     if (fp_is_zero(p)) {
-        if (fp_is_zero(r)) g1_dbl(acc); else g1_set_inf(acc);
+        if (fp_is_zero(r)) ba_dbl(acc); else g1_set_inf(acc);
         return;
     }
     BA_SQR(pp, p); BA_MUL(ppp, p, pp); BA_MUL(q, u1, pp);
@@ -221,7 +243,7 @@ __device__ __noinline__ Fp ba_rare_add(BaCtx c, int round, int k, int K, Fp inv,
     return inv;
 }
 
-__global__ void __launch_bounds__(BA_THREADS) k_msm_ba(BaArgs A) {
+__global__ void __launch_bounds__(BA_THREADS, 4) k_msm_ba(BaArgs A) {
     __shared__ G1 sm[BA_THREADS / 2];
     __shared__ unsigned int s_item;
     const int tid = threadIdx.x;
@@ -312,7 +334,7 @@ __global__ void __launch_bounds__(BA_THREADS) k_msm_ba(BaArgs A) {
         for (int stride = BA_THREADS / 2; stride >= 1; stride >>= 1) {
             if (tid >= stride && tid < 2 * stride) sm[tid - stride] = acc;
             __syncthreads();
-            if (tid < stride) ba_add(acc, sm[tid]);
+            if (tid < stride) { G1 other = sm[tid]; ba_add(acc, other); }
             __syncthreads();
         }
         if (tid == 0) A.partials[item] = acc;
