@@ -118,6 +118,8 @@ typedef struct {
     uint64_t kernel_launches;  /* kernels launched by this handle since load */
     int device, sm_count;
     double setup_seconds;
+    int last_msm_batch_affine; /* 1 when the most recent MSM ran as k_msm_ba (batch-affine), 0 for k_msm (XYZZ) */
+    int ba_grid;               /* persistent grid of k_msm_ba (resident CTAs) */
 } kb200_info;
 int kb200_get_info(kb200_setup* s, kb200_info* info);
 /* CUDA-event timing of the dominant kernel (the fixed-base MSM) for roofline reporting: switch on, run, read the summed

@@ -59,7 +59,7 @@ struct kb200_setup {
     DBuf blobs, c48, p48, zy32, out48, out32, st_blob, st_a, st_b, status, z, y, prod, indom, q, partials, aff_c, aff_p, rlc_part, rlc_s, rmont,
         records, combine, dig, scr_pts, scr_pre;
     // batch-affine MSM (msm_ba.cuh): 0 = automatic (batches that fill the GPU), 1 = always k_msm, 2 = always k_msm_ba
-    int msm_mode = 0, ba_grid = 0;
+    int msm_mode = 0, ba_grid = 0, last_ba = 0;
     unsigned int* d_counter = nullptr;
     BaOffset ba_off{};
     uint8_t last_lhs[48], last_rhs[48];
@@ -349,6 +349,7 @@ extern "C" int kb200_get_info(kb200_setup* s, kb200_info* info) {
     if (!s || !info) return KB200_E_ARG;
     info->window_bits = s->tab.c; info->windows = s->tab.nwin; info->table_bytes = s->table_bytes; info->kernel_launches = s->launches;
     info->device = s->device; info->sm_count = s->sm_count; info->setup_seconds = s->setup_seconds;
+    info->last_msm_batch_affine = s->last_ba; info->ba_grid = s->ba_grid;
     return 0;
 }
 
@@ -368,6 +369,7 @@ static int run_msm(kb200_setup* s, const uint32_t* d_scalars, size_t n, const in
     int S = pick_slices(s, n);
     const bool ba = s->msm_mode == 2 || (s->msm_mode == 0 && S == 1);
     if (ba) S = 1;
+    s->last_ba = ba ? 1 : 0;
     if (int rc = s->partials.ensure(n * S * sizeof(G1))) return rc;
     unsigned grid = 0;
     if (ba) {
