@@ -311,9 +311,17 @@ def main():
         kernel = "k_msm"
         executed_note = "executed = 4096 x windows x 3000 MAC32 (XYZZ mixed additions actually issued) per MSM; achieved = SURVEY 8d yardstick"
     gather_bytes = gather_per_msm * msms_per_launch
+    traffic = None
+    try:        # dram__bytes_read.sum + dram__bytes_write.sum of the committed ncu --set full capture, scaled to this launch
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r01_k_msm_ba_traffic.json")))
+        if ba:
+            traffic = tr["dram_bytes_per_msm"] * msms_per_launch
+    except Exception:
+        pass
     executed = mac_per_msm * msms_per_launch / (msm_ms * 1e-3) / 1e12 if msm_ms > 0 else 0.0
     roofline = {"bound": "imad", "achieved": achieved, "executed": executed, "executed_frac": executed / peak_wide if peak_wide else None, "peak": peak_wide, "unit": "TMAC32/s", "frac": achieved / peak_wide if peak_wide else None,
-                "traffic": None, "kernel": kernel, "launch_ms": msm_ms, "msms_per_launch": msms_per_launch, "share_of_step": prof["ms"] / r["ms_res"],
+                "traffic": traffic, "traffic_note": "DRAM bytes per launch: ncu capture of a 1184-MSM launch (profiles/r01_k_msm_ba_traffic.json) scaled by MSMs per launch; table gathers + per-CTA scratch of the affine rounds",
+                "kernel": kernel, "launch_ms": msm_ms, "msms_per_launch": msms_per_launch, "share_of_step": prof["ms"] / r["ms_res"],
                 "executed_mac32_per_msm": mac_per_msm,
                 "peak_source": "K0 measured in this run: max(IMAD.WIDE.U32.X carry chains %.2f, Fp-product chain %.2f) TMAC32/s; IMAD.WIDE issues at half the 32-bit IMAD rate on sm_100a; no integer peak in MEASURED_PEAKS.json" % (peak_chain, peak_fp),
                 "executed_note": executed_note,
