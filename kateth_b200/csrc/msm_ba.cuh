@@ -286,7 +286,7 @@ __global__ void __launch_bounds__(BA_THREADS, 4) k_msm_ba(BaArgs A) {
                             ba_st(pre + (size_t)k * 3 * BA_THREADS, run);
                             fp_sub(d, x2, x1);
                             if (fp_is_zero(x1) || fp_is_zero(x2) || fp_is_zero(d)) d = ba_rare_den(C, round, k, K);
-                            BA_MUL(run, run, d);
+                            fp_mul(run, run, d);      // inlined: the only product of this loop, so the loads of pair k+1 stay in flight across it
                         }
                     }
                     Fp inv = ba_inv(run);
