@@ -396,7 +396,7 @@ static int run_msm(kb200_setup* s, const uint32_t* d_scalars, size_t n, const in
         LAUNCH(s, (k_msm<FMT>), (unsigned)(n * S), MSM_THREADS, s->tab, d_scalars, d_status, s->partials.as<G1>(), S);
     }
     if (e1) CU(cudaEventRecord(e1, s->stream));
-    LAUNCH(s, k_msm_finish, blocks(n, 32), 32, s->partials.as<G1>(), S, (int)n, d_status, d_out48, (G1Affine*)nullptr);
+    LAUNCH(s, k_msm_finish, blocks(n, FIN_WARPS), 32 * FIN_WARPS, s->partials.as<G1>(), S, (int)n, d_status, d_out48, (G1Affine*)nullptr);
     return 0;
 }
 // evaluation (and optionally quotient) of n blobs at z (canonical limbs in s->z)

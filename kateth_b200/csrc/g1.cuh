@@ -8,6 +8,7 @@
 // Every addition handles P == Q, P == -Q and infinity, so the result is the unique group element blst returns.
 #pragma once
 #include "field.cuh"
+#include "fp_bgcd.cuh"
 
 namespace kb200 {
 
@@ -86,7 +87,7 @@ __device__ __noinline__ void g1_add(G1& acc, const G1& b) {
 __device__ __noinline__ void g1_to_affine(G1Affine& r, const G1& p) {
     if (g1_is_inf(p)) { fp_zero(r.x); fp_zero(r.y); return; }
     Fp i3, zi, i2;
-    fp_inv(i3, p.zzz);                       // Z^-3
+    fp_inv_bgcd(i3, p.zzz);                  // Z^-3 (branchless binary GCD, fp_bgcd.cuh; same value as a^(p-2))
     fp_mul(zi, p.zz, i3); fp_sqr(i2, zi);    // Z^-1, Z^-2
     fp_mul(r.x, p.x, i2); fp_mul(r.y, p.y, i3);
 }

@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(128) k_table_build(uint4* table, uint4* scratc
         fp_mul(pref, pref, z);
     }
     // backward
-    Fp inv; fp_inv(inv, pref);
+    Fp inv; fp_inv_bgcd(inv, pref);
     for (int d = nd; d >= 1; d--) {
         size_t e = (base_e + (size_t)(d - 1) * KB_N) * 6;
         G1Affine xy, zp; load_affine(xy, table + e); load_affine(zp, scratch + e);
@@ -172,24 +172,42 @@ __global__ void __launch_bounds__(MSM_THREADS) k_msm(MsmTable tab, const uint32_
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// Sum the S partials of each item, normalise (one inversion) and emit the 48-byte compressed point
+// Sum the S <= 32 partials of each item, normalise (one inversion) and emit the 48-byte compressed point
 // (Compress::compress, /root/reference/src/bls.rs:491-503).  Optionally also keeps the affine point.
+// One WARP per item: lane l holds partial l, five shuffle levels add them pairwise (the single-blob latency shape has
+// S = 32 partials; summing them one after the other on one thread cost half of the call), lane 0 normalises.
 // ---------------------------------------------------------------------------------------------------------
-__global__ void k_msm_finish(const G1* __restrict__ partials, int S, int n, const int32_t* __restrict__ status, uint32_t* __restrict__ out48,
-                             G1Affine* __restrict__ out_affine) {
-    int item = blockIdx.x * blockDim.x + threadIdx.x;
-    if (item >= n) return;
+#define FIN_WARPS 4
+__device__ __forceinline__ void g1_shfl_down(G1& r, const G1& v, int off) {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(&v);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(&r);
+#pragma unroll
+    for (int k = 0; k < 48; k++) dst[k] = __shfl_down_sync(0xffffffffu, src[k], off);
+}
+__global__ void __launch_bounds__(32 * FIN_WARPS) k_msm_finish(const G1* __restrict__ partials, int S, int n, const int32_t* __restrict__ status,
+                                                                uint32_t* __restrict__ out48, G1Affine* __restrict__ out_affine) {
+    const int item = blockIdx.x * FIN_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (item >= n) return;                                  // whole warp
     uint32_t* o = out48 + (size_t)item * 12;
     if (status != nullptr && status[item] != 0) {
-        for (int k = 0; k < 12; k++) o[k] = 0;
+        if (lane < 12) o[lane] = 0;
         return;
     }
-    G1 acc = partials[(size_t)item * S];
-    for (int k = 1; k < S; k++) { G1 t = partials[(size_t)item * S + k]; g1_add(acc, t); }
-    G1Affine a; g1_to_affine(a, acc);
-    if (out_affine) out_affine[item] = a;
-    uint32_t w[12]; g1_compress(w, a);
-    for (int k = 0; k < 12; k++) o[k] = w[k];
+    G1 acc;
+    if (lane < S) acc = partials[(size_t)item * S + lane]; else g1_set_inf(acc);
+    if (S > 1) {
+#pragma unroll 1
+        for (int off = 16; off >= 1; off >>= 1) {
+            G1 other; g1_shfl_down(other, acc, off);
+            if (lane < off && off < S) g1_add(acc, other);
+        }
+    }
+    if (lane == 0) {
+        G1Affine a; g1_to_affine(a, acc);
+        if (out_affine) out_affine[item] = a;
+        uint32_t w[12]; g1_compress(w, a);
+        for (int k = 0; k < 12; k++) o[k] = w[k];
+    }
 }
 
 }  // namespace kb200
