@@ -111,6 +111,13 @@ int kb200_verify_batch_finish_device(kb200_setup* s, const void* d_records, size
 /* The two compressed G1 operands of the final pairing check of the last finish call (for diffing intermediate sums). */
 int kb200_last_pairing_operands(kb200_setup* s, uint8_t lhs48[48], uint8_t rhs48[48]);
 
+/* ---- random challenge of the batch checks.  0 (default) = kateth's: r = SHA-256("RCKZGBATCH___V1_" | u128(4096) | u128(n))
+ *      mod r and weights [r, r, r^2, ...] (src/kzg/setup.rs:127-136, src/bls.rs:169-187) -- bit-for-bit parity with the reference.
+ *      1 = the consensus-spec verify_kzg_proof_batch transcript: r = hash_to_bls_field(domain | u64(4096) | u64(n) |
+ *      (commitment | z | y | proof) per item), weights [1, r, r^2, ...]; sound against adaptive inputs.  Verdicts agree on every
+ *      test vector.  In mode 1 a batch must be checked in one call (the sharded *_partial entry points return KB200_E_ARG). ---- */
+int kb200_set_batch_challenge(kb200_setup* s, int mode);
+
 /* ---- introspection ---- */
 typedef struct {
     int window_bits, windows;

@@ -60,6 +60,8 @@ struct kb200_setup {
         records, combine, dig, scr_pts, scr_pre;
     // batch-affine MSM (msm_ba.cuh): 0 = automatic (batches that fill the GPU), 1 = always k_msm, 2 = always k_msm_ba
     int msm_mode = 0, ba_grid = 0, last_ba = 0;
+    int challenge_mode = 0;          // batch-verification challenge: 0 = kateth's (parity with the reference), 1 = consensus-spec transcript
+    DBuf transcript;
     unsigned int* d_counter = nullptr;
     BaOffset ba_off{};
     uint8_t last_lhs[48], last_rhs[48];
@@ -318,12 +320,17 @@ extern "C" void kb200_setup_free(kb200_setup* s) {
     if (s->d_table) cudaFree(s->d_table);
     if (s->d_counter) cudaFree(s->d_counter);
     DBuf* bufs[] = {&s->blobs, &s->c48, &s->p48, &s->zy32, &s->out48, &s->out32, &s->st_blob, &s->st_a, &s->st_b, &s->status, &s->z, &s->y, &s->prod,
-                    &s->indom, &s->q, &s->partials, &s->aff_c, &s->aff_p, &s->rlc_part, &s->rlc_s, &s->rmont, &s->records, &s->combine, &s->dig, &s->scr_pts, &s->scr_pre};
+                    &s->indom, &s->q, &s->partials, &s->aff_c, &s->aff_p, &s->rlc_part, &s->rlc_s, &s->rmont, &s->records, &s->combine, &s->dig, &s->scr_pts, &s->scr_pre, &s->transcript};
     for (DBuf* b : bufs) b->release();
     for (cudaEvent_t e : s->prof_ev) cudaEventDestroy(e);
     delete s;
 }
 extern "C" int kb200_set_stream(kb200_setup* s, void* stream) { if (!s) return KB200_E_ARG; s->stream = (cudaStream_t)stream; return 0; }
+extern "C" int kb200_set_batch_challenge(kb200_setup* s, int mode) {
+    if (!s || mode < 0 || mode > 1) return KB200_E_ARG;
+    s->challenge_mode = mode;
+    return 0;
+}
 extern "C" int kb200_set_msm_mode(kb200_setup* s, int mode) {
     if (!s || mode < 0 || mode > 2) return KB200_E_ARG;
     s->msm_mode = mode;
@@ -494,14 +501,78 @@ extern "C" int kb200_compute_proof_device(kb200_setup* s, const void* d_blobs, c
 
 // ---- verification ----
 // RLC partial over n items whose affine proofs/commitments are in s->aff_p / s->aff_c and z, y in s->z / s->y.
-static int run_rlc(kb200_setup* s, size_t n, size_t index_offset, size_t n_total, int raw, RlcRecord* d_record) {
+// host SHA-256 (only for the optional consensus-spec batch challenge: one sequential hash over the whole transcript)
+static void host_sha256(const uint8_t* data, size_t len, uint8_t out[32]) {
+    static const uint32_t Kc[64] = {
+        0x428a2f98, 0x71374491, 0xb5c0fbcf, 0xe9b5dba5, 0x3956c25b, 0x59f111f1, 0x923f82a4, 0xab1c5ed5, 0xd807aa98, 0x12835b01, 0x243185be, 0x550c7dc3,
+        0x72be5d74, 0x80deb1fe, 0x9bdc06a7, 0xc19bf174, 0xe49b69c1, 0xefbe4786, 0x0fc19dc6, 0x240ca1cc, 0x2de92c6f, 0x4a7484aa, 0x5cb0a9dc, 0x76f988da,
+        0x983e5152, 0xa831c66d, 0xb00327c8, 0xbf597fc7, 0xc6e00bf3, 0xd5a79147, 0x06ca6351, 0x14292967, 0x27b70a85, 0x2e1b2138, 0x4d2c6dfc, 0x53380d13,
+        0x650a7354, 0x766a0abb, 0x81c2c92e, 0x92722c85, 0xa2bfe8a1, 0xa81a664b, 0xc24b8b70, 0xc76c51a3, 0xd192e819, 0xd6990624, 0xf40e3585, 0x106aa070,
+        0x19a4c116, 0x1e376c08, 0x2748774c, 0x34b0bcb5, 0x391c0cb3, 0x4ed8aa4a, 0x5b9cca4f, 0x682e6ff3, 0x748f82ee, 0x78a5636f, 0x84c87814, 0x8cc70208,
+        0x90befffa, 0xa4506ceb, 0xbef9a3f7, 0xc67178f2};
+    uint32_t h[8] = {0x6a09e667, 0xbb67ae85, 0x3c6ef372, 0xa54ff53a, 0x510e527f, 0x9b05688c, 0x1f83d9ab, 0x5be0cd19};
+    auto rotr = [](uint32_t x, int k) { return (x >> k) | (x << (32 - k)); };
+    auto block = [&](const uint8_t* b) {
+        uint32_t w[64];
+        for (int i = 0; i < 16; i++) w[i] = (uint32_t)b[4 * i] << 24 | (uint32_t)b[4 * i + 1] << 16 | (uint32_t)b[4 * i + 2] << 8 | b[4 * i + 3];
+        for (int i = 16; i < 64; i++) {
+            uint32_t s0 = rotr(w[i - 15], 7) ^ rotr(w[i - 15], 18) ^ (w[i - 15] >> 3), s1 = rotr(w[i - 2], 17) ^ rotr(w[i - 2], 19) ^ (w[i - 2] >> 10);
+            w[i] = w[i - 16] + s0 + w[i - 7] + s1;
+        }
+        uint32_t a = h[0], bb = h[1], c = h[2], d = h[3], e = h[4], f = h[5], g = h[6], hh = h[7];
+        for (int i = 0; i < 64; i++) {
+            uint32_t t1 = hh + (rotr(e, 6) ^ rotr(e, 11) ^ rotr(e, 25)) + ((e & f) ^ (~e & g)) + Kc[i] + w[i];
+            uint32_t t2 = (rotr(a, 2) ^ rotr(a, 13) ^ rotr(a, 22)) + ((a & bb) ^ (a & c) ^ (bb & c));
+            hh = g; g = f; f = e; e = d + t1; d = c; c = bb; bb = a; a = t1 + t2;
+        }
+        h[0] += a; h[1] += bb; h[2] += c; h[3] += d; h[4] += e; h[5] += f; h[6] += g; h[7] += hh;
+    };
+    size_t off = 0;
+    for (; off + 64 <= len; off += 64) block(data + off);
+    uint8_t tail[128] = {0};
+    size_t rem = len - off;
+    memcpy(tail, data + off, rem);
+    tail[rem] = 0x80;
+    size_t tl = (rem < 56) ? 64 : 128;
+    uint64_t bits = (uint64_t)len * 8;
+    for (int i = 0; i < 8; i++) tail[tl - 1 - i] = (uint8_t)(bits >> (8 * i));
+    block(tail);
+    if (tl == 128) block(tail + 64);
+    for (int i = 0; i < 8; i++) { out[4 * i] = h[i] >> 24; out[4 * i + 1] = h[i] >> 16; out[4 * i + 2] = h[i] >> 8; out[4 * i + 3] = h[i]; }
+}
+
+// RLC sums of a shard.  d_c48 / d_p48 (the compressed inputs, device) are only read in consensus-spec challenge mode.
+static int run_rlc(kb200_setup* s, size_t n, size_t index_offset, size_t n_total, int raw, RlcRecord* d_record, const uint32_t* d_c48 = nullptr,
+                   const uint32_t* d_p48 = nullptr) {
     int nb = blocks(n, RLC_THREADS);
     if (int rc = s->rlc_part.ensure((size_t)3 * nb * sizeof(G1))) return rc;
     if (int rc = s->rlc_s.ensure((size_t)nb * sizeof(Fr))) return rc;
     if (int rc = s->rmont.ensure(sizeof(Fr))) return rc;
-    if (!raw) LAUNCH(s, k_batch_r, 1, 1, (uint32_t)n_total, s->rmont.as<Fr>());
+    const int spec = (!raw && s->challenge_mode == 1) ? 1 : 0;
+    if (spec) {
+        // r = hash_to_bls_field(domain | u64(4096) | u64(n) | sum(commitment | z | y | proof)): needs the whole batch in one place
+        if (n != n_total || index_offset != 0 || !d_c48 || !d_p48) {
+            snprintf(g_err, sizeof g_err, "consensus-spec batch challenge: the batch must be verified in one call (no shards)");
+            return KB200_E_ARG;
+        }
+        if (int rc = s->transcript.ensure(n * 160 + 32)) return rc;
+        LAUNCH(s, k_transcript, blocks(n, 128), 128, d_c48, d_p48, s->z.as<Fr>(), s->y.as<Fr>(), (int)n, s->transcript.as<uint32_t>());
+        std::vector<uint8_t> t(32 + n * 160);
+        memcpy(t.data(), "RCKZGBATCH___V1_", 16);
+        for (int i = 0; i < 8; i++) { t[16 + i] = (uint8_t)((uint64_t)KB_N >> (8 * (7 - i))); t[24 + i] = (uint8_t)((uint64_t)n >> (8 * (7 - i))); }
+        CU(cudaMemcpyAsync(t.data() + 32, s->transcript.p, n * 160, cudaMemcpyDeviceToHost, s->stream));
+        CU(cudaStreamSynchronize(s->stream));
+        uint8_t dg[32]; host_sha256(t.data(), t.size(), dg);
+        uint32_t plain[8];
+        for (int k = 0; k < 8; k++) plain[7 - k] = (uint32_t)dg[4 * k] << 24 | (uint32_t)dg[4 * k + 1] << 16 | (uint32_t)dg[4 * k + 2] << 8 | dg[4 * k + 3];
+        uint32_t* d_plain = s->transcript.as<uint32_t>();           // reuse the head of the transcript buffer
+        CU(cudaMemcpyAsync(d_plain, plain, 32, cudaMemcpyHostToDevice, s->stream));
+        LAUNCH(s, k_set_r, 1, 1, d_plain, s->rmont.as<Fr>());
+    } else if (!raw) {
+        LAUNCH(s, k_batch_r, 1, 1, (uint32_t)n_total, s->rmont.as<Fr>());
+    }
     LAUNCH(s, k_rlc, dim3(nb, 3), RLC_THREADS, s->aff_p.as<G1Affine>(), s->aff_c.as<G1Affine>(), s->z.as<Fr>(), s->y.as<Fr>(), (int)n, (uint32_t)index_offset,
-           s->rmont.as<Fr>(), raw, s->rlc_part.as<G1>(), s->rlc_s.as<Fr>());
+           s->rmont.as<Fr>(), raw, spec, s->rlc_part.as<G1>(), s->rlc_s.as<Fr>());
     LAUNCH(s, k_rlc_finish, 3, RLC_FIN_THREADS, s->rlc_part.as<G1>(), s->rlc_s.as<Fr>(), nb, d_record);
     return 0;
 }
@@ -569,7 +640,7 @@ extern "C" int kb200_verify_blob_proof_batch_partial_device(kb200_setup* s, cons
     int err = 0;
     if (n) { err = verify_prepare(s, (const uint32_t*)d_blobs, (const uint32_t*)d_c48, (const uint32_t*)d_p48, n, d_status); if (err < 0) return err; }
     else { if (int rc = s->aff_c.ensure(16)) return rc; if (int rc = s->aff_p.ensure(16)) return rc; if (int rc = s->z.ensure(32)) return rc; if (int rc = s->y.ensure(32)) return rc; }
-    if (int rc = run_rlc(s, n, index_offset, n_total, 0, (RlcRecord*)d_record)) return rc;
+    if (int rc = run_rlc(s, n, index_offset, n_total, 0, (RlcRecord*)d_record, (const uint32_t*)d_c48, (const uint32_t*)d_p48)) return rc;
     CU(cudaStreamSynchronize(s->stream));
     CU(cudaGetLastError());
     return err;
@@ -738,7 +809,7 @@ static int verify_points(kb200_setup* s, const uint8_t* proofs48, const uint8_t*
     if (status) for (size_t i = 0; i < n; i++) status[i] = h[0][i] ? h[0][i] : h[1][i] ? h[1][i] : h[2][i] ? h[2][i] : h[3][i];
     for (int k = 0; k < 4; k++) if (int e = first_nonzero(h[k])) return e;
     if (int rc = s->records.ensure(sizeof(RlcRecord))) return rc;
-    if (int rc = run_rlc(s, n, 0, n, raw, s->records.as<RlcRecord>())) return rc;
+    if (int rc = run_rlc(s, n, 0, n, raw, s->records.as<RlcRecord>(), s->c48.as<uint32_t>(), s->p48.as<uint32_t>())) return rc;
     return finish_records(s, s->records.as<RlcRecord>(), 1, ok);
 }
 extern "C" int kb200_verify_proof(kb200_setup* s, const uint8_t proof48[48], const uint8_t comm48[48], const uint8_t z32[32], const uint8_t y32[32], int* ok) {

@@ -57,13 +57,35 @@ __global__ void k_batch_r(uint32_t n_total, Fr* r_mont) {
     *r_mont = m;
 }
 
+// Consensus-spec batch challenge (optional mode): the transcript of verify_kzg_proof_batch is
+// domain | u64(4096) | u64(n) | (commitment | z | y | proof) per item; this kernel lays out the per-item part (160 bytes
+// each) from the compressed points and the canonical scalars; the host hashes it (one sequential SHA-256).
+__global__ void k_transcript(const uint32_t* __restrict__ c48, const uint32_t* __restrict__ p48, const Fr* __restrict__ z_canon,
+                             const Fr* __restrict__ y_canon, int n, uint32_t* __restrict__ out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t* o = out + (size_t)i * 40;
+    for (int k = 0; k < 12; k++) o[k] = c48[(size_t)i * 12 + k];
+    Fr z = z_canon[i], y = y_canon[i];
+    fr_store_be(o + 12, z); fr_store_be(o + 20, y);
+    for (int k = 0; k < 12; k++) o[28 + k] = p48[(size_t)i * 12 + k];
+}
+// r given as 8 plain little-endian limbs (already < 2^256; reduced here) -> Montgomery
+__global__ void k_set_r(const uint32_t* plain, Fr* r_mont) {
+    Fr v;
+    for (int k = 0; k < 8; k++) v.l[k] = plain[k];
+    fr_reduce_256(v);
+    Fr m; fr_to_mont(m, v);
+    *r_mont = m;
+}
+
 #define RLC_THREADS 64
 // grid (ceil(n/RLC_THREADS), 3).  which = blockIdx.y: 0 -> w_i*pi_i, 1 -> (w_i z_i)*pi_i, 2 -> w_i*C_i.
 // raw != 0: weights are 1 (single-proof check, src/kzg/setup.rs:84-94 rearranged to avoid the G2 scalar mul:
 //   e(pi, [tau]_2) == e(C - y G1 + z pi, G2)).
 __global__ void __launch_bounds__(RLC_THREADS) k_rlc(const G1Affine* __restrict__ proofs, const G1Affine* __restrict__ comms,
                                                       const Fr* __restrict__ z_canon, const Fr* __restrict__ y_canon, int n, uint32_t index_offset,
-                                                      const Fr* __restrict__ r_mont, int raw, G1* __restrict__ partials, Fr* __restrict__ s_partials) {
+                                                      const Fr* __restrict__ r_mont, int raw, int spec, G1* __restrict__ partials, Fr* __restrict__ s_partials) {
     __shared__ G1 sm[RLC_THREADS / 2];
     __shared__ Fr sms[RLC_THREADS];
     const int tid = threadIdx.x, which = blockIdx.y;
@@ -76,7 +98,7 @@ __global__ void __launch_bounds__(RLC_THREADS) k_rlc(const G1Affine* __restrict_
         else {
             uint32_t gi = index_offset + (uint32_t)i;
             Fr r = *r_mont;
-            fr_pow_u32(wgt, r, gi == 0 ? 1u : gi);     // Fr::pow(r, 0) == r quirk
+            fr_pow_u32(wgt, r, (gi == 0 && !spec) ? 1u : gi);     // Fr::pow(r, 0) == r quirk (kateth); r^0 = 1 in spec mode
         }
         Fr k;      // canonical scalar
         if (which == 1) { Fr z = z_canon[i]; fr_mul(k, z, wgt); }

@@ -40,7 +40,7 @@ SYMBOLS = [
     "kb200_blob_to_commitment", "kb200_blob_to_commitment_device", "kb200_compute_blob_proof", "kb200_compute_blob_proof_device",
     "kb200_compute_proof", "kb200_compute_proof_device", "kb200_verify_proof", "kb200_verify_proof_batch", "kb200_verify_blob_proof",
     "kb200_verify_blob_proof_batch", "kb200_verify_blob_proof_batch_device", "kb200_verify_blob_proof_batch_partial_device",
-    "kb200_verify_blob_proof_batch_partial", "kb200_verify_batch_finish_device", "kb200_set_profiling", "kb200_set_msm_mode", "kb200_get_msm_profile", "kb200_last_pairing_operands", "kb200_get_info", "kb200_test_fp_mul", "kb200_test_fr_mul",
+    "kb200_verify_blob_proof_batch_partial", "kb200_verify_batch_finish_device", "kb200_set_profiling", "kb200_set_msm_mode", "kb200_set_batch_challenge", "kb200_get_msm_profile", "kb200_last_pairing_operands", "kb200_get_info", "kb200_test_fp_mul", "kb200_test_fr_mul",
     "kb200_test_g1_decompress", "kb200_test_mac_peak", "kb200_test_host_pairing",
 ]
 
@@ -236,6 +236,10 @@ class Setup:
     def set_msm_mode(self, mode):
         """0 = automatic, 1 = XYZZ accumulation (k_msm), 2 = batch-affine summation (k_msm_ba); same bytes either way."""
         _check(lib().kb200_set_msm_mode(self._h, int(mode)))
+
+    def set_batch_challenge(self, mode):
+        """0 = kateth's batch challenge (default, parity with the reference), 1 = consensus-spec transcript challenge."""
+        _check(lib().kb200_set_batch_challenge(self._h, int(mode)))
 
     def set_profiling(self, on=True):
         _check(lib().kb200_set_profiling(self._h, 1 if on else 0))

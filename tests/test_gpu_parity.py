@@ -327,3 +327,41 @@ def test_degenerate_setup_exercises_exceptional_additions(mode, tmp_path):
             assert comm[48 * i:48 * i + 48] == o.blob_to_commitment(b), i
     finally:
         s.close()
+
+
+# ---------------------------------------------------------------- optional consensus-spec batch challenge
+def test_consensus_spec_batch_challenge(engine_setup, oracle_setup):
+    """Mode 1 of kb200_set_batch_challenge: r comes from the verify_kzg_proof_batch transcript and the weights are
+    [1, r, r^2, ...].  The left pairing operand sum r^i * proof_i is recomputed here from hashlib + the oracle's G1."""
+    from oracle import oracle as O
+    s = engine_setup
+    n = 5
+    blobs = [rand_blob(4200 + i) for i in range(n)]
+    cat = b"".join(blobs)
+    comm, _ = s.blob_to_commitment_many(cat, n)
+    proofs, _ = s.blob_proof_many(cat, comm, n)
+    cs = [comm[48 * i:48 * i + 48] for i in range(n)]
+    ps = [proofs[48 * i:48 * i + 48] for i in range(n)]
+    s.set_batch_challenge(1)
+    try:
+        assert s.verify_blob_proof_batch(blobs, cs, ps) is True
+        lhs, _ = s.last_pairing_operands()
+        zy = [oracle_setup.challenge_eval(blobs[i], cs[i]) for i in range(n)]
+        data = b"RCKZGBATCH___V1_" + (4096).to_bytes(8, "big") + n.to_bytes(8, "big")
+        data += b"".join(cs[i] + zy[i][0] + zy[i][1] + ps[i] for i in range(n))
+        r = int.from_bytes(hashlib.sha256(data).digest(), "big") % R
+        assert lhs == O.g1_lincomb(ps, [pow(r, i, R).to_bytes(32, "big") for i in range(n)])
+        # a wrong proof is still rejected, the vectors' verdicts do not change, shards are refused
+        assert s.verify_blob_proof_batch(blobs, cs, [ps[1]] + ps[1:]) is False
+        assert s.verify_blob_proof_batch([], [], []) is True
+        zs, ys = b"".join(z for z, _ in zy), b"".join(y for _, y in zy)
+        assert s.verify_proof_batch(proofs, comm, zs, ys, n) is True
+        import torch
+        d = lambda b: torch.frombuffer(bytearray(b), dtype=torch.uint8).cuda()
+        db, dc, dp = d(cat), d(comm), d(proofs)
+        rec = torch.zeros(320, dtype=torch.uint8, device="cuda"); st = torch.zeros(n, dtype=torch.int32, device="cuda")
+        assert s.verify_partial_device(db.data_ptr(), dc.data_ptr(), dp.data_ptr(), 2, 0, n, rec.data_ptr(), st.data_ptr()) == -20
+    finally:
+        s.set_batch_challenge(0)
+    assert s.verify_blob_proof_batch(blobs, cs, ps) is True
+    assert s.last_pairing_operands() == oracle_setup.verify_blob_proof_batch_sums(blobs, cs, ps)
