@@ -365,3 +365,35 @@ def test_consensus_spec_batch_challenge(engine_setup, oracle_setup):
         s.set_batch_challenge(0)
     assert s.verify_blob_proof_batch(blobs, cs, ps) is True
     assert s.last_pairing_operands() == oracle_setup.verify_blob_proof_batch_sums(blobs, cs, ps)
+
+
+# ---------------------------------------------------------------- the batch-affine shape at its own batch size
+def test_batch_affine_at_scale_with_bad_items(engine_setup, oracle_setup):
+    """n >= 592 selects k_msm_ba on its own (automatic mode): persistent CTAs pull several blobs each, items with a non-zero
+    status are skipped by the recoder and by the MSM, every other output is unaffected (idempotence over copies + oracle)."""
+    import kateth_b200 as K
+    from oracle import oracle as O
+    n = 700
+    base = [rand_blob(5000 + i) for i in range(4)] + [bytes(131072), b"".join(RV.fe(R - 1) for _ in range(4096))]
+    blobs = [base[i % len(base)] for i in range(n)]
+    bad_at = [0, 17, 599, 699]
+    for i in bad_at:
+        b = bytearray(blobs[i]); b[32 * (i % 4096):32 * (i % 4096) + 32] = RV.be32(R + i); blobs[i] = bytes(b)
+    cat = b"".join(blobs)
+    engine_setup.set_msm_mode(0)
+    comm, st = engine_setup.blob_to_commitment_many(cat, n)
+    assert engine_setup.info()["last_msm_batch_affine"] == 1
+    assert [i for i in range(n) if st[i] != 0] == bad_at and all(st[i] == 2 for i in bad_at)
+    want = [oracle_setup.blob_to_commitment(b) for b in base]
+    for i in range(n):
+        if i not in bad_at:
+            assert comm[48 * i:48 * i + 48] == want[i % len(base)], i
+    # proofs over the good items (quotient scalars, FMT 1 recoding)
+    good = [i for i in range(n) if i not in bad_at][:640]
+    gcat = b"".join(blobs[i] for i in good); gcomm = b"".join(comm[48 * i:48 * i + 48] for i in good)
+    proofs, st2 = engine_setup.blob_proof_many(gcat, gcomm, len(good))
+    assert engine_setup.info()["last_msm_batch_affine"] == 1 and st2 == [0] * len(good)
+    wantp = [oracle_setup.blob_proof(b, c) for b, c in zip(base, want)]
+    for k, i in enumerate(good):
+        assert proofs[48 * k:48 * k + 48] == wantp[i % len(base)], i
+    assert engine_setup.verify_blob_proof_batch_concat(gcat, gcomm, proofs, len(good)) is True
