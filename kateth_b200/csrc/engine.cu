@@ -63,6 +63,8 @@ struct kb200_setup {
     int challenge_mode = 0;          // batch-verification challenge: 0 = kateth's (parity with the reference), 1 = consensus-spec transcript
     DBuf transcript;
     unsigned int* d_counter = nullptr;
+    cudaStream_t aux_stream = nullptr;      // independent light kernels of one call run beside each other (verify_prepare)
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     BaOffset ba_off{};
     uint8_t last_lhs[48], last_rhs[48];
     bool have_last = false;
@@ -274,6 +276,9 @@ static int build_setup(kb200_setup* s, const uint8_t* g1, const uint8_t* g2, int
         if (occ < 1) occ = 1;
         s->ba_grid = occ * s->sm_count;
         CU(cudaMalloc(&s->d_counter, sizeof(unsigned int)));
+        CU(cudaStreamCreateWithFlags(&s->aux_stream, cudaStreamNonBlocking));
+        CU(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&s->ev_join, cudaEventDisableTiming));
         if (const char* e = getenv("KB200_MSM_MODE")) { int m = atoi(e); if (m >= 0 && m <= 2) s->msm_mode = m; }
     }
     s->table_bytes = bytes;
@@ -319,6 +324,9 @@ extern "C" void kb200_setup_free(kb200_setup* s) {
     if (s->d_neg_g_pow) cudaFree(s->d_neg_g_pow);
     if (s->d_table) cudaFree(s->d_table);
     if (s->d_counter) cudaFree(s->d_counter);
+    if (s->aux_stream) cudaStreamDestroy(s->aux_stream);
+    if (s->ev_fork) cudaEventDestroy(s->ev_fork);
+    if (s->ev_join) cudaEventDestroy(s->ev_join);
     DBuf* bufs[] = {&s->blobs, &s->c48, &s->p48, &s->zy32, &s->out48, &s->out32, &s->st_blob, &s->st_a, &s->st_b, &s->status, &s->z, &s->y, &s->prod,
                     &s->indom, &s->q, &s->partials, &s->aff_c, &s->aff_p, &s->rlc_part, &s->rlc_s, &s->rmont, &s->records, &s->combine, &s->dig, &s->scr_pts, &s->scr_pre, &s->transcript};
     for (DBuf* b : bufs) b->release();
@@ -544,7 +552,7 @@ static void host_sha256(const uint8_t* data, size_t len, uint8_t out[32]) {
 // RLC sums of a shard.  d_c48 / d_p48 (the compressed inputs, device) are only read in consensus-spec challenge mode.
 static int run_rlc(kb200_setup* s, size_t n, size_t index_offset, size_t n_total, int raw, RlcRecord* d_record, const uint32_t* d_c48 = nullptr,
                    const uint32_t* d_p48 = nullptr) {
-    int nb = blocks(n, RLC_THREADS);
+    int nb = blocks(2 * n, RLC_THREADS);          // two threads per term (GLV halves)
     if (int rc = s->rlc_part.ensure((size_t)3 * nb * sizeof(G1))) return rc;
     if (int rc = s->rlc_s.ensure((size_t)nb * sizeof(Fr))) return rc;
     if (int rc = s->rmont.ensure(sizeof(Fr))) return rc;
@@ -619,11 +627,19 @@ static int verify_prepare(kb200_setup* s, const uint32_t* d_blobs, const uint32_
     CU(cudaMemsetAsync(s->st_blob.p, 0, n * 4, s->stream));
     CU(cudaMemsetAsync(s->st_a.p, 0, n * 4, s->stream));
     CU(cudaMemsetAsync(s->st_b.p, 0, n * 4, s->stream));
+    // Two latency-bound kernels that do not depend on each other run side by side: the point decompression (a 380-step
+    // square-and-multiply chain per point) on the auxiliary stream, the blob check and the serial SHA-256 of each blob on the
+    // main one.  The challenge only needs the blob's own status; items with a bad point are dropped after the join.
+    CU(cudaEventRecord(s->ev_fork, s->stream));
+    CU(cudaStreamWaitEvent(s->aux_stream, s->ev_fork, 0));
+    k_g1_decompress<<<blocks(2 * n, 64), 64, 0, s->aux_stream>>>(d_c48, d_p48, (int)n, s->aff_c.as<G1Affine>(), s->aff_p.as<G1Affine>(),
+                                                                  s->st_a.as<int32_t>(), s->st_b.as<int32_t>(), 0);
+    s->launches++;
+    CU(cudaEventRecord(s->ev_join, s->aux_stream));
     LAUNCH(s, k_blob_check, blocks(n * KB_N, 256), 256, d_blobs, (int)n, s->st_blob.as<int32_t>());
-    LAUNCH(s, k_g1_decompress, blocks(2 * n, 64), 64, d_c48, d_p48, (int)n, s->aff_c.as<G1Affine>(), s->aff_p.as<G1Affine>(), s->st_a.as<int32_t>(),
-           s->st_b.as<int32_t>(), 0);
+    LAUNCH(s, k_challenge, blocks(n, 32), 32, d_blobs, d_c48, (int)n, s->st_blob.as<int32_t>(), s->z.as<Fr>());
+    CU(cudaStreamWaitEvent(s->stream, s->ev_join, 0));
     LAUNCH(s, k_merge_status, blocks(n, 256), 256, s->st_blob.as<int32_t>(), s->st_a.as<int32_t>(), s->st_b.as<int32_t>(), (int)n, d_status);
-    LAUNCH(s, k_challenge, blocks(n, 32), 32, d_blobs, d_c48, (int)n, d_status, s->z.as<Fr>());
     if (int rc = run_eval<false>(s, d_blobs, n, d_status)) return rc;
     std::vector<int32_t> h0, h1, h2;
     if (int rc = fetch_status(s, s->st_blob.as<int32_t>(), n, h0)) return rc;

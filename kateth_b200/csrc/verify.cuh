@@ -89,7 +89,10 @@ __global__ void __launch_bounds__(RLC_THREADS) k_rlc(const G1Affine* __restrict_
     __shared__ G1 sm[RLC_THREADS / 2];
     __shared__ Fr sms[RLC_THREADS];
     const int tid = threadIdx.x, which = blockIdx.y;
-    const int i = blockIdx.x * RLC_THREADS + tid;
+    // two threads per term: the scalar is split along the endomorphism (fr_glv_split) and each thread runs a 128-bit
+    // double-and-add; the halves need no recombination because everything is summed anyway.
+    const int t = blockIdx.x * RLC_THREADS + tid;
+    const int i = t >> 1, half = t & 1;
     G1 acc; g1_set_inf(acc);
     Fr s; fr_zero(s);
     if (i < n) {
@@ -104,8 +107,12 @@ __global__ void __launch_bounds__(RLC_THREADS) k_rlc(const G1Affine* __restrict_
         if (which == 1) { Fr z = z_canon[i]; fr_mul(k, z, wgt); }
         else fr_from_mont(k, wgt);
         G1Affine p = (which == 2) ? comms[i] : proofs[i];
-        g1_mul(acc, p, k);
-        if (which == 0) { Fr y = y_canon[i]; fr_mul(s, y, wgt); }
+        Fr k1, k2; fr_glv_split(k1, k2, k);
+        if (half) {
+            if (!g1a_is_inf(p)) { Fp b; fp_set(b, c_k.fp_beta); fp_mul(p.x, p.x, b); fp_neg(p.y, p.y); }      // Q = (beta x, -y)
+            k1 = k2;
+        } else if (which == 0) { Fr y = y_canon[i]; fr_mul(s, y, wgt); }
+        g1_mul(acc, p, k1, 128);          // ONE call site: the two halves of a warp must not serialise their scalar multiplications
     }
 #pragma unroll 1
     for (int stride = RLC_THREADS / 2; stride >= 1; stride >>= 1) {
