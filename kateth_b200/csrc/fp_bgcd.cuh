@@ -147,8 +147,17 @@ KB_HD int bg_inverse(uint32_t (&out)[12], const uint32_t (&x)[12]) {
         uint32_t nu[12], nv[12];
         bg_update_uv(nu, u, v, f0, g0);
         bg_update_uv(nv, u, v, f1, g1);
+        uint32_t anz = 0;
 #pragma unroll
-        for (int i = 0; i < 12; i++) { a[i] = na[i]; b[i] = nb[i]; u[i] = nu[i]; v[i] = nv[i]; }
+        for (int i = 0; i < 12; i++) { a[i] = na[i]; b[i] = nb[i]; u[i] = nu[i]; v[i] = nv[i]; anz |= na[i]; }
+        // Once a == 0 every further iteration is the identity on (b, v) (the matrix is ((1, 0), (0, 2^30)) and the update divides
+        // by 2^30), so the loop may stop as soon as every lane of the warp is there: 17-20 iterations for random inputs
+        // instead of the worst-case 26.
+#if defined(__CUDA_ARCH__)
+        if (!__any_sync(__activemask(), anz != 0u)) break;
+#else
+        if (anz == 0u) break;
+#endif
     }
     uint32_t rest = b[0] ^ 1u;
 #pragma unroll
