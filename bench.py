@@ -241,6 +241,20 @@ def run_engine(args):
     # ---- end-to-end arm (host buffers)
     e2e_steps = max(1, min(args.steps, args.e2e_steps))
     ms_e2e = timed(step_e2e, e2e_steps, 1)
+    # config 4's second run: one corrupted proof (rank 0, item 1 gets item 0's proof) must flip the verdict of the
+    # whole sharded batch on every rank.  Untimed.
+    d_bad = d_proof.clone()
+    if rank == 0 and n > 1:
+        d_bad[48:96] = d_proof[0:48]
+    check(s.verify_partial_device(d_blobs.data_ptr(), d_comm.data_ptr(), d_bad.data_ptr(), n, rank * n, world * n, d_rec.data_ptr(), d_status.data_ptr()),
+          "verify_blob_proof_batch(partial, corrupted)")
+    if world > 1:
+        dist.all_gather_into_tensor(d_all, d_rec)
+        corrupted_verdict = s.verify_finish_device(d_all.data_ptr(), world)
+    else:
+        corrupted_verdict = s.verify_finish_device(d_rec.data_ptr(), 1)
+    if corrupted_verdict is not False:
+        raise SystemExit("bench.py: a batch with one corrupted proof verified as true")
     # parity guard inside the bench: the host-buffer path and the resident path must agree byte for byte
     if not (torch.equal(h_comm, d_comm.cpu()) and torch.equal(h_proof, d_proof.cpu())):
         raise SystemExit("bench.py: host-buffer and resident outputs differ")
@@ -353,7 +367,9 @@ def main():
             "e2e": {"value": total / (ms_e2e * 1e-3), "unit": "blobs/s", "h2d_bytes_per_step": 3 * n * BLOB + 3 * n * 48, "d2h_bytes_per_step": 2 * n * 48 + 200 + 8 * n,
                     "ms_per_step": ms_e2e, "steps": r["e2e_steps"], "api": "kb200_blob_to_commitment + kb200_compute_blob_proof + kb200_verify_blob_proof_batch_partial (pinned host buffers)"},
             "gpu_launches": int(r["launches"]), "roofline": roofline, "cpu_baseline": cpu_baseline, "clocks": r["clocks"],
-            "setup_seconds": info["setup_seconds"]}
+            "setup_seconds": info["setup_seconds"],
+            "checks": {"valid_batch_verdict": True, "one_corrupted_proof_verdict": False, "host_buffer_outputs_equal_resident": True,
+                       "oracle_outputs_equal_engine_on_cpu_sample": cpu_baseline is not None}}
     print(json.dumps(line), flush=True)
     s.close()
     if world > 1:

@@ -70,6 +70,10 @@ void kb200_setup_free(kb200_setup* s);
 /* Stream for all later work on this handle (a cudaStream_t passed as void*; NULL = default stream). */
 int kb200_set_stream(kb200_setup* s, void* cuda_stream);
 const char* kb200_last_error(void);
+/* Page-locked host buffers for the host-buffer entry points (cudaMemcpyAsync from pageable memory is staged and slower);
+ * optional: any host pointer is accepted everywhere. */
+int kb200_alloc_pinned(size_t bytes, void** out);
+int kb200_free_pinned(void* p);
 
 /* ---- Setup::blob_to_commitment (src/kzg/setup.rs:167-171) + Compress::compress; n = 1 is the reference call ---- */
 int kb200_blob_to_commitment(kb200_setup* s, const uint8_t* blobs, size_t n, uint8_t* out48, int32_t* status);

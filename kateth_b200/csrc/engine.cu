@@ -333,6 +333,15 @@ extern "C" void kb200_setup_free(kb200_setup* s) {
     for (cudaEvent_t e : s->prof_ev) cudaEventDestroy(e);
     delete s;
 }
+extern "C" int kb200_alloc_pinned(size_t bytes, void** out) {
+    if (!out) return KB200_E_ARG;
+    CU(cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault));
+    return 0;
+}
+extern "C" int kb200_free_pinned(void* p) {
+    if (p) CU(cudaFreeHost(p));
+    return 0;
+}
 extern "C" int kb200_set_stream(kb200_setup* s, void* stream) { if (!s) return KB200_E_ARG; s->stream = (cudaStream_t)stream; return 0; }
 extern "C" int kb200_set_batch_challenge(kb200_setup* s, int mode) {
     if (!s || mode < 0 || mode > 1) return KB200_E_ARG;

@@ -36,7 +36,7 @@ class _Info(C.Structure):
 
 # every symbol include/kateth_b200.h declares (tests/test_abi.py checks the header against this list and the .so)
 SYMBOLS = [
-    "kb200_setup_load_json", "kb200_setup_load_raw", "kb200_setup_free", "kb200_set_stream", "kb200_last_error",
+    "kb200_setup_load_json", "kb200_setup_load_raw", "kb200_setup_free", "kb200_set_stream", "kb200_last_error", "kb200_alloc_pinned", "kb200_free_pinned",
     "kb200_blob_to_commitment", "kb200_blob_to_commitment_device", "kb200_compute_blob_proof", "kb200_compute_blob_proof_device",
     "kb200_compute_proof", "kb200_compute_proof_device", "kb200_verify_proof", "kb200_verify_proof_batch", "kb200_verify_blob_proof",
     "kb200_verify_blob_proof_batch", "kb200_verify_blob_proof_batch_device", "kb200_verify_blob_proof_batch_partial_device",
