@@ -204,7 +204,6 @@ static int first_nonzero(const std::vector<int32_t>& v) { for (int32_t x : v) if
 static int build_setup(kb200_setup* s, const uint8_t* g1, const uint8_t* g2, int window_bits) {
     auto t0 = std::chrono::steady_clock::now();
     CU(cudaSetDevice(s->device));
-    if (const char* e = getenv("KB200_STACK")) CU(cudaDeviceSetLimit(cudaLimitStackSize, (size_t)atoi(e)));
     cudaDeviceProp prop; CU(cudaGetDeviceProperties(&prop, s->device));
     s->sm_count = prop.multiProcessorCount;
     if (int rc = init_consts()) return rc;
