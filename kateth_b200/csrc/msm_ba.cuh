@@ -39,10 +39,6 @@ struct BaOffset { uint32_t l[8]; };     // sum_{j < nwin-1} 2^(c-1) * 2^(c*j)
 // instruction product inlined at every call site the instruction working set is > 100 KB and the warps stall on
 // instruction fetch (ncu: no_instructions 28 %).  Arguments and result travel in registers (by-value structs: no stack).
 __device__ __noinline__ Fp fp_mulc(Fp a, Fp b) { Fp r; fp_mul(r, a, b); return r; }
-// Two independent products in one call: their IMAD.WIDE carry chains interleave, so a warp that is alone on the multiplier
-// keeps it busier than with two dependent-latency-bound single products (and one call's worth of argument moves is saved).
-struct Fp2 { Fp a, b; };
-__device__ __noinline__ Fp2 fp_mul2c(Fp a, Fp b, Fp c, Fp d) { Fp2 r; fp_mul(r.a, a, b); fp_mul(r.b, c, d); return r; }
 #define BA_MUL(r, a, b) r = fp_mulc(a, b)
 #define BA_SQR(r, a) r = fp_mulc(a, a)
 
@@ -313,7 +309,7 @@ __global__ void __launch_bounds__(BA_THREADS, 4) k_msm_ba(BaArgs A) {
                                 inv = ba_rare_add(C, round, k, K, inv, pk);
                             } else {
                                 Fp dinv, lam, t, x3, y3;
-                                { Fp2 q = fp_mul2c(inv, pk, inv, d); dinv = q.a; inv = q.b; }
+                                BA_MUL(dinv, inv, pk); BA_MUL(inv, inv, d);
                                 fp_sub(t, y2, y1); BA_MUL(lam, t, dinv);
                                 BA_SQR(x3, lam); fp_sub(x3, x3, x1); fp_sub(x3, x3, x2);
                                 fp_sub(t, x1, x3); BA_MUL(t, lam, t); fp_sub(y3, t, y1);
