@@ -287,7 +287,11 @@ def main():
     r = run_engine(args)
     rank, world, n, s = r["rank"], r["world"], r["n"], r["s"]
     if rank != 0:
+        # leave together with rank 0 (it still formats and prints the line): no rank tears NCCL down while another is alive
+        import torch.distributed as dist
         s.close()
+        dist.barrier()
+        dist.destroy_process_group()
         return
     import torch
     total = n * world
@@ -370,10 +374,12 @@ def main():
             "setup_seconds": info["setup_seconds"],
             "checks": {"valid_batch_verdict": True, "one_corrupted_proof_verdict": False, "host_buffer_outputs_equal_resident": True,
                        "oracle_outputs_equal_engine_on_cpu_sample": cpu_baseline is not None}}
-    print(json.dumps(line), flush=True)
+    sys.stdout.write(json.dumps(line) + "\n")
+    sys.stdout.flush()
     s.close()
     if world > 1:
         import torch.distributed as dist
+        dist.barrier()
         dist.destroy_process_group()
 
 
