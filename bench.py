@@ -140,7 +140,7 @@ def run_reference(args):
                        "blobs_per_step": n, "note": "kateth is Rust over blst (no toolchain, crate absent): this is oracle/'s C restatement of its algorithm"},
             "cpu_baseline": {"value": val, "unit": "blobs/s", "cores": threads, "kind": "port", "sample": "%d blobs per step, %d threads" % (n, threads)},
             "e2e": {"value": val, "unit": "blobs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------ the sm_100a engine
@@ -269,6 +269,25 @@ def load_peaks():
         return None
 
 
+_REAL_STDOUT = None
+
+
+def keep_stdout_clean():
+    """The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner to stdout when
+    NCCL_DEBUG=VERSION is set in the environment): point fd 1 at stderr for the rest of the run and keep the real stdout aside."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line):
+    out = _REAL_STDOUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -282,6 +301,7 @@ def main():
     ap.add_argument("--ref-blobs", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    keep_stdout_clean()
     if args.impl == "reference":
         return run_reference(args)
     r = run_engine(args)
@@ -374,8 +394,7 @@ def main():
             "setup_seconds": info["setup_seconds"],
             "checks": {"valid_batch_verdict": True, "one_corrupted_proof_verdict": False, "host_buffer_outputs_equal_resident": True,
                        "oracle_outputs_equal_engine_on_cpu_sample": cpu_baseline is not None}}
-    sys.stdout.write(json.dumps(line) + "\n")
-    sys.stdout.flush()
+    emit(line)
     s.close()
     if world > 1:
         import torch.distributed as dist
