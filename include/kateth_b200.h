@@ -63,6 +63,9 @@ typedef struct kb200_setup kb200_setup;
  * table and the fixed-base window table on `device`.  window_bits: 0 = default (13 -> 28.6 GiB table), else 4..15
  * (15 -> 17 windows, 107 GiB).  The top window is unsigned; the others hold signed-digit magnitudes. */
 int kb200_setup_load_json(const char* path, int device, int window_bits, kb200_setup** out);
+/* Same from c-kzg-4844's trusted_setup.txt ("4096", "65", 4096 G1 Lagrange lines, 65 G2 monomial lines, optional G1 monomial
+ * lines which are ignored); kateth itself only reads the JSON form. */
+int kb200_setup_load_txt(const char* path, int device, int window_bits, kb200_setup** out);
 /* Same from decoded bytes: n_g1 x 48 bytes, n_g2 x 96 bytes. */
 int kb200_setup_load_raw(const uint8_t* g1_lagrange48, size_t n_g1, const uint8_t* g2_monomial96, size_t n_g2, int device, int window_bits,
                          kb200_setup** out);

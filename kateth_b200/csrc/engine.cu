@@ -4,6 +4,7 @@
 // There is no CPU fallback anywhere in this file: every path launches the sm_100a kernels or fails.
 #include <cuda_runtime.h>
 #include <stdio.h>
+#include <ctype.h>
 #include <stdlib.h>
 #include <string.h>
 #include <string>
@@ -313,6 +314,46 @@ extern "C" int kb200_setup_load_json(const char* path, int device, int window_bi
     // kateth reads 48/96 bytes behind the pointer without a length check (src/bls.rs:514); the ABI checks.
     for (size_t i = 0; i < g1.size(); i++) { if (g1[i].size() != 48) return KB200_E_G1_INVALID_ENCODING; memcpy(&b1[48 * i], g1[i].data(), 48); }
     for (size_t i = 0; i < g2.size(); i++) { if (g2[i].size() != 96) return KB200_E_G1_INVALID_ENCODING; memcpy(&b2[96 * i], g2[i].data(), 96); }
+    return kb200_setup_load_raw(b1.data(), KB_N, b2.data(), 65, device, window_bits, out);
+}
+// c-kzg-4844's trusted_setup.txt: "4096\n65\n", then 4096 lines of 96 hex digits (g1_lagrange), 65 lines of 192 hex digits
+// (g2_monomial) and, in newer files, 4096 more G1 lines (g1_monomial, ignored here).  Whitespace-separated tokens, no "0x".
+extern "C" int kb200_setup_load_txt(const char* path, int device, int window_bits, kb200_setup** out) {
+    if (!path || !out) return KB200_E_ARG;
+    FILE* f = fopen(path, "rb");
+    if (!f) { snprintf(g_err, sizeof g_err, "cannot open %s", path); return KB200_E_IO; }
+    std::string doc; char buf[65536]; size_t k;
+    while ((k = fread(buf, 1, sizeof buf, f)) > 0) doc.append(buf, k);
+    fclose(f);
+    std::vector<std::string> tok;
+    for (size_t i = 0; i < doc.size();) {
+        while (i < doc.size() && isspace((unsigned char)doc[i])) i++;
+        size_t j = i;
+        while (j < doc.size() && !isspace((unsigned char)doc[j])) j++;
+        if (j > i) tok.emplace_back(doc, i, j - i);
+        i = j;
+    }
+    if (tok.size() < 2) { snprintf(g_err, sizeof g_err, "trusted setup text: missing counts"); return KB200_E_PARSE; }
+    char* end = nullptr;
+    unsigned long n1 = strtoul(tok[0].c_str(), &end, 10); if (*end) return KB200_E_PARSE;
+    unsigned long n2 = strtoul(tok[1].c_str(), &end, 10); if (*end) return KB200_E_PARSE;
+    if (n1 != KB_N) return KB200_E_SETUP_G1_LEN;
+    if (n2 != 65) return KB200_E_SETUP_G2_LEN;
+    if (tok.size() < 2 + n1 + n2) { snprintf(g_err, sizeof g_err, "trusted setup text: %zu tokens, need %lu", tok.size(), 2 + n1 + n2); return KB200_E_PARSE; }
+    std::vector<uint8_t> b1(KB_N * 48), b2(65 * 96);
+    auto unhex = [&](const std::string& t, uint8_t* dst, size_t bytes) -> int {
+        const char* p = t.c_str(); size_t len = t.size();
+        if (len >= 2 && p[0] == '0' && (p[1] == 'x' || p[1] == 'X')) { p += 2; len -= 2; }
+        if (len != 2 * bytes) return KB200_E_G1_INVALID_ENCODING;
+        for (size_t i = 0; i < bytes; i++) {
+            int hi = hexval(p[2 * i]), lo = hexval(p[2 * i + 1]);
+            if (hi < 0 || lo < 0) return KB200_E_PARSE;
+            dst[i] = (uint8_t)(hi << 4 | lo);
+        }
+        return 0;
+    };
+    for (size_t i = 0; i < n1; i++) if (int rc = unhex(tok[2 + i], &b1[48 * i], 48)) return rc;
+    for (size_t i = 0; i < n2; i++) if (int rc = unhex(tok[2 + n1 + i], &b2[96 * i], 96)) return rc;
     return kb200_setup_load_raw(b1.data(), KB_N, b2.data(), 65, device, window_bits, out);
 }
 extern "C" void kb200_setup_free(kb200_setup* s) {

@@ -36,7 +36,7 @@ class _Info(C.Structure):
 
 # every symbol include/kateth_b200.h declares (tests/test_abi.py checks the header against this list and the .so)
 SYMBOLS = [
-    "kb200_setup_load_json", "kb200_setup_load_raw", "kb200_setup_free", "kb200_set_stream", "kb200_last_error", "kb200_alloc_pinned", "kb200_free_pinned",
+    "kb200_setup_load_json", "kb200_setup_load_txt", "kb200_setup_load_raw", "kb200_setup_free", "kb200_set_stream", "kb200_last_error", "kb200_alloc_pinned", "kb200_free_pinned",
     "kb200_blob_to_commitment", "kb200_blob_to_commitment_device", "kb200_compute_blob_proof", "kb200_compute_blob_proof_device",
     "kb200_compute_proof", "kb200_compute_proof_device", "kb200_verify_proof", "kb200_verify_proof_batch", "kb200_verify_blob_proof",
     "kb200_verify_blob_proof_batch", "kb200_verify_blob_proof_batch_device", "kb200_verify_blob_proof_batch_partial_device",
@@ -82,6 +82,13 @@ class Setup:
     def load_json(cls, path, device=0, window_bits=0):
         h = C.c_void_p()
         _check(lib().kb200_setup_load_json(os.fsencode(path), int(device), int(window_bits), C.byref(h)))
+        return cls(h)
+
+    @classmethod
+    def load_txt(cls, path, device=0, window_bits=0):
+        """c-kzg-4844 trusted_setup.txt (not a kateth format; same tables as load_json of the same points)."""
+        h = C.c_void_p()
+        _check(lib().kb200_setup_load_txt(os.fsencode(path), int(device), int(window_bits), C.byref(h)))
         return cls(h)
 
     def close(self):

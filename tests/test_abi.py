@@ -53,3 +53,38 @@ def test_engine_does_not_reference_oracle():
                 assert "kzg_oracle" not in txt and "from oracle" not in txt and "import oracle" not in txt, f
     out = subprocess.check_output(["nm", "-D", os.path.join(ROOT, "kateth_b200", "libkateth_b200.so")]).decode()
     assert "kzo_" not in out
+
+
+def _write_txt(path, mutate=None):
+    import json
+    d = json.load(open(os.path.join(ROOT, "tests/golden/trusted_setup_4096.json")))
+    g1 = [x[2:] for x in d["g1_lagrange"]]; g2 = [x[2:] for x in d["g2_monomial"]]
+    lines = [str(len(g1)), str(len(g2))] + g1 + g2 + g1[:3]          # trailing G1 monomial lines are ignored
+    if mutate:
+        lines = mutate(lines)
+    open(path, "w").write("\n".join(lines) + "\n")
+
+
+def test_txt_setup_parser(tmp_path):
+    """c-kzg text setups: parse errors are reported before the device is touched; a good file gets as far as the GPU."""
+    import torch
+    import kateth_b200 as K
+    good = tmp_path / "trusted_setup.txt"
+    _write_txt(good)
+    if torch.cuda.is_available():
+        s = K.Setup.load_txt(str(good)); s.close()
+    else:
+        with pytest.raises(K.KzgError) as e:
+            K.Setup.load_txt(str(good))
+        assert e.value.status == -1                                   # parsed; no CUDA device (no CPU fallback)
+    cases = [(lambda l: ["4095"] + l[1:], -10), (lambda l: [l[0], "64"] + l[2:], -11), (lambda l: l[:100], -3),
+             (lambda l: l[:2] + ["zz" + l[2][2:]] + l[3:], -3), (lambda l: l[:2] + [l[2][:-2]] + l[3:], 3)]
+    for k, (mut, want) in enumerate(cases):
+        bad = tmp_path / ("bad%d.txt" % k)
+        _write_txt(bad, mut)
+        with pytest.raises(K.KzgError) as e:
+            K.Setup.load_txt(str(bad))
+        assert e.value.status == want, k
+    with pytest.raises(K.KzgError) as e:
+        K.Setup.load_txt(str(tmp_path / "missing.txt"))
+    assert e.value.status == -2

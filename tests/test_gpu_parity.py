@@ -397,3 +397,20 @@ def test_batch_affine_at_scale_with_bad_items(engine_setup, oracle_setup):
     for k, i in enumerate(good):
         assert proofs[48 * k:48 * k + 48] == wantp[i % len(base)], i
     assert engine_setup.verify_blob_proof_batch_concat(gcat, gcomm, proofs, len(good)) is True
+
+
+def test_txt_setup_gives_the_same_engine(tmp_path):
+    import json
+    import kateth_b200 as K
+    d = json.load(open(os.path.join(ROOT, "tests/golden/trusted_setup_4096.json")))
+    p = tmp_path / "trusted_setup.txt"
+    p.write_text("\n".join(["4096", "65"] + [x[2:] for x in d["g1_lagrange"]] + [x[2:] for x in d["g2_monomial"]]) + "\n")
+    s = K.Setup.load_txt(str(p), window_bits=9)
+    try:
+        vb = RV.valid_blobs()
+        c = s.blob_to_commitment(vb[2])
+        assert c.hex() == GOLD_COMM[2]
+        pr = s.blob_proof(vb[2], c)
+        assert s.verify_blob_proof(vb[2], c, pr) is True
+    finally:
+        s.close()
