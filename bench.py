@@ -295,8 +295,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="engine", choices=["engine", "reference"])
     ap.add_argument("--blobs", type=int, default=4096, help="blobs per GPU per step (BASELINE configs[2]: 4096)")
-    ap.add_argument("--window-bits", type=int, default=int(os.environ.get("KB200_WINDOW_BITS", "15")),
-                    help="fixed-base table window width: 15 = 17 windows, 107 GiB table (throughput configuration); library default 13 = 28.6 GiB")
+    ap.add_argument("--window-bits", type=int, default=int(os.environ.get("KB200_WINDOW_BITS", "16")),
+                    help="fixed-base table window width: 15 = 17 windows, 107 GiB table; 16 = GLV form, 2 x 8 windows on a 100 GiB table; library default 13 = 28.6 GiB")
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--ref-blobs", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -331,7 +331,7 @@ def main():
     peaks = load_peaks()
     hbm_peak = peaks["hbm_gbs"] if peaks else 6650.0
     info1 = s.info()
-    W = info["windows"]
+    W = info["windows"] * (info.get("glv", 0) + 1)      # gathered points per scalar (GLV tables: two halves share the windows)
     ba = bool(info1.get("last_msm_batch_affine", 0))
     if ba:
         # k_msm_ba (msm_ba.cuh): per thread 31W affine additions (6 Fp products each: 1 prefix, 2 suffix, 1 slope, 1 square,
@@ -383,7 +383,7 @@ def main():
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32 limbs (Fp 12x32, Fr 8x32 Montgomery, IMAD.WIDE)",
             "data": "synthetic canonical field elements, uniform in [0, r)",
             "config": {"workload": "commit + compute_blob_kzg_proof + verify_blob_kzg_proof_batch over %d blobs per GPU (BASELINE configs[2] size; configs[3] sharding)" % n,
-                       "blobs_per_gpu": n, "global_blobs": total, "window_bits": info["window_bits"], "windows": info["windows"], "msm_shape": "batch-affine (k_msm_ba)" if ba else "xyzz (k_msm)",
+                       "blobs_per_gpu": n, "global_blobs": total, "window_bits": info["window_bits"], "windows": info["windows"], "glv": bool(info.get("glv", 0)), "points_per_scalar": W, "msm_shape": "batch-affine (k_msm_ba)" if ba else "xyzz (k_msm)",
                        "table_gb": round(info["table_bytes"] / 2 ** 30, 2), "parallelism": "blob shards x%d, replicated tables, 1 all-gather of 320 B" % world,
                        "l2": "inputs (%d MiB of blobs + multi-GB table) exceed the 126 MB L2; no flush needed" % (n * BLOB >> 20)},
             "stages_ms": {"commit": stage[0], "prove": stage[1], "verify": stage[2]},

@@ -61,7 +61,9 @@ typedef struct kb200_setup kb200_setup;
  * Parses {"g1_lagrange": [4096 x "0x" + 96 hex], "g2_monomial": [65 x "0x" + 192 hex]}, validates every point
  * (curve + subgroup; G1 on the GPU, G2 on the host), bit-reverses the Lagrange points, builds the roots-of-unity
  * table and the fixed-base window table on `device`.  window_bits: 0 = default (13 -> 28.6 GiB table), else 4..15
- * (15 -> 17 windows, 107 GiB).  The top window is unsigned; the others hold signed-digit magnitudes. */
+ * (15 -> 17 windows, 107 GiB).  The top window is unsigned; the others hold signed-digit magnitudes.
+ * 16, or 100 + c for c in 4..16, selects the GLV form: every scalar is split along the G1 endomorphism into two 128-bit
+ * halves that share one table of ceil(128 / c) windows (16 -> 8 windows, 100 GiB, 16 gathered points per scalar instead of 17). */
 int kb200_setup_load_json(const char* path, int device, int window_bits, kb200_setup** out);
 /* Same from c-kzg-4844's trusted_setup.txt ("4096", "65", 4096 G1 Lagrange lines, 65 G2 monomial lines, optional G1 monomial
  * lines which are ignored); kateth itself only reads the JSON form. */
@@ -134,6 +136,7 @@ typedef struct {
     double setup_seconds;
     int last_msm_batch_affine; /* 1 when the most recent MSM ran as k_msm_ba (batch-affine), 0 for k_msm (XYZZ) */
     int ba_grid;               /* persistent grid of k_msm_ba (resident CTAs) */
+    int glv;                   /* 1: GLV table (windows = windows per 128-bit half, 2 * windows points per scalar) */
 } kb200_info;
 int kb200_get_info(kb200_setup* s, kb200_info* info);
 /* CUDA-event timing of the dominant kernel (the fixed-base MSM) for roofline reporting: switch on, run, read the summed

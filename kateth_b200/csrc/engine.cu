@@ -236,14 +236,22 @@ static int build_setup(kb200_setup* s, const uint8_t* g1, const uint8_t* g2, int
     LAUNCH(s, k_neg_g_table, 1, 32, s->d_neg_g_pow);
     // fixed-base window table: nwin = ceil(255 / c) windows; windows below the top hold the 2^(c-1) signed-digit magnitudes, the top
     // window is unsigned and holds (r >> c*(nwin-1)) + 1 magnitudes (scalars are canonical, so its digit never exceeds that)
+    // GLV form (window_bits 16, or 100 + c for any c): the windows cover one 128-bit half of the scalar split k = k1 + k2*N
+    // (glv.cuh), nwin = ceil(128 / c), and the top window holds (N >> c*(nwin-1)) + 1 magnitudes; both halves read the same table.
     int c = window_bits ? window_bits : 13;
-    if (c < 4 || c > 15) { cudaFree(d_pts); return KB200_E_ARG; }
-    int nwin = (255 + c - 1) / c;
+    int glv = 0;
+    if (c == 16) glv = 1;
+    else if (c >= 100) { glv = 1; c -= 100; }
+    if (c < 4 || c > (glv ? 16 : 15)) { cudaFree(d_pts); return KB200_E_ARG; }
+    int nwin = ((glv ? 128 : 255) + c - 1) / c;
     int dlast;
     {
+        static const uint32_t GLV_N[4] = {0x00000000u, 0x00000001u, 0x0001a402u, 0xac45a401u};
+        const uint32_t* top_of = glv ? GLV_N : kb200::consts::H_FR_R;
+        const int limbs = glv ? 4 : 8;
         int sh = c * (nwin - 1), limb = sh >> 5, off = sh & 31;
-        uint64_t top = kb200::consts::H_FR_R[limb];
-        if (limb + 1 < 8) top |= (uint64_t)kb200::consts::H_FR_R[limb + 1] << 32;
+        uint64_t top = top_of[limb];
+        if (limb + 1 < limbs) top |= (uint64_t)top_of[limb + 1] << 32;
         dlast = (int)(top >> off) + 1;
     }
     size_t win_rows = (size_t)1 << (c - 1);
@@ -267,7 +275,7 @@ static int build_setup(kb200_setup* s, const uint8_t* g1, const uint8_t* g2, int
     CU(cudaStreamSynchronize(s->stream));
     CU(cudaGetLastError());
     cudaFree(scratch); cudaFree(d_pts);
-    s->tab.data = s->d_table; s->tab.c = c; s->tab.nwin = nwin; s->tab.dlast = dlast;
+    s->tab.data = s->d_table; s->tab.c = c; s->tab.nwin = nwin; s->tab.dlast = dlast; s->tab.glv = glv;
     {   // batch-affine MSM: signed-digit offset, persistent grid, work counter
         memset(&s->ba_off, 0, sizeof s->ba_off);
         for (int j = 0; j < nwin - 1; j++) { int bit = c * j + c - 1; s->ba_off.l[bit >> 5] |= 1u << (bit & 31); }
@@ -413,7 +421,7 @@ extern "C" int kb200_get_info(kb200_setup* s, kb200_info* info) {
     if (!s || !info) return KB200_E_ARG;
     info->window_bits = s->tab.c; info->windows = s->tab.nwin; info->table_bytes = s->table_bytes; info->kernel_launches = s->launches;
     info->device = s->device; info->sm_count = s->sm_count; info->setup_seconds = s->setup_seconds;
-    info->last_msm_batch_affine = s->last_ba; info->ba_grid = s->ba_grid;
+    info->last_msm_batch_affine = s->last_ba; info->ba_grid = s->ba_grid; info->glv = s->tab.glv;
     return 0;
 }
 
@@ -437,9 +445,9 @@ static int run_msm(kb200_setup* s, const uint32_t* d_scalars, size_t n, const in
     if (int rc = s->partials.ensure(n * S * sizeof(G1))) return rc;
     unsigned grid = 0;
     if (ba) {
-        const size_t K1 = (size_t)BA_UB * s->tab.nwin / 2;
+        const size_t K1 = (size_t)BA_UB * s->tab.nwin * (s->tab.glv + 1) / 2;
         grid = (unsigned)((n < (size_t)s->ba_grid) ? n : (size_t)s->ba_grid);
-        if (int rc = s->dig.ensure(n * KB_N * (size_t)s->tab.nwin * 4)) return rc;
+        if (int rc = s->dig.ensure(n * KB_N * (size_t)s->tab.nwin * (s->tab.glv + 1) * 4)) return rc;
         if (int rc = s->scr_pts.ensure((size_t)s->ba_grid * K1 * 6 * BA_THREADS * sizeof(uint4))) return rc;
         if (int rc = s->scr_pre.ensure((size_t)s->ba_grid * K1 * 3 * BA_THREADS * sizeof(uint4))) return rc;
     }

@@ -9,6 +9,7 @@
 #pragma once
 #include "field.cuh"
 #include "fp_bgcd.cuh"
+#include "glv.cuh"
 
 namespace kb200 {
 
@@ -104,30 +105,13 @@ __device__ __noinline__ void g1_mul(G1& r, const G1Affine& p, const Fr& k, int n
     r = acc;
 }
 
-// GLV split of a canonical scalar k < r along the endomorphism phi(x, y) = (beta x, y) = [-x^2]P (see g1_in_subgroup below):
-// with N = x^2 = 0xac45a4010001a4020000000100000000 (r = N^2 - N + 1), k = k1 + k2 * N, 0 <= k1 < N, 0 <= k2 < N, so
-//     [k]P = [k1]P + [k2]Q,   Q = -phi(P) = (beta x, -y),
-// two 128-bit scalar multiplications that can run on two threads.  Plain restoring division, once per scalar.
-__device__ __noinline__ void fr_glv_split(Fr& k1, Fr& k2, const Fr& k) {
-    const uint32_t N[5] = {0x00000000u, 0x00000001u, 0x0001a402u, 0xac45a401u, 0u};
-    uint32_t rem[5] = {0, 0, 0, 0, 0}, q[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-#pragma unroll 1
-    for (int i = 254; i >= 0; i--) {
-        const uint32_t bit = (k.l[i >> 5] >> (i & 31)) & 1u;
+// GLV split of a canonical scalar k < r (glv.cuh): [k]P = [k1]P + [k2]Q, Q = -phi(P) = (beta x, -y), two 128-bit scalar
+// multiplications that can run on two threads.
+__device__ __forceinline__ void fr_glv_split(Fr& k1, Fr& k2, const Fr& k) {
+    uint32_t a[4], b[4];
+    glv_split(a, b, k.l);
 #pragma unroll
-        for (int j = 4; j > 0; j--) rem[j] = (rem[j] << 1) | (rem[j - 1] >> 31);
-        rem[0] = (rem[0] << 1) | bit;
-        uint32_t d[5], bw = 0;
-#pragma unroll
-        for (int j = 0; j < 5; j++) { uint64_t t = (uint64_t)rem[j] - N[j] - bw; d[j] = (uint32_t)t; bw = (uint32_t)(t >> 63); }
-        if (!bw) {
-#pragma unroll
-            for (int j = 0; j < 5; j++) rem[j] = d[j];
-            q[i >> 5] |= 1u << (i & 31);
-        }
-    }
-#pragma unroll
-    for (int j = 0; j < 8; j++) { k1.l[j] = j < 4 ? rem[j] : 0u; k2.l[j] = q[j]; }
+    for (int j = 0; j < 8; j++) { k1.l[j] = j < 4 ? a[j] : 0u; k2.l[j] = j < 4 ? b[j] : 0u; }
 }
 
 // ---- ZCash 48-byte compressed form ----

@@ -27,6 +27,8 @@ struct MsmTable {
     int c;               // window bits
     int nwin;            // windows
     int dlast;           // digit magnitudes stored for the top (unsigned) window: (r >> c*(nwin-1)) + 1
+    int glv;             // 1: nwin windows cover a 128-bit GLV half (glv.cuh) and dlast is ((N >> c*(nwin-1)) + 1); every
+                         //    scalar contributes 2 * nwin points, the second half through Q = (beta x, -y)
 };
 
 __device__ __forceinline__ void load_affine(G1Affine& p, const uint4* src) {
@@ -126,6 +128,10 @@ __global__ void __launch_bounds__(MSM_THREADS) k_msm(MsmTable tab, const uint32_
         const int c = tab.c, nwin = tab.nwin;
         const uint32_t mask = (1u << c) - 1, D = 1u << (c - 1);
         const uint32_t* sbase = scalars + (size_t)item * (KB_N * 8);
+        // GLV tables (tab.glv): pass h = 1 sums the k2 halves, the sum is mapped through (X, Y) -> (beta X, -Y), then pass
+        // h = 0 adds the k1 halves on top.  Plain tables: one pass over the whole scalar.
+#pragma unroll 1
+        for (int h = tab.glv; h >= 0; h--) {
 #pragma unroll 1
         for (int i = slice * per_slice + tid; i < (slice + 1) * per_slice; i += MSM_THREADS) {
             uint32_t s[8];
@@ -139,6 +145,12 @@ __global__ void __launch_bounds__(MSM_THREADS) k_msm(MsmTable tab, const uint32_
                     s[0] = a.x; s[1] = a.y; s[2] = a.z; s[3] = a.w; s[4] = b.x; s[5] = b.y; s[6] = b.z; s[7] = b.w;
                 }
             }
+            if (tab.glv) {
+                uint32_t k1[4], k2[4];
+                glv_split(k1, k2, s);
+#pragma unroll
+                for (int k = 0; k < 4; k++) { s[k] = h ? k2[k] : k1[k]; s[4 + k] = 0; }
+            }
             uint32_t carry = 0;
             size_t e = (size_t)i;                                  // entry index of (window 0, d = 1, base i)
 #pragma unroll 1
@@ -148,7 +160,7 @@ __global__ void __launch_bounds__(MSM_THREADS) k_msm(MsmTable tab, const uint32_
 #pragma unroll
                 for (int k = 0; k < 7; k++) s[k] = __funnelshift_r(s[k], s[k + 1], c);
                 s[7] >>= c;
-                bool neg = d > D && j != nwin - 1;                 // the top window is unsigned (its digits are bounded by r >> c*(nwin-1))
+                bool neg = d > D && j != nwin - 1;                 // the top window is unsigned (its digits are bounded by dlast)
                 carry = neg ? 1u : 0u;
                 uint32_t mag = neg ? ((1u << c) - d) : d;
                 if (mag != 0) {
@@ -158,6 +170,8 @@ __global__ void __launch_bounds__(MSM_THREADS) k_msm(MsmTable tab, const uint32_
                 }
                 e += (size_t)D * KB_N;
             }
+        }
+        if (h == 1) { Fp b; fp_set(b, c_k.fp_beta); fp_mul(acc.x, acc.x, b); fp_neg(acc.y, acc.y); }
         }
     }
     // CTA tree reduction through shared memory

@@ -102,8 +102,8 @@ __device__ __noinline__ Fp ba_inv(Fp a) {
     Fp r; fp_inv(r, a); return r;
 }
 
-// digits: dig[((item * BA_UNITS + u) * NP + p) * BA_THREADS + t],  NP = BA_UB * nwin,  p = j * BA_UB + b,
-// for base i = (u * BA_UB + b) * BA_THREADS + t and window j.  Value: bit 31 = negative, low bits = table row
+// digits: dig[((item * BA_UNITS + u) * NP + p) * BA_THREADS + t],  NP = BA_UB * nwin * halves,  p = (h * nwin + j) * BA_UB + b,
+// for base i = (u * BA_UB + b) * BA_THREADS + t, window j and GLV half h (halves = 1 for a plain table: the whole scalar).  Value: bit 31 = negative, low bits = table row
 // (j << (c-1)) + |d| - 1, or BA_ZERO.
 template <int FMT>
 __global__ void __launch_bounds__(256) k_msm_recode(MsmTable tab, BaOffset off, const uint32_t* __restrict__ scalars, const int32_t* __restrict__ status,
@@ -123,32 +123,46 @@ __global__ void __launch_bounds__(256) k_msm_recode(MsmTable tab, BaOffset off, 
             s[0] = a.x; s[1] = a.y; s[2] = a.z; s[3] = a.w; s[4] = b.x; s[5] = b.y; s[6] = b.z; s[7] = b.w;
         }
     }
-    {   // s += off  (s < r < 2^255 and off < 2^255: no carry out)
-        uint32_t cy = 0;
-#pragma unroll
-        for (int k = 0; k < 8; k++) { uint64_t t = (uint64_t)s[k] + off.l[k] + cy; s[k] = (uint32_t)t; cy = (uint32_t)(t >> 32); }
-    }
-    const int c = tab.c, nwin = tab.nwin;
+    const int c = tab.c, nwin = tab.nwin, halves = tab.glv + 1;
     const uint32_t mask = (1u << c) - 1, D = 1u << (c - 1);
     const int t = i & (BA_THREADS - 1), ub = i >> 7, u = ub >> BA_UB_LOG, b = ub & (BA_UB - 1);
-    const int NP = BA_UB * nwin;
+    const int NP = BA_UB * nwin * halves;
     uint32_t* out = dig + (((size_t)item * BA_UNITS + u) * NP + b) * BA_THREADS + t;
-#pragma unroll 1
-    for (int j = 0; j < nwin; j++) {
-        uint32_t v = s[0] & mask;
+    uint32_t k2[4] = {0, 0, 0, 0};
+    if (tab.glv) {
+        uint32_t k1[4];
+        glv_split(k1, k2, s);
 #pragma unroll
-        for (int k = 0; k < 7; k++) s[k] = __funnelshift_r(s[k], s[k + 1], c);
-        s[7] >>= c;
-        uint32_t e;
-        if (j == nwin - 1) {
-            v = s[0] << c | v;       // the top window keeps everything that is left (it is unsigned)
-            e = v ? (((uint32_t)j << (c - 1)) + v - 1) : BA_ZERO;
-        } else {
-            int d = (int)v - (int)D;
-            uint32_t mag = d < 0 ? (uint32_t)(-d) : (uint32_t)d;
-            e = d ? ((((uint32_t)j << (c - 1)) + mag - 1) | (d < 0 ? 0x80000000u : 0u)) : BA_ZERO;
+        for (int k = 0; k < 4; k++) { s[k] = k1[k]; s[4 + k] = 0; }
+    }
+#pragma unroll 1
+    for (int h = 0; h < halves; h++) {
+        if (h == 1) {
+#pragma unroll
+            for (int k = 0; k < 4; k++) { s[k] = k2[k]; s[4 + k] = 0; }
         }
-        out[(size_t)j * BA_UB * BA_THREADS] = e;
+        {   // s += off  (s < r < 2^255 and off < 2^255, or s < N < 2^128 and off < 2^128: no carry out of the eight limbs)
+            uint32_t cy = 0;
+#pragma unroll
+            for (int k = 0; k < 8; k++) { uint64_t w = (uint64_t)s[k] + off.l[k] + cy; s[k] = (uint32_t)w; cy = (uint32_t)(w >> 32); }
+        }
+#pragma unroll 1
+        for (int j = 0; j < nwin; j++) {
+            uint32_t v = s[0] & mask;
+#pragma unroll
+            for (int k = 0; k < 7; k++) s[k] = __funnelshift_r(s[k], s[k + 1], c);
+            s[7] >>= c;
+            uint32_t e;
+            if (j == nwin - 1) {
+                v = s[0] << c | v;       // the top window keeps everything that is left (it is unsigned)
+                e = v ? (((uint32_t)j << (c - 1)) + v - 1) : BA_ZERO;
+            } else {
+                int d = (int)v - (int)D;
+                uint32_t mag = d < 0 ? (uint32_t)(-d) : (uint32_t)d;
+                e = d ? ((((uint32_t)j << (c - 1)) + mag - 1) | (d < 0 ? 0x80000000u : 0u)) : BA_ZERO;
+            }
+            out[(size_t)(h * nwin + j) * BA_UB * BA_THREADS] = e;
+        }
     }
 }
 
@@ -204,11 +218,18 @@ __device__ __forceinline__ void ba_prefetch(const BaRef& r) {
     asm volatile("prefetch.global.L2 [%0];" ::"l"(r.p + 5));
 }
 
+// Pair k of a round adds operands i1 = ba_i1(k, Kh) and i1 + Kh and leaves the sum in slot k.  Kh = pairs per GLV half: a
+// plain table has one half (i1 = k); with two halves the operands of half h sit at [2*h*Kh, 2*(h+1)*Kh) and its sums land in
+// [h*Kh, (h+1)*Kh), so the halves never mix and every round halves both.  The sums are written in ascending k: slot k is
+// never an operand of a later pair.
+__device__ __forceinline__ int ba_i1(int k, int Kh) { return k + (k >= Kh ? Kh : 0); }
+
 // Exceptional pairs (an operand at infinity, or x1 == x2) leave the hot loops through these two out-of-line functions;
 // they re-read their operands themselves so that nothing in the hot loops has its address taken.
 // Denominator: 2*y1 for a doubling, else 1 (nothing to invert).
-__device__ __noinline__ Fp ba_rare_den(BaCtx c, int round, int k, int K) {
-    BaRef r1 = ba_ref(c, round, k, round == 0 ? ba_digit(c, k) : 0u), r2 = ba_ref(c, round, k + K, round == 0 ? ba_digit(c, k + K) : 0u);
+__device__ __noinline__ Fp ba_rare_den(BaCtx c, int round, int k, int Kh) {
+    const int i1 = ba_i1(k, Kh), i2 = i1 + Kh;
+    BaRef r1 = ba_ref(c, round, i1, round == 0 ? ba_digit(c, i1) : 0u), r2 = ba_ref(c, round, i2, round == 0 ? ba_digit(c, i2) : 0u);
     Fp den, x1, x2;
     fp_set(den, c_k.fp_one);
     ba_ldx(x1, r1); ba_ldx(x2, r2);
@@ -219,8 +240,9 @@ __device__ __noinline__ Fp ba_rare_den(BaCtx c, int round, int k, int K) {
 }
 // Sum of an exceptional pair, written to scratch slot k; returns the running inverse advanced exactly as the forward pass
 // advanced the running product.
-__device__ __noinline__ Fp ba_rare_add(BaCtx c, int round, int k, int K, Fp inv, Fp pk) {
-    BaRef r1 = ba_ref(c, round, k, round == 0 ? ba_digit(c, k) : 0u), r2 = ba_ref(c, round, k + K, round == 0 ? ba_digit(c, k + K) : 0u);
+__device__ __noinline__ Fp ba_rare_add(BaCtx c, int round, int k, int Kh, Fp inv, Fp pk) {
+    const int o1 = ba_i1(k, Kh), o2 = o1 + Kh;
+    BaRef r1 = ba_ref(c, round, o1, round == 0 ? ba_digit(c, o1) : 0u), r2 = ba_ref(c, round, o2, round == 0 ? ba_digit(c, o2) : 0u);
     Fp x1, y1, x2, y2, x3, y3;
     ba_ldx(x1, r1); ba_ldy(y1, r1); ba_ldx(x2, r2); ba_ldy(y2, r2);
     const bool i1 = fp_is_zero(x1), i2 = fp_is_zero(x2);
@@ -244,11 +266,12 @@ __device__ __noinline__ Fp ba_rare_add(BaCtx c, int round, int k, int K, Fp inv,
 }
 
 __global__ void __launch_bounds__(BA_THREADS, 4) k_msm_ba(BaArgs A) {
+    static_assert(BA_UNITS == 1, "the GLV map below is applied to the accumulator of one unit");
     __shared__ G1 sm[BA_THREADS / 2];
     __shared__ unsigned int s_item;
     const int tid = threadIdx.x;
-    const int nwin = A.tab.nwin;
-    const int NP = BA_UB * nwin, K1 = NP / 2;
+    const int nwin = A.tab.nwin, halves = A.tab.glv + 1;
+    const int NP = BA_UB * nwin * halves, K1 = NP / 2;
     uint4* const pts = A.scr_pts + (size_t)blockIdx.x * K1 * 6 * BA_THREADS + tid;
     uint4* const pre = A.scr_pre + (size_t)blockIdx.x * K1 * 3 * BA_THREADS + tid;
     for (;;) {
@@ -259,74 +282,80 @@ __global__ void __launch_bounds__(BA_THREADS, 4) k_msm_ba(BaArgs A) {
         if (item >= (unsigned int)A.n) break;
         G1 acc; g1_set_inf(acc);
         if (A.status == nullptr || A.status[item] == 0) {
+            BaCtx C;
+            C.tab = A.tab.data; C.dg = A.dig + (size_t)item * NP * BA_THREADS + tid; C.pts = pts;
+            C.base0 = tid;
 #pragma unroll 1
-            for (int u = 0; u < BA_UNITS; u++) {
-                BaCtx C;
-                C.tab = A.tab.data; C.dg = A.dig + ((size_t)item * BA_UNITS + u) * NP * BA_THREADS + tid; C.pts = pts;
-                C.base0 = u * BA_UB * BA_THREADS + tid;
+            for (int round = 0, Kh = (BA_UB / 2) * nwin; round < BA_UB_LOG; round++, Kh >>= 1) {
+                const bool tab = round == 0;
+                const int K = Kh * halves;
+                // ---- forward (k descending): prefix products of the denominators.  Operands of the next pair are loaded
+                // before the product of this pair is issued, the digits of the pair after that before that.
+                Fp run; fp_set(run, c_k.fp_one);
+                {
+                    int i1 = ba_i1(K - 1, Kh);
+                    uint32_t d1 = tab ? ba_digit(C, i1) : 0u, d2 = tab ? ba_digit(C, i1 + Kh) : 0u;
+                    BaRef r1 = ba_ref(C, round, i1, d1), r2 = ba_ref(C, round, i1 + Kh, d2);
+                    Fp nx1, nx2; ba_ldx(nx1, r1); ba_ldx(nx2, r2);
+                    if (tab && K > 1) { i1 = ba_i1(K - 2, Kh); d1 = ba_digit(C, i1); d2 = ba_digit(C, i1 + Kh); }
 #pragma unroll 1
-                for (int round = 0, K = K1; round < BA_UB_LOG; round++, K >>= 1) {
-                    const bool tab = round == 0;
-                    // ---- forward: prefix products of the denominators.  Operands of pair k+1 are loaded before the
-                    // product of pair k is issued, the digits of pair k+2 before that.
-                    Fp run; fp_set(run, c_k.fp_one);
-                    {
-                        uint32_t d1 = tab ? ba_digit(C, 0) : 0u, d2 = tab ? ba_digit(C, K) : 0u;
-                        BaRef r1 = ba_ref(C, round, 0, d1), r2 = ba_ref(C, round, K, d2);
-                        Fp nx1, nx2; ba_ldx(nx1, r1); ba_ldx(nx2, r2);
-                        d1 = (tab && K > 1) ? ba_digit(C, 1) : 0u; d2 = (tab && K > 1) ? ba_digit(C, 1 + K) : 0u;
-#pragma unroll 1
-                        for (int k = 0; k < K; k++) {
-                            Fp x1 = nx1, x2 = nx2, d;
-                            if (k + 1 < K) {
-                                r1 = ba_ref(C, round, k + 1, d1); r2 = ba_ref(C, round, k + 1 + K, d2);
-                                ba_ldx(nx1, r1); ba_ldx(nx2, r2);
-                                if (tab && k + 2 < K) { d1 = ba_digit(C, k + 2); d2 = ba_digit(C, k + 2 + K); }
-                            }
-                            ba_st(pre + (size_t)k * 3 * BA_THREADS, run);
-                            fp_sub(d, x2, x1);
-                            if (fp_is_zero(x1) || fp_is_zero(x2) || fp_is_zero(d)) d = ba_rare_den(C, round, k, K);
-                            fp_mul(run, run, d);      // inlined: the only product of this loop, so the loads of pair k+1 stay in flight across it
+                    for (int k = K - 1; k >= 0; k--) {
+                        Fp x1 = nx1, x2 = nx2, d;
+                        if (k > 0) {
+                            i1 = ba_i1(k - 1, Kh);
+                            r1 = ba_ref(C, round, i1, d1); r2 = ba_ref(C, round, i1 + Kh, d2);
+                            ba_ldx(nx1, r1); ba_ldx(nx2, r2);
+                            if (tab && k > 1) { i1 = ba_i1(k - 2, Kh); d1 = ba_digit(C, i1); d2 = ba_digit(C, i1 + Kh); }
                         }
+                        ba_st(pre + (size_t)k * 3 * BA_THREADS, run);
+                        fp_sub(d, x2, x1);
+                        if (fp_is_zero(x1) || fp_is_zero(x2) || fp_is_zero(d)) d = ba_rare_den(C, round, k, Kh);
+                        fp_mul(run, run, d);      // inlined: the only product of this loop, so the loads of the next pair stay in flight across it
                     }
-                    Fp inv = ba_inv(run);
-                    // ---- backward: the additions.  The table entries of pair k-1 are pulled into L2 while pair k is added.
-                    {
-                        uint32_t d1 = tab ? ba_digit(C, K - 1) : 0u, d2 = tab ? ba_digit(C, 2 * K - 1) : 0u;
+                }
+                Fp inv = ba_inv(run);
+                // ---- backward (k ascending): the additions.  The table entries of pair k+1 are pulled into L2 while pair k is added.
+                {
+                    uint32_t d1 = tab ? ba_digit(C, 0) : 0u, d2 = tab ? ba_digit(C, Kh) : 0u;
 #pragma unroll 1
-                        for (int k = K - 1; k >= 0; k--) {
-                            BaRef r1 = ba_ref(C, round, k, d1), r2 = ba_ref(C, round, k + K, d2);
-                            Fp x1, y1, x2, y2, pk, d;
-                            ba_ldx(x1, r1); ba_ldx(x2, r2);
-                            ba_ld(pk, pre + (size_t)k * 3 * BA_THREADS, BA_THREADS);
-                            ba_ldy(y1, r1); ba_ldy(y2, r2);
-                            if (tab && k > 0) {
-                                d1 = ba_digit(C, k - 1); d2 = ba_digit(C, k - 1 + K);
-                                ba_prefetch(ba_ref(C, 0, k - 1, d1)); ba_prefetch(ba_ref(C, 0, k - 1 + K, d2));
-                            }
-                            fp_sub(d, x2, x1);
-                            if (fp_is_zero(x1) || fp_is_zero(x2) || fp_is_zero(d)) {
-                                inv = ba_rare_add(C, round, k, K, inv, pk);
-                            } else {
-                                Fp dinv, lam, t, x3, y3;
-                                BA_MUL(dinv, inv, pk); BA_MUL(inv, inv, d);
-                                fp_sub(t, y2, y1); BA_MUL(lam, t, dinv);
-                                BA_SQR(x3, lam); fp_sub(x3, x3, x1); fp_sub(x3, x3, x2);
-                                fp_sub(t, x1, x3); BA_MUL(t, lam, t); fp_sub(y3, t, y1);
-                                uint4* o = pts + (size_t)k * 6 * BA_THREADS;
-                                ba_st(o, x3); ba_st(o + 3 * BA_THREADS, y3);
-                            }
+                    for (int k = 0; k < K; k++) {
+                        const int i1 = ba_i1(k, Kh);
+                        BaRef r1 = ba_ref(C, round, i1, d1), r2 = ba_ref(C, round, i1 + Kh, d2);
+                        Fp x1, y1, x2, y2, pk, d;
+                        ba_ldx(x1, r1); ba_ldx(x2, r2);
+                        ba_ld(pk, pre + (size_t)k * 3 * BA_THREADS, BA_THREADS);
+                        ba_ldy(y1, r1); ba_ldy(y2, r2);
+                        if (tab && k + 1 < K) {
+                            const int j1 = ba_i1(k + 1, Kh);
+                            d1 = ba_digit(C, j1); d2 = ba_digit(C, j1 + Kh);
+                            ba_prefetch(ba_ref(C, 0, j1, d1)); ba_prefetch(ba_ref(C, 0, j1 + Kh, d2));
+                        }
+                        fp_sub(d, x2, x1);
+                        if (fp_is_zero(x1) || fp_is_zero(x2) || fp_is_zero(d)) {
+                            inv = ba_rare_add(C, round, k, Kh, inv, pk);
+                        } else {
+                            Fp dinv, lam, t, x3, y3;
+                            BA_MUL(dinv, inv, pk); BA_MUL(inv, inv, d);
+                            fp_sub(t, y2, y1); BA_MUL(lam, t, dinv);
+                            BA_SQR(x3, lam); fp_sub(x3, x3, x1); fp_sub(x3, x3, x2);
+                            fp_sub(t, x1, x3); BA_MUL(t, lam, t); fp_sub(y3, t, y1);
+                            uint4* o = pts + (size_t)k * 6 * BA_THREADS;
+                            ba_st(o, x3); ba_st(o + 3 * BA_THREADS, y3);
                         }
                     }
                 }
-                // the W sums of this unit -> XYZZ accumulator
+            }
+            // the nwin sums of each half -> XYZZ accumulator; the k2 half first, mapped through Q = (beta x, -y) as one sum
 #pragma unroll 1
-                for (int k = 0; k < nwin; k++) {
+            for (int h = halves - 1; h >= 0; h--) {
+#pragma unroll 1
+                for (int k = h * nwin; k < (h + 1) * nwin; k++) {
                     G1Affine pt;
                     ba_ld(pt.x, pts + (size_t)k * 6 * BA_THREADS, BA_THREADS);
                     ba_ld(pt.y, pts + (size_t)k * 6 * BA_THREADS + 3 * BA_THREADS, BA_THREADS);
                     ba_madd(acc, pt.x, pt.y);
                 }
+                if (h == 1) { Fp b; fp_set(b, c_k.fp_beta); BA_MUL(acc.x, acc.x, b); fp_neg(acc.y, acc.y); }
             }
         }
         // CTA tree reduction through shared memory

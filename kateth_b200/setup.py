@@ -31,7 +31,7 @@ _lib = None
 class _Info(C.Structure):
     _fields_ = [("window_bits", C.c_int), ("windows", C.c_int), ("table_bytes", C.c_uint64), ("kernel_launches", C.c_uint64),
                 ("device", C.c_int), ("sm_count", C.c_int), ("setup_seconds", C.c_double),
-                ("last_msm_batch_affine", C.c_int), ("ba_grid", C.c_int)]
+                ("last_msm_batch_affine", C.c_int), ("ba_grid", C.c_int), ("glv", C.c_int)]
 
 
 # every symbol include/kateth_b200.h declares (tests/test_abi.py checks the header against this list and the .so)

@@ -200,10 +200,14 @@ def test_g1_decompress_classes(engine_setup):
     assert re[0] == RV.G1 and re[1] == RV.INF
 
 
-@pytest.mark.parametrize("wb,mode", [(9, 1), (15, 1), (9, 2), (13, 2), (15, 2)])
+GLV_N = 0xac45a4010001a4020000000100000000      # x^2; r = N^2 - N + 1 (kateth_b200/csrc/glv.cuh)
+
+
+@pytest.mark.parametrize("wb,mode", [(9, 1), (15, 1), (9, 2), (13, 2), (15, 2), (109, 1), (109, 2), (111, 2), (16, 1), (16, 2)])
 def test_other_window_width_gives_same_bytes(wb, mode, oracle_setup):
-    """The window width is a tuning knob, not a semantic one.  15 is bench.py's throughput configuration (17 windows, the
-    top one unsigned and 15 bits wide, 107 GiB table); 9 exercises a 3-bit top window."""
+    """The window width is a tuning knob, not a semantic one.  15 is the widest plain table (17 windows, the top one unsigned
+    and 15 bits wide, 107 GiB); 9 exercises a 3-bit top window; 16 and 100 + c are the GLV form (two 128-bit halves per scalar
+    on ceil(128 / c) windows, the second half mapped through the endomorphism)."""
     import kateth_b200 as K
     s = K.Setup.load_json(os.path.join(ROOT, "tests/golden/trusted_setup_4096.json"), window_bits=wb)
     try:
@@ -211,9 +215,14 @@ def test_other_window_width_gives_same_bytes(wb, mode, oracle_setup):
         vb = RV.valid_blobs()
         for i, hexv in GOLD_COMM.items():
             assert s.blob_to_commitment(vb[i]).hex() == hexv
-        assert s.info()["window_bits"] == wb
-        # r - 1 everywhere, then scalars whose top window is maximal with and without a carry coming in
-        hi = [R - 1, R - 2 ** 240, (R >> 240 << 240) + 2 ** 239 + 5, (R >> 240 << 240) + 2 ** 239 - 5, 2 ** 254, 2 ** 240 - 1]
+        assert R == GLV_N * GLV_N - GLV_N + 1
+        assert s.info()["window_bits"] == wb % 100 and s.info()["glv"] == (1 if wb >= 16 else 0)
+        # r - 1 everywhere, then scalars whose top window is maximal with and without a carry coming in, then scalars whose GLV
+        # halves are extreme (k1 = N - 1, k2 = N - 1, either half zero, top window of a half maximal)
+        hi = [R - 1, R - 2 ** 240, (R >> 240 << 240) + 2 ** 239 + 5, (R >> 240 << 240) + 2 ** 239 - 5, 2 ** 254, 2 ** 240 - 1,
+              GLV_N - 1 + 700, GLV_N + 700, (GLV_N - 2) * GLV_N + GLV_N - 1, (GLV_N - 1) * GLV_N, 5 * GLV_N + 700, 2 ** 128 + 700,
+              (GLV_N >> 112 << 112) + 2 ** 111 + 705, ((GLV_N >> 112 << 112) + 2 ** 111 + 695) * GLV_N + GLV_N - 1]
+        assert all(0 <= v - 700 and v < R for v in hi)
         blob = b"".join(RV.fe(hi[k % len(hi)] - (k // len(hi))) for k in range(4096))
         c = s.blob_to_commitment(blob)
         assert c == oracle_setup.blob_to_commitment(blob)
@@ -295,8 +304,8 @@ def test_all_253_vectors_through_batch_affine_msm(monkeypatch):
     assert not missing
 
 
-@pytest.mark.parametrize("mode", [1, 2])
-def test_degenerate_setup_exercises_exceptional_additions(mode, tmp_path):
+@pytest.mark.parametrize("mode,wb", [(1, 9), (2, 9), (1, 109), (2, 109)])
+def test_degenerate_setup_exercises_exceptional_additions(mode, wb, tmp_path):
     """A setup whose Lagrange points are small multiples of the generator makes gathered table points and partial sums
     collide all the time (P == Q, P == -Q, infinity): the complete-formula paths of both MSM shapes must still give the
     group element the oracle's Pippenger gives."""
@@ -310,7 +319,7 @@ def test_degenerate_setup_exercises_exceptional_additions(mode, tmp_path):
     pts = ["0x" + _compress(mult[1 + (i * 7 + i // 64) % 7]).hex() for i in range(4096)]
     path = tmp_path / "degenerate_setup.json"
     path.write_text(json.dumps({"g1_lagrange": pts, "g2_monomial": real["g2_monomial"]}))
-    s = K.Setup.load_json(str(path), window_bits=9)
+    s = K.Setup.load_json(str(path), window_bits=wb)
     o = O.Setup.load_json(str(path))
     try:
         s.set_msm_mode(mode)

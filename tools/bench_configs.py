@@ -19,7 +19,7 @@ import bench as B
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--blobs", type=int, default=4096)
-    ap.add_argument("--window-bits", type=int, default=15)
+    ap.add_argument("--window-bits", type=int, default=16)
     ap.add_argument("--iters", type=int, default=300)
     args = ap.parse_args()
     import torch
