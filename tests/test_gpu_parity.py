@@ -408,6 +408,38 @@ def test_batch_affine_at_scale_with_bad_items(engine_setup, oracle_setup):
     assert engine_setup.verify_blob_proof_batch_concat(gcat, gcomm, proofs, len(good)) is True
 
 
+def test_host_batches_copied_in_two_pieces(engine_setup, oracle_setup):
+    """From 2 x 592 blobs on, the host-buffer commit call copies a head of one MSM wave and the rest separately and runs them as
+    two device passes (engine.cu h2d_split): outputs and statuses are those of one pass; the proof call takes the same inputs
+    in one piece."""
+    n = 1300
+    base = [rand_blob(6000 + i) for i in range(3)] + [b"".join(RV.fe(R - 1 - k) for k in range(4096))]
+    blobs = [base[i % len(base)] for i in range(n)]
+    bad_at = [5, 591, 592, 1299]                  # both sides of the split
+    for i in bad_at:
+        b = bytearray(blobs[i]); b[32 * (i % 4096):32 * (i % 4096) + 32] = RV.be32(R + i); blobs[i] = bytes(b)
+    cat = b"".join(blobs)
+    engine_setup.set_msm_mode(0)
+    comm, st = engine_setup.blob_to_commitment_many(cat, n)
+    assert [i for i in range(n) if st[i] != 0] == bad_at
+    want = [oracle_setup.blob_to_commitment(b) for b in base]
+    for i in range(n):
+        if i not in bad_at:
+            assert comm[48 * i:48 * i + 48] == want[i % len(base)], i
+    good = [i for i in range(n) if i not in bad_at][:1250]
+    gcat = b"".join(blobs[i] for i in good); gcomm = b"".join(comm[48 * i:48 * i + 48] for i in good)
+    proofs, st2 = engine_setup.blob_proof_many(gcat, gcomm, len(good))
+    assert st2 == [0] * len(good)
+    wantp = [oracle_setup.blob_proof(b, c) for b, c in zip(base, want)]
+    for k, i in enumerate(good):
+        assert proofs[48 * k:48 * k + 48] == wantp[i % len(base)], i
+    assert engine_setup.verify_blob_proof_batch_concat(gcat, gcomm, proofs, len(good)) is True
+    # a bad commitment in the tail is reported in the status of its own item only
+    bc = bytearray(gcomm); bc[48 * 1000:48 * 1000 + 48] = bytes([0xff] * 48)
+    _, st3 = engine_setup.blob_proof_many(gcat, bytes(bc), len(good))
+    assert [k for k in range(len(good)) if st3[k] != 0] == [1000]
+
+
 def test_txt_setup_gives_the_same_engine(tmp_path):
     import json
     import kateth_b200 as K

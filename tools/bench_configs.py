@@ -63,6 +63,7 @@ def main():
     for m in [1, 8, 64, 148, 296, 592, 1184, 2368, 4096]:
         if m > n:
             break
+        s.blob_to_commitment_device(d_blobs.data_ptr(), m, d_comm.data_ptr(), d_status.data_ptr())      # first call at a new size grows the scratch buffers
         ms = ev_ms(lambda: s.blob_to_commitment_device(d_blobs.data_ptr(), m, d_comm.data_ptr(), d_status.data_ptr()), 3)
         sweep.append({"blobs": m, "ms": ms, "blobs_per_s": m / ms * 1e3, "batch_affine": bool(s.info()["last_msm_batch_affine"])})
     print(json.dumps({"config": "sweep", "what": "blob_to_commitment, resident, by batch size", "points": sweep}), flush=True)
@@ -72,7 +73,11 @@ def main():
     assert s.blob_to_commitment_device(d_blobs.data_ptr(), n, d_comm.data_ptr(), d_status.data_ptr()) == 0
     ms_proof = ev_ms(lambda: s.proof_device(d_blobs.data_ptr(), z.data_ptr(), n, d_proof.data_ptr(), d_y.data_ptr(), d_status.data_ptr()), 3)
     pr, cm, zz, yy = (bytes(t.cpu().numpy()) for t in (d_proof, d_comm, z, d_y))
-    t0 = time.perf_counter(); ok = s.verify_proof_batch(pr, cm, zz, yy, n); ms_verify = (time.perf_counter() - t0) * 1e3
+    ok = s.verify_proof_batch(pr, cm, zz, yy, n)          # first call allocates
+    t0 = time.perf_counter()
+    for _ in range(3):
+        ok = s.verify_proof_batch(pr, cm, zz, yy, n) and ok
+    ms_verify = (time.perf_counter() - t0) * 1e3 / 3
     bad = bytearray(pr); bad[48:96] = pr[0:48]
     ok_bad = s.verify_proof_batch(bytes(bad), cm, zz, yy, n)
     one = s.verify_proof(pr[:48], cm[:48], zz[:32], yy[:32])
