@@ -393,7 +393,7 @@ def main():
             "gpu_launches": int(r["launches"]), "roofline": roofline, "cpu_baseline": cpu_baseline, "clocks": r["clocks"],
             "setup_seconds": info["setup_seconds"],
             "checks": {"valid_batch_verdict": True, "one_corrupted_proof_verdict": False, "host_buffer_outputs_equal_resident": True,
-                       "oracle_outputs_equal_engine_on_cpu_sample": cpu_baseline is not None}}
+                       "oracle_outputs_equal_engine_on_cpu_sample": True if cpu_baseline is not None else None}}      # None: CPU leg not run (N > 1 or --no-cpu-baseline)
     emit(line)
     s.close()
     if world > 1:
