@@ -543,10 +543,18 @@ extern "C" int kb200_compute_blob_proof_device(kb200_setup* s, const void* d_blo
     if (int rc = s->z.ensure(n * sizeof(Fr))) return rc;
     CU(cudaMemsetAsync(s->st_blob.p, 0, n * 4, s->stream));
     CU(cudaMemsetAsync(s->st_a.p, 0, n * 4, s->stream));
+    // as in verify_prepare: the commitment check (a 380-step chain per point) runs on the auxiliary stream beside the blob check
+    // and the serial SHA-256 of each blob; the challenge only needs the blob's own status
+    CU(cudaEventRecord(s->ev_fork, s->stream));
+    CU(cudaStreamWaitEvent(s->aux_stream, s->ev_fork, 0));
+    k_g1_decompress<<<blocks(n, 64), 64, 0, s->aux_stream>>>((const uint32_t*)d_comm48, (const uint32_t*)nullptr, (int)n, s->aff_c.as<G1Affine>(), (G1Affine*)nullptr,
+                                                              s->st_a.as<int32_t>(), (int32_t*)nullptr, 0);
+    s->launches++;
+    CU(cudaEventRecord(s->ev_join, s->aux_stream));
     LAUNCH(s, k_blob_check, blocks(n * KB_N, 256), 256, (const uint32_t*)d_blobs, (int)n, s->st_blob.as<int32_t>());
-    LAUNCH(s, k_g1_decompress, blocks(n, 64), 64, (const uint32_t*)d_comm48, (const uint32_t*)nullptr, (int)n, s->aff_c.as<G1Affine>(), (G1Affine*)nullptr, s->st_a.as<int32_t>(), (int32_t*)nullptr, 0);
+    LAUNCH(s, k_challenge, blocks(n, 32), 32, (const uint32_t*)d_blobs, (const uint32_t*)d_comm48, (int)n, s->st_blob.as<int32_t>(), s->z.as<Fr>());
+    CU(cudaStreamWaitEvent(s->stream, s->ev_join, 0));
     LAUNCH(s, k_merge_status, blocks(n, 256), 256, s->st_blob.as<int32_t>(), s->st_a.as<int32_t>(), (const int32_t*)nullptr, (int)n, d_status);
-    LAUNCH(s, k_challenge, blocks(n, 32), 32, (const uint32_t*)d_blobs, (const uint32_t*)d_comm48, (int)n, d_status, s->z.as<Fr>());
     if (int rc = prove_tail(s, (const uint32_t*)d_blobs, n, d_status, (uint32_t*)d_out48)) return rc;
     std::vector<int32_t> hb, ha;
     if (int rc = fetch_status(s, s->st_blob.as<int32_t>(), n, hb)) return rc;
