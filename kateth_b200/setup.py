@@ -22,7 +22,8 @@ class KzgError(Exception):
 
 
 def lib_path():
-    return os.path.join(_HERE, "libkateth_b200.so")
+    # KB200_LIB: another build of the same library (A/B measurements of kernel variants on one box)
+    return os.environ.get("KB200_LIB") or os.path.join(_HERE, "libkateth_b200.so")
 
 
 _lib = None
