@@ -69,6 +69,10 @@ struct kb200_setup {
     cudaStream_t copy_stream = nullptr;     // host-buffer entry points: blobs cross PCIe in two pieces (h2d_split)
     bool split_copy = true;                 // KB200_H2D_SPLIT=0 copies in one piece (measurement switch)
     cudaEvent_t ev_copy = nullptr, ev_head = nullptr, ev_tail = nullptr;
+    cudaEvent_t ev_col[8] = {};             // column pieces of a hashed upload (h2d_blobs_hashed)
+    DBuf sha_state;                         // chaining values between the pieces, [8][n] words
+    bool z_ready = false;                   // the challenges of the next proof / verify pass are already in s->z
+    bool fork_recorded = false;             // ev_fork already marks the point of the main stream the point decompression may start from
     BaOffset ba_off{};
     uint8_t last_lhs[48], last_rhs[48];
     bool have_last = false;
@@ -294,6 +298,7 @@ static int build_setup(kb200_setup* s, const uint8_t* g1, const uint8_t* g2, int
         CU(cudaEventCreateWithFlags(&s->ev_copy, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&s->ev_head, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&s->ev_tail, cudaEventDisableTiming));
+        for (int j = 0; j < 8; j++) CU(cudaEventCreateWithFlags(&s->ev_col[j], cudaEventDisableTiming));
         if (const char* e = getenv("KB200_MSM_MODE")) { int m = atoi(e); if (m >= 0 && m <= 2) s->msm_mode = m; }
         if (const char* e = getenv("KB200_H2D_SPLIT")) s->split_copy = atoi(e) != 0;
     }
@@ -387,6 +392,8 @@ extern "C" void kb200_setup_free(kb200_setup* s) {
     if (s->ev_copy) cudaEventDestroy(s->ev_copy);
     if (s->ev_head) cudaEventDestroy(s->ev_head);
     if (s->ev_tail) cudaEventDestroy(s->ev_tail);
+    for (int j = 0; j < 8; j++) if (s->ev_col[j]) cudaEventDestroy(s->ev_col[j]);
+    s->sha_state.release();
     DBuf* bufs[] = {&s->blobs, &s->c48, &s->p48, &s->zy32, &s->out48, &s->out32, &s->st_blob, &s->st_a, &s->st_b, &s->status, &s->z, &s->y, &s->prod,
                     &s->indom, &s->q, &s->partials, &s->aff_c, &s->aff_p, &s->rlc_part, &s->rlc_s, &s->rmont, &s->records, &s->combine, &s->dig, &s->scr_pts, &s->scr_pre, &s->transcript};
     for (DBuf* b : bufs) b->release();
@@ -542,17 +549,19 @@ extern "C" int kb200_compute_blob_proof_device(kb200_setup* s, const void* d_blo
     if (int rc = s->aff_c.ensure(n * sizeof(G1Affine))) return rc;
     if (int rc = s->z.ensure(n * sizeof(Fr))) return rc;
     CU(cudaMemsetAsync(s->st_blob.p, 0, n * 4, s->stream));
-    CU(cudaMemsetAsync(s->st_a.p, 0, n * 4, s->stream));
     // as in verify_prepare: the commitment check (a 380-step chain per point) runs on the auxiliary stream beside the blob check
     // and the serial SHA-256 of each blob; the challenge only needs the blob's own status
-    CU(cudaEventRecord(s->ev_fork, s->stream));
+    if (!s->fork_recorded) CU(cudaEventRecord(s->ev_fork, s->stream));
+    s->fork_recorded = false;
     CU(cudaStreamWaitEvent(s->aux_stream, s->ev_fork, 0));
+    CU(cudaMemsetAsync(s->st_a.p, 0, n * 4, s->aux_stream));
     k_g1_decompress<<<blocks(n, 64), 64, 0, s->aux_stream>>>((const uint32_t*)d_comm48, (const uint32_t*)nullptr, (int)n, s->aff_c.as<G1Affine>(), (G1Affine*)nullptr,
                                                               s->st_a.as<int32_t>(), (int32_t*)nullptr, 0);
     s->launches++;
     CU(cudaEventRecord(s->ev_join, s->aux_stream));
     LAUNCH(s, k_blob_check, blocks(n * KB_N, 256), 256, (const uint32_t*)d_blobs, (int)n, s->st_blob.as<int32_t>());
-    LAUNCH(s, k_challenge, blocks(n, 32), 32, (const uint32_t*)d_blobs, (const uint32_t*)d_comm48, (int)n, s->st_blob.as<int32_t>(), s->z.as<Fr>());
+    if (!s->z_ready) LAUNCH(s, k_challenge, blocks(n, 32), 32, (const uint32_t*)d_blobs, (const uint32_t*)d_comm48, (int)n, s->st_blob.as<int32_t>(), s->z.as<Fr>());
+    s->z_ready = false;
     CU(cudaStreamWaitEvent(s->stream, s->ev_join, 0));
     LAUNCH(s, k_merge_status, blocks(n, 256), 256, s->st_blob.as<int32_t>(), s->st_a.as<int32_t>(), (const int32_t*)nullptr, (int)n, d_status);
     if (int rc = prove_tail(s, (const uint32_t*)d_blobs, n, d_status, (uint32_t*)d_out48)) return rc;
@@ -702,19 +711,22 @@ static int verify_prepare(kb200_setup* s, const uint32_t* d_blobs, const uint32_
     if (int rc = s->aff_p.ensure(n * sizeof(G1Affine))) return rc;
     if (int rc = s->z.ensure(n * sizeof(Fr))) return rc;
     CU(cudaMemsetAsync(s->st_blob.p, 0, n * 4, s->stream));
-    CU(cudaMemsetAsync(s->st_a.p, 0, n * 4, s->stream));
-    CU(cudaMemsetAsync(s->st_b.p, 0, n * 4, s->stream));
     // Two latency-bound kernels that do not depend on each other run side by side: the point decompression (a 380-step
     // square-and-multiply chain per point) on the auxiliary stream, the blob check and the serial SHA-256 of each blob on the
     // main one.  The challenge only needs the blob's own status; items with a bad point are dropped after the join.
-    CU(cudaEventRecord(s->ev_fork, s->stream));
+    // (A host-buffer caller has already marked the fork point, before the blob upload it queued: fork_recorded.)
+    if (!s->fork_recorded) CU(cudaEventRecord(s->ev_fork, s->stream));
+    s->fork_recorded = false;
     CU(cudaStreamWaitEvent(s->aux_stream, s->ev_fork, 0));
+    CU(cudaMemsetAsync(s->st_a.p, 0, n * 4, s->aux_stream));
+    CU(cudaMemsetAsync(s->st_b.p, 0, n * 4, s->aux_stream));
     k_g1_decompress<<<blocks(2 * n, 64), 64, 0, s->aux_stream>>>(d_c48, d_p48, (int)n, s->aff_c.as<G1Affine>(), s->aff_p.as<G1Affine>(),
                                                                   s->st_a.as<int32_t>(), s->st_b.as<int32_t>(), 0);
     s->launches++;
     CU(cudaEventRecord(s->ev_join, s->aux_stream));
     LAUNCH(s, k_blob_check, blocks(n * KB_N, 256), 256, d_blobs, (int)n, s->st_blob.as<int32_t>());
-    LAUNCH(s, k_challenge, blocks(n, 32), 32, d_blobs, d_c48, (int)n, s->st_blob.as<int32_t>(), s->z.as<Fr>());
+    if (!s->z_ready) LAUNCH(s, k_challenge, blocks(n, 32), 32, d_blobs, d_c48, (int)n, s->st_blob.as<int32_t>(), s->z.as<Fr>());
+    s->z_ready = false;
     CU(cudaStreamWaitEvent(s->stream, s->ev_join, 0));
     LAUNCH(s, k_merge_status, blocks(n, 256), 256, s->st_blob.as<int32_t>(), s->st_a.as<int32_t>(), s->st_b.as<int32_t>(), (int)n, d_status);
     if (int rc = run_eval<false>(s, d_blobs, n, d_status)) return rc;
@@ -771,7 +783,7 @@ static int d2h(kb200_setup* s, void* dst, const void* src, size_t bytes) {
 static size_t head_items(kb200_setup* s, size_t m) { return (s->split_copy && s->msm_mode != 1 && m >= 2 * (size_t)s->ba_grid) ? (size_t)s->ba_grid : m; }
 struct CopyGuard {      // the caller's host buffer must not be read after the entry point returns, whatever the exit path
     kb200_setup* s;
-    ~CopyGuard() { if (s->copy_stream) cudaStreamSynchronize(s->copy_stream); }
+    ~CopyGuard() { if (s->copy_stream) cudaStreamSynchronize(s->copy_stream); s->z_ready = false; s->fork_recorded = false; }
 };
 // copies `bytes` into b in two pieces; the main stream waits for the first (head_bytes), ev_tail marks the second
 static int h2d_split(kb200_setup* s, DBuf& b, const uint8_t* src, size_t bytes, size_t head_bytes) {
@@ -786,6 +798,41 @@ static int h2d_split(kb200_setup* s, DBuf& b, const uint8_t* src, size_t bytes, 
         CU(cudaEventRecord(s->ev_tail, s->copy_stream));
     }
     CU(cudaStreamWaitEvent(s->stream, s->ev_head, 0));
+    return 0;
+}
+// Upload for the calls that start with the Fiat-Shamir challenge (blob proof, blob verification).  The challenge is one serial
+// SHA-256 stream per blob, ~4 ms per launch whatever the batch size, and it cannot start before the blob is there -- so the
+// blobs are copied in NCOL = 8 column pieces (bytes [j*W, (j+1)*W) of every blob, a strided 2-D copy) and the hash advances over
+// each piece while the next one is on the wire: the batch is hashed ~1 ms after its last byte arrives instead of ~4 ms.
+// Commitments must already be queued to d_c48 on the main stream.  Leaves the challenges in s->z and sets z_ready.
+#ifndef KB_NCOL
+#define KB_NCOL 8
+#endif
+static const int NCOL = KB_NCOL;     // <= 8 (ev_col)
+static const size_t HASHED_UPLOAD_MIN = 1024;     // below this the upload is shorter than one hash launch
+static int h2d_blobs_hashed(kb200_setup* s, const uint8_t* blobs, size_t n, const uint32_t* d_c48) {
+    if (int rc = s->blobs.ensure(n * KB_BLOB_BYTES)) return rc;
+    if (!s->split_copy || n < HASHED_UPLOAD_MIN) {
+        CU(cudaMemcpyAsync(s->blobs.p, blobs, n * KB_BLOB_BYTES, cudaMemcpyHostToDevice, s->stream));
+        return 0;
+    }
+    if (int rc = s->sha_state.ensure(n * 32)) return rc;
+    if (int rc = s->z.ensure(n * sizeof(Fr))) return rc;
+    const size_t W = KB_BLOB_BYTES / NCOL;
+    CU(cudaEventRecord(s->ev_fork, s->stream));      // commitments and proofs are queued: their decompression need not wait for the blobs
+    s->fork_recorded = true;
+    CU(cudaEventRecord(s->ev_copy, s->stream));
+    CU(cudaStreamWaitEvent(s->copy_stream, s->ev_copy, 0));
+    for (int j = 0; j < NCOL; j++) {
+        CU(cudaMemcpy2DAsync((char*)s->blobs.p + j * W, KB_BLOB_BYTES, blobs + j * W, KB_BLOB_BYTES, W, n, cudaMemcpyHostToDevice, s->copy_stream));
+        CU(cudaEventRecord(s->ev_col[j], s->copy_stream));
+    }
+    for (int j = 0; j < NCOL; j++) {
+        CU(cudaStreamWaitEvent(s->stream, s->ev_col[j], 0));
+        const int blk0 = (int)(j * W / 64), blk1 = (j == NCOL - 1) ? 2050 : (int)((j + 1) * W / 64);
+        LAUNCH(s, k_challenge_range, blocks(n, 32), 32, s->blobs.as<uint32_t>(), d_c48, (int)n, s->sha_state.as<uint32_t>(), s->z.as<Fr>(), blk0, blk1);
+    }
+    s->z_ready = true;
     return 0;
 }
 extern "C" int kb200_blob_to_commitment(kb200_setup* s, const uint8_t* blobs, size_t n, uint8_t* out48, int32_t* status) {
@@ -809,18 +856,19 @@ extern "C" int kb200_blob_to_commitment(kb200_setup* s, const uint8_t* blobs, si
     }
     return first;
 }
-// (No two-piece copy here: the proof path runs latency-bound per-blob kernels in front of its MSM -- the serial SHA-256 of the
+// (No head/rest copy here: the proof path runs latency-bound per-blob kernels in front of its MSM -- the serial SHA-256 of the
 // challenge takes ~4 ms whether it hashes 592 or 4096 blobs -- so running them twice costs what the hidden copy saves;
-// measured with tools/e2e_probe.py: 97.1 ms split against 95.9 ms in one piece for 4096 blobs.)
+// measured with tools/e2e_probe.py: 97.1 ms split against 95.9 ms in one piece for 4096 blobs.  Column pieces instead.)
 extern "C" int kb200_compute_blob_proof(kb200_setup* s, const uint8_t* blobs, const uint8_t* comm48, size_t n, uint8_t* out48, int32_t* status) {
     if (!s || (n && (!blobs || !comm48 || !out48))) return KB200_E_ARG;
     CU(cudaSetDevice(s->device));
+    CopyGuard guard{s};
     // kateth's order within one call is blob first, then commitment; across a batch we report the first item's error
     int first = 0;
     for (size_t off = 0; off < n; off += CHUNK) {
         size_t m = (n - off < CHUNK) ? n - off : CHUNK;
-        if (int rc = h2d(s, s->blobs, blobs + off * KB_BLOB_BYTES, m * KB_BLOB_BYTES)) return rc;
         if (int rc = h2d(s, s->c48, comm48 + off * 48, m * 48)) return rc;
+        if (int rc = h2d_blobs_hashed(s, blobs + off * KB_BLOB_BYTES, m, s->c48.as<uint32_t>())) return rc;
         if (int rc = s->out48.ensure(m * 48)) return rc;
         if (int rc = s->status.ensure(m * 4)) return rc;
         int e = kb200_compute_blob_proof_device(s, s->blobs.p, s->c48.p, m, s->out48.p, s->status.as<int32_t>());
@@ -856,6 +904,7 @@ extern "C" int kb200_verify_blob_proof_batch(kb200_setup* s, const uint8_t* blob
     if (!s || !ok || (n && (!blobs || !comm48 || !proofs48))) return KB200_E_ARG;
     CU(cudaSetDevice(s->device));
     if (n == 0) { *ok = 1; return 0; }
+    CopyGuard guard{s};
     size_t nch = (n + CHUNK - 1) / CHUNK;
     if (int rc = s->records.ensure(nch * sizeof(RlcRecord))) return rc;
     // kateth checks ALL blobs, then ALL commitments, then ALL proofs (src/kzg/setup.rs:259-271); with chunking we
@@ -863,9 +912,9 @@ extern "C" int kb200_verify_blob_proof_batch(kb200_setup* s, const uint8_t* blob
     int e_blob = 0, e_comm = 0, e_proof = 0;
     for (size_t c = 0; c < nch; c++) {
         size_t off = c * CHUNK, m = (n - off < CHUNK) ? n - off : CHUNK;
-        if (int rc = h2d(s, s->blobs, blobs + off * KB_BLOB_BYTES, m * KB_BLOB_BYTES)) return rc;
         if (int rc = h2d(s, s->c48, comm48 + off * 48, m * 48)) return rc;
         if (int rc = h2d(s, s->p48, proofs48 + off * 48, m * 48)) return rc;
+        if (int rc = h2d_blobs_hashed(s, blobs + off * KB_BLOB_BYTES, m, s->c48.as<uint32_t>())) return rc;
         if (int rc = s->status.ensure(m * 4)) return rc;
         int e = kb200_verify_blob_proof_batch_partial_device(s, s->blobs.p, s->c48.p, s->p48.p, m, off, n, (char*)s->records.p + c * sizeof(RlcRecord),
                                                              s->status.as<int32_t>());
@@ -892,9 +941,10 @@ extern "C" int kb200_verify_blob_proof_batch_partial(kb200_setup* s, const uint8
     if (!s || !d_record || (n && (!blobs || !comm48 || !proofs48))) return KB200_E_ARG;
     CU(cudaSetDevice(s->device));
     if (n > CHUNK) { snprintf(g_err, sizeof g_err, "partial: at most %zu blobs per call", CHUNK); return KB200_E_ARG; }
-    if (int rc = h2d(s, s->blobs, blobs, n * KB_BLOB_BYTES)) return rc;
+    CopyGuard guard{s};
     if (int rc = h2d(s, s->c48, comm48, n * 48)) return rc;
     if (int rc = h2d(s, s->p48, proofs48, n * 48)) return rc;
+    if (int rc = h2d_blobs_hashed(s, blobs, n, s->c48.as<uint32_t>())) return rc;
     if (int rc = s->status.ensure(n ? n * 4 : 16)) return rc;
     int e = kb200_verify_blob_proof_batch_partial_device(s, s->blobs.p, s->c48.p, s->p48.p, n, index_offset, n_total, d_record, s->status.as<int32_t>());
     if (e < 0) return e;

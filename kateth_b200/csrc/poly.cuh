@@ -104,6 +104,70 @@ __global__ void k_challenge(const uint32_t* __restrict__ blobs, const uint32_t* 
     z_out[b] = z;
 }
 
+// The same hash over a range [blk0, blk1) of the 2,050 blocks of the preimage, with the chaining value parked in `state`
+// (8 words per blob) between launches.  The host-buffer entry points upload a batch of blobs in column pieces (bytes
+// [j*W, (j+1)*W) of every blob) and hash each piece while the next one crosses PCIe: block k needs blob bytes up to 64k + 32.
+// blk1 == 2050 finishes (both commitment blocks, reduction mod r); otherwise blk1 <= 2048.
+__global__ void k_challenge_range(const uint32_t* __restrict__ blobs, const uint32_t* __restrict__ comm48, int n, uint32_t* __restrict__ state,
+                                  Fr* __restrict__ z_out, int blk0, int blk1) {
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= n) return;
+    const uint4* bp = reinterpret_cast<const uint4*>(blobs + (size_t)b * (KB_N * 8));
+    uint32_t h[8], w[16];
+    int k = blk0;
+    if (k == 0) {
+        sha256_init(h);
+        w[0] = 0x4653424c; w[1] = 0x4f425645; w[2] = 0x52494659; w[3] = 0x5f56315f;   // "FSBLOBVERIFY_V1_"
+        w[4] = 0; w[5] = 0; w[6] = 0; w[7] = KB_N;
+        uint4 c0 = __ldg(bp), c1 = __ldg(bp + 1);
+        w[8] = bswap32(c0.x); w[9] = bswap32(c0.y); w[10] = bswap32(c0.z); w[11] = bswap32(c0.w);
+        w[12] = bswap32(c1.x); w[13] = bswap32(c1.y); w[14] = bswap32(c1.z); w[15] = bswap32(c1.w);
+        sha256_block(h, w);
+        k = 1;
+    } else {
+#pragma unroll
+        for (int q = 0; q < 8; q++) h[q] = state[(size_t)q * n + b];
+    }
+    const int kend = blk1 < 2048 ? blk1 : 2048;
+#pragma unroll 1
+    for (; k < kend; k++) {
+        const uint4* p = bp + (4 * k - 2);
+        uint4 v0 = __ldg(p), v1 = __ldg(p + 1), v2 = __ldg(p + 2), v3 = __ldg(p + 3);
+        w[0] = bswap32(v0.x); w[1] = bswap32(v0.y); w[2] = bswap32(v0.z); w[3] = bswap32(v0.w);
+        w[4] = bswap32(v1.x); w[5] = bswap32(v1.y); w[6] = bswap32(v1.z); w[7] = bswap32(v1.w);
+        w[8] = bswap32(v2.x); w[9] = bswap32(v2.y); w[10] = bswap32(v2.z); w[11] = bswap32(v2.w);
+        w[12] = bswap32(v3.x); w[13] = bswap32(v3.y); w[14] = bswap32(v3.z); w[15] = bswap32(v3.w);
+        sha256_block(h, w);
+    }
+    if (blk1 <= 2048) {
+#pragma unroll
+        for (int q = 0; q < 8; q++) state[(size_t)q * n + b] = h[q];
+        return;
+    }
+    {
+        const uint4* p = bp + (4 * 2048 - 2);
+        uint4 v0 = __ldg(p), v1 = __ldg(p + 1);
+        const uint32_t* cp = comm48 + (size_t)b * 12;
+        w[0] = bswap32(v0.x); w[1] = bswap32(v0.y); w[2] = bswap32(v0.z); w[3] = bswap32(v0.w);
+        w[4] = bswap32(v1.x); w[5] = bswap32(v1.y); w[6] = bswap32(v1.z); w[7] = bswap32(v1.w);
+#pragma unroll
+        for (int q = 0; q < 8; q++) w[8 + q] = bswap32(cp[q]);
+        sha256_block(h, w);
+#pragma unroll
+        for (int q = 0; q < 4; q++) w[q] = bswap32(cp[8 + q]);
+        w[4] = 0x80000000u;
+#pragma unroll
+        for (int q = 5; q < 15; q++) w[q] = 0;
+        w[15] = 131152u * 8u;
+        sha256_block(h, w);
+    }
+    Fr z;
+#pragma unroll
+    for (int q = 0; q < 8; q++) z.l[7 - q] = h[q];
+    fr_reduce_256(z);
+    z_out[b] = z;
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // Evaluation, phase 1.  CTA per blob, EV_THREADS threads, EV_PER = 4096/EV_THREADS denominators per thread
 // (element index i = k*EV_THREADS + tid).  d_i = z - w_i; if some d_m == 0 (z in the domain, poly.rs:14-18) the

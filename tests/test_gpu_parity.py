@@ -434,6 +434,11 @@ def test_host_batches_copied_in_two_pieces(engine_setup, oracle_setup):
     for k, i in enumerate(good):
         assert proofs[48 * k:48 * k + 48] == wantp[i % len(base)], i
     assert engine_setup.verify_blob_proof_batch_concat(gcat, gcomm, proofs, len(good)) is True
+    # proof and verify calls of this size upload the blobs in column pieces and hash each piece as it lands (h2d_blobs_hashed):
+    # a flipped low byte in any piece of any blob must change that blob's challenge, hence the verdict
+    for item, byte in ((0, 31), (700, 32768 + 63), (1249, 65536 + 95), (3, 131071)):
+        gb = bytearray(gcat); gb[131072 * item + byte] ^= 1
+        assert engine_setup.verify_blob_proof_batch_concat(bytes(gb), gcomm, proofs, len(good)) is False, (item, byte)
     # a bad commitment in the tail is reported in the status of its own item only
     bc = bytearray(gcomm); bc[48 * 1000:48 * 1000 + 48] = bytes([0xff] * 48)
     _, st3 = engine_setup.blob_proof_many(gcat, bytes(bc), len(good))
