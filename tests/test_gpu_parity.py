@@ -460,3 +460,38 @@ def test_txt_setup_gives_the_same_engine(tmp_path):
         assert s.verify_blob_proof(vb[2], c, pr) is True
     finally:
         s.close()
+
+
+def test_full_size_batch_checksum_of_checksums(engine_setup, oracle_setup):
+    """BASELINE configs[2] at its full size, 4096 DISTINCT blobs (bench.py's generator), through the host-buffer C ABI, pinned by
+    size-independent properties: (1) linearity -- the sum of the 4096 commitments is the commitment of the element-wise sum
+    of the blobs mod r (a checksum of checksums: any wrong MSM in the batch breaks it); (2) commit -> prove -> batch-verify
+    round trip is true, and false once one proof or one blob byte is changed; (3) a seeded sample equals the oracle."""
+    from oracle import oracle as O
+    sys.path.insert(0, ROOT)
+    import bench
+    n = 4096
+    flat = bench.synth_blobs(n, 0x4b5a4700 + 77)
+    cat = flat.tobytes()
+    engine_setup.set_msm_mode(0)
+    comm, st = engine_setup.blob_to_commitment_many(cat, n)
+    assert st == [0] * n and engine_setup.info()["last_msm_batch_affine"] == 1
+    # (1) element-wise sum of the blobs: per 32-bit big-endian limb in uint64 (4096 x 2^32 < 2^64), then carried in Python
+    limbs = flat.view(">u4").reshape(n, 4096, 8).astype(np.uint64).sum(axis=0)
+    sum_blob = b"".join((sum(int(limbs[e, k]) << (32 * (7 - k)) for k in range(8)) % R).to_bytes(32, "big") for e in range(4096))
+    cs = [comm[48 * i:48 * i + 48] for i in range(n)]
+    assert len(set(cs)) == n
+    assert O.g1_lincomb(cs, [(1).to_bytes(32, "big")] * n) == engine_setup.blob_to_commitment(sum_blob) == oracle_setup.blob_to_commitment(sum_blob)
+    # (2) round trip
+    proofs, st2 = engine_setup.blob_proof_many(cat, comm, n)
+    assert st2 == [0] * n
+    assert engine_setup.verify_blob_proof_batch_concat(cat, comm, proofs, n) is True
+    bad = bytearray(proofs); bad[48 * 4095:48 * 4096] = proofs[0:48]
+    assert engine_setup.verify_blob_proof_batch_concat(cat, comm, bytes(bad), n) is False
+    gb = bytearray(cat); gb[131072 * 2048 + 131071] ^= 1
+    assert engine_setup.verify_blob_proof_batch_concat(bytes(gb), comm, proofs, n) is False
+    # (3) sample against the oracle
+    for i in (0, 591, 592, 2047, 4095):
+        b = cat[131072 * i:131072 * (i + 1)]
+        assert cs[i] == oracle_setup.blob_to_commitment(b), i
+        assert proofs[48 * i:48 * i + 48] == oracle_setup.blob_proof(b, cs[i]), i
