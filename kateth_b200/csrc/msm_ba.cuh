@@ -182,8 +182,27 @@ struct BaRef { const uint4* p; int stride; bool neg, zero; };
 // what a thread needs to find the operands of its current unit
 struct BaCtx { const uint4* tab; const uint32_t* dg; uint4* pts; int base0; };
 
+// KB200_TAB_LD (A/B switch, default off): table entries (stride 1) are read once per pass with no reuse in L1, so they can be
+// loaded without allocating there (1: ld.global.nc.L1::no_allocate, 2: ld.global.cs) and leave L1 to the scratch area.
+#if defined(KB200_TAB_LD) && KB200_TAB_LD > 0
+__device__ __forceinline__ uint4 ba_ld_tab(const uint4* p) {
+    uint4 v;
+#if KB200_TAB_LD == 1
+    asm("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+#else
+    asm("ld.global.cs.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+#endif
+    return v;
+}
+#endif
 __device__ __forceinline__ void ba_ld(Fp& r, const uint4* p, int stride) {
+#if defined(KB200_TAB_LD) && KB200_TAB_LD > 0
+    uint4 a, b, c;
+    if (stride == 1) { a = ba_ld_tab(p); b = ba_ld_tab(p + 1); c = ba_ld_tab(p + 2); }
+    else { a = p[0]; b = p[stride]; c = p[2 * stride]; }
+#else
     uint4 a = p[0], b = p[stride], c = p[2 * stride];
+#endif
     r.l[0] = a.x; r.l[1] = a.y; r.l[2] = a.z; r.l[3] = a.w; r.l[4] = b.x; r.l[5] = b.y; r.l[6] = b.z; r.l[7] = b.w;
     r.l[8] = c.x; r.l[9] = c.y; r.l[10] = c.z; r.l[11] = c.w;
 }
