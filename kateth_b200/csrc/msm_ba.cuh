@@ -182,9 +182,10 @@ struct BaRef { const uint4* p; int stride; bool neg, zero; };
 // what a thread needs to find the operands of its current unit
 struct BaCtx { const uint4* tab; const uint32_t* dg; uint4* pts; int base0; };
 
-// KB200_TAB_LD (A/B switch, default off): table entries (stride 1) are read once per pass with no reuse in L1, so they can be
-// loaded without allocating there (1: ld.global.nc.L1::no_allocate, 2: ld.global.cs) and leave L1 to the scratch area.
-#if defined(KB200_TAB_LD) && KB200_TAB_LD > 0
+// KB200_TAB_LD (A/B switch, default off): other ways of loading a table entry (stride 1) -- 1: ld.global.nc.L1::no_allocate,
+// 2: ld.global.cs, 3: one 256-bit + one 128-bit load per coordinate.  All three measured slower than the plain loads: L1 is
+// what merges the six 16-byte loads of an entry into three sector requests.
+#if defined(KB200_TAB_LD) && KB200_TAB_LD > 0 && KB200_TAB_LD < 3
 __device__ __forceinline__ uint4 ba_ld_tab(const uint4* p) {
     uint4 v;
 #if KB200_TAB_LD == 1
@@ -196,7 +197,19 @@ __device__ __forceinline__ uint4 ba_ld_tab(const uint4* p) {
 }
 #endif
 __device__ __forceinline__ void ba_ld(Fp& r, const uint4* p, int stride) {
-#if defined(KB200_TAB_LD) && KB200_TAB_LD > 0
+#if defined(KB200_TAB_LD) && KB200_TAB_LD == 3
+    // 3: a coordinate (48 bytes) of a table entry as one 256-bit and one 128-bit load (x starts a 32-byte sector, y ends one)
+    uint4 a, b, c;
+    if (stride == 1) {
+        if (((size_t)p & 31) == 0) {
+            asm("ld.global.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];" : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w) : "l"(p));
+            c = p[2];
+        } else {
+            a = p[0];
+            asm("ld.global.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];" : "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w), "=r"(c.x), "=r"(c.y), "=r"(c.z), "=r"(c.w) : "l"(p + 1));
+        }
+    } else { a = p[0]; b = p[stride]; c = p[2 * stride]; }
+#elif defined(KB200_TAB_LD) && KB200_TAB_LD > 0
     uint4 a, b, c;
     if (stride == 1) { a = ba_ld_tab(p); b = ba_ld_tab(p + 1); c = ba_ld_tab(p + 2); }
     else { a = p[0]; b = p[stride]; c = p[2 * stride]; }
