@@ -20,7 +20,9 @@
  *   - `*_device` variants take device pointers (data already resident in HBM, 16-byte aligned) and run on the
  *     stream set by kb200_set_stream (default: the legacy default stream); they return after enqueueing AND
  *     synchronising that stream unless noted.
- *   - no function aborts or throws across the ABI.  A handle may be used from one host thread at a time.
+ *   - no function aborts or throws across the ABI.
+ *   - a handle may be shared by any number of host threads (kateth's Setup is Send + Sync, src/kzg/setup.rs:84-275): calls on one
+ *     handle are serialised on an internal lock -- one batch call already fills the GPU; kb200_last_error is per thread.
  *   - there is NO CPU fallback: without a CUDA device kb200_setup_load_* returns KB200_E_CUDA.
  */
 #ifndef KATETH_B200_H
@@ -37,7 +39,7 @@ extern "C" {
 #define KB200_BYTES_PER_G1 48
 #define KB200_BYTES_PER_G2 96
 #define KB200_BYTES_PER_SCALAR 32
-#define KB200_RECORD_BYTES 320 /* per-GPU partial of batch verification: 3 affine G1 sums + 1 Fr */
+#define KB200_RECORD_BYTES 336 /* per-GPU partial of batch verification: 3 affine G1 sums + 1 Fr + the shard's first blob / commitment / proof error */
 
 /* status codes */
 #define KB200_OK 0
@@ -84,6 +86,11 @@ int kb200_free_pinned(void* p);
 int kb200_blob_to_commitment(kb200_setup* s, const uint8_t* blobs, size_t n, uint8_t* out48, int32_t* status);
 int kb200_blob_to_commitment_device(kb200_setup* s, const void* d_blobs, size_t n, void* d_out48, int32_t* d_status);
 
+/* Blob::from_slice alone (src/blob.rs:26-37) over n full-length blobs: status[i] = 0 or KB200_E_INVALID_FIELD_ELEMENT; returns the first
+ * non-zero status.  For wrappers whose callers pass blobs of unequal byte lengths (kateth: `impl AsRef<[u8]>` per blob) and that must
+ * report the first error in blob order -- an element error of blob 3 before the length error of blob 7. */
+int kb200_check_blobs(kb200_setup* s, const uint8_t* blobs, size_t n, int32_t* status);
+
 /* ---- Setup::blob_proof (src/kzg/setup.rs:177-183) + compress ---- */
 int kb200_compute_blob_proof(kb200_setup* s, const uint8_t* blobs, const uint8_t* commitments48, size_t n, uint8_t* out48, int32_t* status);
 int kb200_compute_blob_proof_device(kb200_setup* s, const void* d_blobs, const void* d_commitments48, size_t n, void* d_out48, int32_t* d_status);
@@ -108,11 +115,15 @@ int kb200_verify_blob_proof_batch_device(kb200_setup* s, const void* d_blobs, co
                                          int32_t* d_status);
 
 /* ---- multi-GPU batch verification: each rank computes the partial of its contiguous shard
- *      [index_offset, index_offset + n_local) of a batch of n_total, the KB200_RECORD_BYTES records are exchanged with
- *      one all-gather (NCCL over NVLink, done by the caller), and any rank finishes.  d_record: device memory. ---- */
+ *      [index_offset, index_offset + n_local) of a batch of n_total (n_local may be 0), the KB200_RECORD_BYTES records are
+ *      exchanged with one all-gather (NCCL over NVLink: kb200_group_* below does it inside the library; a caller with its own
+ *      communicator may do it itself), and any rank finishes.  d_record: device memory.
+ *      A shard with an invalid blob / commitment / proof returns that error AND writes it into its record, the failing items
+ *      contribute nothing to the sums, and kb200_verify_batch_finish_device returns -- on every rank -- the error kateth would:
+ *      the first blob error in rank order, else the first commitment error, else the first proof error. ---- */
 int kb200_verify_blob_proof_batch_partial_device(kb200_setup* s, const void* d_blobs, const void* d_commitments48, const void* d_proofs48,
                                                  size_t n_local, size_t index_offset, size_t n_total, void* d_record, int32_t* d_status);
-/* Same with the shard's inputs in host memory (n_local <= 4096); the record is still written to device memory. */
+/* Same with the shard's inputs in host memory (any n_local; blobs are uploaded in chunks); the record is still written to device memory. */
 int kb200_verify_blob_proof_batch_partial(kb200_setup* s, const uint8_t* blobs, const uint8_t* commitments48, const uint8_t* proofs48, size_t n_local,
                                           size_t index_offset, size_t n_total, void* d_record, int32_t* status);
 /* d_records: n_records x KB200_RECORD_BYTES in device memory. */
@@ -124,7 +135,8 @@ int kb200_last_pairing_operands(kb200_setup* s, uint8_t lhs48[48], uint8_t rhs48
  *      mod r and weights [r, r, r^2, ...] (src/kzg/setup.rs:127-136, src/bls.rs:169-187) -- bit-for-bit parity with the reference.
  *      1 = the consensus-spec verify_kzg_proof_batch transcript: r = hash_to_bls_field(domain | u64(4096) | u64(n) |
  *      (commitment | z | y | proof) per item), weights [1, r, r^2, ...]; sound against adaptive inputs.  Verdicts agree on every
- *      test vector.  In mode 1 a batch must be checked in one call (the sharded *_partial entry points return KB200_E_ARG). ---- */
+ *      test vector.  In mode 1 a batch must be checked in one call of any size (the sharded *_partial entry points return
+ *      KB200_E_ARG: the transcript needs every item in one place). ---- */
 int kb200_set_batch_challenge(kb200_setup* s, int mode);
 
 /* ---- introspection ---- */

@@ -10,6 +10,7 @@
 #include <string>
 #include <vector>
 #include <chrono>
+#include <mutex>
 
 #include "../../include/kateth_b200.h"
 #include "verify.cuh"
@@ -45,6 +46,10 @@ struct DBuf {
 };
 
 struct kb200_setup {
+    // kateth's Setup is Send + Sync (immutable tables, &self methods, src/kzg/setup.rs:84-275).  The tables here are immutable too, but
+    // every call uses the handle's workspace and streams, so concurrent callers are serialised on this lock (recursive: the
+    // host-buffer entry points call the device ones).
+    std::recursive_mutex mu;
     int device = 0, sm_count = 148;
     cudaStream_t stream = 0;
     G1Affine* d_bases = nullptr;     // g1_lagrange_brp, affine Montgomery   (src/kzg/setup.rs:39)
@@ -83,6 +88,7 @@ struct kb200_setup {
     uint64_t prof_items = 0;            // MSMs (4096-point) covered by the recorded launches
 };
 
+#define LOCK(s) std::lock_guard<std::recursive_mutex> lock_((s)->mu)
 #define LAUNCH(s, kern, grid, block, ...)                   \
     do {                                                    \
         kern<<<grid, block, 0, (s)->stream>>>(__VA_ARGS__); \
@@ -209,6 +215,13 @@ static int json_hex_array(const std::string& doc, const char* key, std::vector<s
 
 static int first_nonzero(const std::vector<int32_t>& v) { for (int32_t x : v) if (x) return x; return 0; }
 
+// scoped device allocation: freed on every exit path
+struct DevTmp {
+    void* p = nullptr;
+    ~DevTmp() { if (p) cudaFree(p); }
+    template <class T> T* as() { return reinterpret_cast<T*>(p); }
+};
+
 static int build_setup(kb200_setup* s, const uint8_t* g1, const uint8_t* g2, int window_bits) {
     auto t0 = std::chrono::steady_clock::now();
     CU(cudaSetDevice(s->device));
@@ -216,22 +229,22 @@ static int build_setup(kb200_setup* s, const uint8_t* g1, const uint8_t* g2, int
     s->sm_count = prop.multiProcessorCount;
     if (int rc = init_consts()) return rc;
     // G1: decompress + subgroup-check the 4096 Lagrange points on the GPU (src/kzg/setup.rs:59-65)
-    uint32_t* d_in; G1Affine* d_pts; int32_t* d_st;
-    CU(cudaMalloc(&d_in, KB_N * 48)); CU(cudaMalloc(&d_pts, KB_N * sizeof(G1Affine))); CU(cudaMalloc(&d_st, KB_N * 4));
+    DevTmp t_in, t_pts, t_st, t_scratch;
+    CU(cudaMalloc(&t_in.p, KB_N * 48)); CU(cudaMalloc(&t_pts.p, KB_N * sizeof(G1Affine))); CU(cudaMalloc(&t_st.p, KB_N * 4));
+    uint32_t* d_in = t_in.as<uint32_t>(); G1Affine* d_pts = t_pts.as<G1Affine>(); int32_t* d_st = t_st.as<int32_t>();
     CU(cudaMemcpy(d_in, g1, KB_N * 48, cudaMemcpyHostToDevice));
     CU(cudaMemset(d_st, 0, KB_N * 4));
     LAUNCH(s, k_g1_decompress, KB_N / 64, 64, d_in, (const uint32_t*)nullptr, KB_N, d_pts, (G1Affine*)nullptr, d_st, (int32_t*)nullptr, 0);
     std::vector<int32_t> st(KB_N);
     CU(cudaMemcpy(st.data(), d_st, KB_N * 4, cudaMemcpyDeviceToHost));
-    cudaFree(d_in); cudaFree(d_st);
-    if (int e = first_nonzero(st)) { cudaFree(d_pts); return e; }
+    if (int e = first_nonzero(st)) return e;
     CU(cudaMalloc(&s->d_bases, KB_N * sizeof(G1Affine)));
     LAUNCH(s, k_brp_permute, KB_N / 256, 256, d_pts, s->d_bases);
     // G2: all 65 points are validated on the host (src/kzg/setup.rs:68-72); only [1] is ever used (:91,:158)
     host::G2A tau, gen;
     for (int i = 0; i < 65; i++) {
         host::G2A q; int e = host::g2_decompress(q, g2 + 96 * i);
-        if (e) { cudaFree(d_pts); return e; }
+        if (e) return e;
         if (i == 1) tau = q;
     }
     host::g2_generator(gen);
@@ -249,7 +262,7 @@ static int build_setup(kb200_setup* s, const uint8_t* g1, const uint8_t* g2, int
     int glv = 0;
     if (c == 16) glv = 1;
     else if (c >= 100) { glv = 1; c -= 100; }
-    if (c < 4 || c > (glv ? 16 : 15)) { cudaFree(d_pts); return KB200_E_ARG; }
+    if (c < 4 || c > (glv ? 16 : 15)) return KB200_E_ARG;
     int nwin = ((glv ? 128 : 255) + c - 1) / c;
     int dlast;
     {
@@ -271,9 +284,9 @@ static int build_setup(kb200_setup* s, const uint8_t* g1, const uint8_t* g2, int
     if (group > nwin - 1) group = nwin - 1;
     size_t scratch_rows = (size_t)group * win_rows;
     if ((size_t)dlast > scratch_rows) scratch_rows = dlast;
-    uint4* scratch;
     CU(cudaMalloc(&s->d_table, bytes));
-    CU(cudaMalloc(&scratch, scratch_rows * row_bytes));
+    CU(cudaMalloc(&t_scratch.p, scratch_rows * row_bytes));
+    uint4* scratch = t_scratch.as<uint4>();
     for (int j0 = 0; j0 < nwin;) {
         int cnt = (j0 == nwin - 1) ? 1 : ((nwin - 1 - j0 < group) ? nwin - 1 - j0 : group);
         LAUNCH(s, k_table_build, (KB_N * cnt + 31) / 32, 32, s->d_table, scratch, s->d_bases, c, nwin, dlast, j0, cnt);
@@ -281,7 +294,6 @@ static int build_setup(kb200_setup* s, const uint8_t* g1, const uint8_t* g2, int
     }
     CU(cudaStreamSynchronize(s->stream));
     CU(cudaGetLastError());
-    cudaFree(scratch); cudaFree(d_pts);
     s->tab.data = s->d_table; s->tab.c = c; s->tab.nwin = nwin; s->tab.dlast = dlast; s->tab.glv = glv;
     {   // batch-affine MSM: signed-digit offset, persistent grid, work counter
         memset(&s->ba_off, 0, sizeof s->ba_off);
@@ -409,25 +421,29 @@ extern "C" int kb200_free_pinned(void* p) {
     if (p) CU(cudaFreeHost(p));
     return 0;
 }
-extern "C" int kb200_set_stream(kb200_setup* s, void* stream) { if (!s) return KB200_E_ARG; s->stream = (cudaStream_t)stream; return 0; }
+extern "C" int kb200_set_stream(kb200_setup* s, void* stream) { if (!s) return KB200_E_ARG; LOCK(s); s->stream = (cudaStream_t)stream; return 0; }
 extern "C" int kb200_set_batch_challenge(kb200_setup* s, int mode) {
     if (!s || mode < 0 || mode > 1) return KB200_E_ARG;
+    LOCK(s);
     s->challenge_mode = mode;
     return 0;
 }
 extern "C" int kb200_set_msm_mode(kb200_setup* s, int mode) {
     if (!s || mode < 0 || mode > 2) return KB200_E_ARG;
+    LOCK(s);
     s->msm_mode = mode;
     return 0;
 }
 extern "C" int kb200_set_profiling(kb200_setup* s, int on) {
     if (!s) return KB200_E_ARG;
+    LOCK(s);
     s->prof = on != 0; s->prof_used = 0; s->prof_items = 0;
     return 0;
 }
 // total device time (ms) of the k_msm launches since the last call / set_profiling, their count and the MSMs they covered
 extern "C" int kb200_get_msm_profile(kb200_setup* s, double* ms_total, uint64_t* launches, uint64_t* msms) {
     if (!s || !ms_total || !launches || !msms) return KB200_E_ARG;
+    LOCK(s);
     CU(cudaSetDevice(s->device));
     CU(cudaStreamSynchronize(s->stream));
     double tot = 0;
@@ -438,6 +454,7 @@ extern "C" int kb200_get_msm_profile(kb200_setup* s, double* ms_total, uint64_t*
 }
 extern "C" int kb200_get_info(kb200_setup* s, kb200_info* info) {
     if (!s || !info) return KB200_E_ARG;
+    LOCK(s);
     info->window_bits = s->tab.c; info->windows = s->tab.nwin; info->table_bytes = s->table_bytes; info->kernel_launches = s->launches;
     info->device = s->device; info->sm_count = s->sm_count; info->setup_seconds = s->setup_seconds;
     info->last_msm_batch_affine = s->last_ba; info->ba_grid = s->ba_grid; info->glv = s->tab.glv;
@@ -490,17 +507,16 @@ static int run_msm(kb200_setup* s, const uint32_t* d_scalars, size_t n, const in
     LAUNCH(s, k_msm_finish, blocks(n, FIN_WARPS), 32 * FIN_WARPS, s->partials.as<G1>(), S, (int)n, d_status, d_out48, (G1Affine*)nullptr);
     return 0;
 }
-// evaluation (and optionally quotient) of n blobs at z (canonical limbs in s->z)
+// evaluation (and optionally quotient) of n blobs at the canonical points d_z; y -> d_y (canonical)
 template <bool WANT_Q>
-static int run_eval(kb200_setup* s, const uint32_t* d_blobs, size_t n, const int32_t* d_status) {
+static int run_eval(kb200_setup* s, const uint32_t* d_blobs, size_t n, const int32_t* d_status, const Fr* d_z, Fr* d_y) {
     if (int rc = s->prod.ensure(n * sizeof(Fr))) return rc;
     if (int rc = s->indom.ensure(n * 4)) return rc;
-    if (int rc = s->y.ensure(n * sizeof(Fr))) return rc;
     if (WANT_Q) if (int rc = s->q.ensure(n * (size_t)KB_BLOB_BYTES)) return rc;
-    LAUNCH(s, k_eval_prod, (unsigned)n, EV_THREADS, s->z.as<Fr>(), s->d_roots, (int)n, s->prod.as<Fr>(), s->indom.as<int32_t>());
+    LAUNCH(s, k_eval_prod, (unsigned)n, EV_THREADS, d_z, s->d_roots, (int)n, s->prod.as<Fr>(), s->indom.as<int32_t>());
     LAUNCH(s, k_eval_inv, blocks(n, 32), 32, s->prod.as<Fr>(), (int)n);
-    LAUNCH(s, (k_eval_finish<WANT_Q>), (unsigned)n, EV_THREADS, d_blobs, s->z.as<Fr>(), s->d_roots, s->prod.as<Fr>(), s->indom.as<int32_t>(), d_status,
-           (int)n, s->y.as<Fr>(), s->q.as<uint32_t>());
+    LAUNCH(s, (k_eval_finish<WANT_Q>), (unsigned)n, EV_THREADS, d_blobs, d_z, s->d_roots, s->prod.as<Fr>(), s->indom.as<int32_t>(), d_status,
+           (int)n, d_y, s->q.as<uint32_t>());
     return 0;
 }
 static int fetch_status(kb200_setup* s, const int32_t* d_status, size_t n, std::vector<int32_t>& h) {
@@ -514,6 +530,7 @@ static int fetch_status(kb200_setup* s, const int32_t* d_status, size_t n, std::
 
 extern "C" int kb200_blob_to_commitment_device(kb200_setup* s, const void* d_blobs, size_t n, void* d_out48, int32_t* d_status) {
     if (!s || (n && (!d_blobs || !d_out48 || !d_status))) return KB200_E_ARG;
+    LOCK(s);
     CU(cudaSetDevice(s->device));
     if (n == 0) return 0;
     CU(cudaMemsetAsync(d_status, 0, n * 4, s->stream));
@@ -523,25 +540,20 @@ extern "C" int kb200_blob_to_commitment_device(kb200_setup* s, const void* d_blo
     return first_nonzero(h);
 }
 
-// shared tail of blob_proof / proof: z in s->z, status final -> quotient -> MSM -> compressed proofs
+// shared tail of blob_proof / proof: z in s->z (n items), status final -> quotient -> MSM -> compressed proofs; y is left in s->out32
 static int prove_tail(kb200_setup* s, const uint32_t* d_blobs, size_t n, int32_t* d_status, uint32_t* d_out48) {
+    if (int rc = s->out32.ensure(n * sizeof(Fr))) return rc;       // before the loop: growing it would drop the earlier chunks' y
     for (size_t off = 0; off < n; off += CHUNK) {
         size_t m = (n - off < CHUNK) ? n - off : CHUNK;
-        // run_eval works on chunk-local arrays: shift the inputs
-        DBuf zsave = s->z; s->z.p = (char*)zsave.p + off * sizeof(Fr);
-        int rc = run_eval<true>(s, d_blobs + off * (KB_N * 8), m, d_status + off);
-        s->z = zsave;
-        if (rc) return rc;
-        if (int rc2 = run_msm<1>(s, s->q.as<uint32_t>(), m, d_status + off, d_out48 + off * 12)) return rc2;
-        // keep y for the caller (proof-at-z returns it)
-        if (int rc3 = s->out32.ensure(n * sizeof(Fr))) return rc3;
-        CU(cudaMemcpyAsync((char*)s->out32.p + off * sizeof(Fr), s->y.p, m * sizeof(Fr), cudaMemcpyDeviceToDevice, s->stream));
+        if (int rc = run_eval<true>(s, d_blobs + off * (KB_N * 8), m, d_status + off, s->z.as<Fr>() + off, s->out32.as<Fr>() + off)) return rc;
+        if (int rc = run_msm<1>(s, s->q.as<uint32_t>(), m, d_status + off, d_out48 + off * 12)) return rc;
     }
     return 0;
 }
 
 extern "C" int kb200_compute_blob_proof_device(kb200_setup* s, const void* d_blobs, const void* d_comm48, size_t n, void* d_out48, int32_t* d_status) {
     if (!s || (n && (!d_blobs || !d_comm48 || !d_out48 || !d_status))) return KB200_E_ARG;
+    LOCK(s);
     CU(cudaSetDevice(s->device));
     if (n == 0) return 0;
     if (int rc = s->st_blob.ensure(n * 4)) return rc;
@@ -574,6 +586,7 @@ extern "C" int kb200_compute_blob_proof_device(kb200_setup* s, const void* d_blo
 
 extern "C" int kb200_compute_proof_device(kb200_setup* s, const void* d_blobs, const void* d_z32, size_t n, void* d_out48, void* d_y32, int32_t* d_status) {
     if (!s || (n && (!d_blobs || !d_z32 || !d_out48 || !d_y32 || !d_status))) return KB200_E_ARG;
+    LOCK(s);
     CU(cudaSetDevice(s->device));
     if (n == 0) return 0;
     if (int rc = s->st_blob.ensure(n * 4)) return rc;
@@ -594,7 +607,6 @@ extern "C" int kb200_compute_proof_device(kb200_setup* s, const void* d_blobs, c
 }
 
 // ---- verification ----
-// RLC partial over n items whose affine proofs/commitments are in s->aff_p / s->aff_c and z, y in s->z / s->y.
 // host SHA-256 (only for the optional consensus-spec batch challenge: one sequential hash over the whole transcript)
 static void host_sha256(const uint8_t* data, size_t len, uint8_t out[32]) {
     static const uint32_t Kc[64] = {
@@ -635,12 +647,30 @@ static void host_sha256(const uint8_t* data, size_t len, uint8_t out[32]) {
     for (int i = 0; i < 8; i++) { out[4 * i] = h[i] >> 24; out[4 * i + 1] = h[i] >> 16; out[4 * i + 2] = h[i] >> 8; out[4 * i + 3] = h[i]; }
 }
 
-// RLC sums of a shard.  d_c48 / d_p48 (the compressed inputs, device) are only read in consensus-spec challenge mode.
-static int run_rlc(kb200_setup* s, size_t n, size_t index_offset, size_t n_total, int raw, RlcRecord* d_record, const uint32_t* d_c48 = nullptr,
-                   const uint32_t* d_p48 = nullptr) {
-    int nb = blocks(2 * n, RLC_THREADS);          // two threads per term (GLV halves)
-    if (int rc = s->rlc_part.ensure((size_t)3 * nb * sizeof(G1))) return rc;
-    if (int rc = s->rlc_s.ensure((size_t)nb * sizeof(Fr))) return rc;
+
+// first error of each class over the items of a call, in kateth's order (src/kzg/setup.rs:259-271)
+struct VErr {
+    int blob = 0, comm = 0, proof = 0;
+    int first() const { return blob ? blob : (comm ? comm : proof); }
+};
+// workspace of a verification call over n items (must precede verify_prepare: growing a buffer drops its contents)
+static int verify_reserve(kb200_setup* s, size_t n) {
+    if (n == 0) n = 1;
+    DBuf* st[] = {&s->st_blob, &s->st_a, &s->st_b};
+    for (DBuf* b : st) if (int rc = b->ensure(n * 4)) return rc;
+    if (int rc = s->aff_c.ensure(n * sizeof(G1Affine))) return rc;
+    if (int rc = s->aff_p.ensure(n * sizeof(G1Affine))) return rc;
+    if (int rc = s->z.ensure(n * sizeof(Fr))) return rc;
+    return s->y.ensure(n * sizeof(Fr));
+}
+
+// RLC sums of a shard of n items (affine points in s->aff_p / s->aff_c, z and y in s->z / s->y, per-item status in d_status or null)
+// -> one record.  d_c48 / d_p48 (the compressed inputs, device) are only read in consensus-spec challenge mode.
+static int run_rlc(kb200_setup* s, size_t n, size_t index_offset, size_t n_total, int raw, RlcRecord* d_record, const int32_t* d_status,
+                   const uint32_t* d_c48 = nullptr, const uint32_t* d_p48 = nullptr) {
+    int nb = blocks(2 * n, RLC_THREADS);          // two threads per term (GLV halves); 0 for an empty shard
+    if (int rc = s->rlc_part.ensure((size_t)3 * (nb ? nb : 1) * sizeof(G1))) return rc;
+    if (int rc = s->rlc_s.ensure((size_t)(nb ? nb : 1) * sizeof(Fr))) return rc;
     if (int rc = s->rmont.ensure(sizeof(Fr))) return rc;
     const int spec = (!raw && s->challenge_mode == 1) ? 1 : 0;
     if (spec) {
@@ -665,9 +695,17 @@ static int run_rlc(kb200_setup* s, size_t n, size_t index_offset, size_t n_total
     } else if (!raw) {
         LAUNCH(s, k_batch_r, 1, 1, (uint32_t)n_total, s->rmont.as<Fr>());
     }
-    LAUNCH(s, k_rlc, dim3(nb, 3), RLC_THREADS, s->aff_p.as<G1Affine>(), s->aff_c.as<G1Affine>(), s->z.as<Fr>(), s->y.as<Fr>(), (int)n, (uint32_t)index_offset,
-           s->rmont.as<Fr>(), raw, spec, s->rlc_part.as<G1>(), s->rlc_s.as<Fr>());
-    LAUNCH(s, k_rlc_finish, 3, RLC_FIN_THREADS, s->rlc_part.as<G1>(), s->rlc_s.as<Fr>(), nb, d_record);
+    if (nb) LAUNCH(s, k_rlc, dim3(nb, 3), RLC_THREADS, s->aff_p.as<G1Affine>(), s->aff_c.as<G1Affine>(), s->z.as<Fr>(), s->y.as<Fr>(), (int)n, (uint32_t)index_offset,
+                   s->rmont.as<Fr>(), raw, spec, d_status, s->rlc_part.as<G1>(), s->rlc_s.as<Fr>());
+    LAUNCH(s, k_rlc_finish, 3, RLC_FIN_THREADS, s->rlc_part.as<G1>(), s->rlc_s.as<Fr>(), nb, d_record);     // nb == 0: the identity record
+    return 0;
+}
+// the shard's errors travel with its sums (k_rlc_finish wrote zeros)
+static int set_record_err(kb200_setup* s, RlcRecord* d_record, const VErr& e) {
+    if (!e.first()) return 0;
+    const int32_t h[4] = {e.blob, e.comm, e.proof, 0};
+    CU(cudaMemcpyAsync(d_record->err, h, sizeof h, cudaMemcpyHostToDevice, s->stream));
+    CU(cudaStreamSynchronize(s->stream));
     return 0;
 }
 static void u32_to_be48(uint8_t* out, const uint32_t* limbs12) { for (int i = 0; i < 12; i++) { uint32_t w = limbs12[11 - i]; out[4 * i] = w >> 24; out[4 * i + 1] = w >> 16; out[4 * i + 2] = w >> 8; out[4 * i + 3] = w; } }
@@ -681,13 +719,16 @@ static void compress_plain(uint8_t out[48], const uint32_t* xy24, bool inf) {
     for (int i = 11; i >= 0; i--) { if (xy24[12 + i] > H_FP_HALF[i]) { gt = true; break; } if (xy24[12 + i] < H_FP_HALF[i]) break; }
     if (gt) out[0] |= 0x20;
 }
+// records of all shards -> error of the whole batch in kateth's order, or the verdict of the two-pairing check
 static int finish_records(kb200_setup* s, const RlcRecord* d_records, size_t nrec, int* ok) {
     if (int rc = s->combine.ensure(64 * 4)) return rc;
     LAUNCH(s, k_rlc_combine, 1, 32, d_records, (int)nrec, s->d_neg_g_pow, s->combine.as<uint32_t>());
-    uint32_t h[50];
+    uint32_t h[53];
     CU(cudaMemcpyAsync(h, s->combine.p, sizeof h, cudaMemcpyDeviceToHost, s->stream));
     CU(cudaStreamSynchronize(s->stream));
     CU(cudaGetLastError());
+    *ok = 0;
+    for (int k = 50; k < 53; k++) if (h[k]) return (int)h[k];      // Err(..): no verdict (src/kzg/setup.rs:259-271)
     host::G1A a, b;
     a.inf = h[48] != 0; b.inf = h[49] != 0;
     host::fp_from_plain_u32(a.x, h); host::fp_from_plain_u32(a.y, h + 12);
@@ -698,19 +739,21 @@ static int finish_records(kb200_setup* s, const RlcRecord* d_records, size_t nre
     return 0;
 }
 extern "C" int kb200_last_pairing_operands(kb200_setup* s, uint8_t lhs48[48], uint8_t rhs48[48]) {
-    if (!s || !s->have_last) return KB200_E_ARG;
+    if (!s) return KB200_E_ARG;
+    LOCK(s);
+    if (!s->have_last) return KB200_E_ARG;
     memcpy(lhs48, s->last_lhs, 48); memcpy(rhs48, s->last_rhs, 48); return 0;
 }
 
-// decode + decompress + challenge + evaluate for a shard; leaves aff_c, aff_p, z, y filled. Returns kateth-ordered first error.
-static int verify_prepare(kb200_setup* s, const uint32_t* d_blobs, const uint32_t* d_c48, const uint32_t* d_p48, size_t n, int32_t* d_status) {
-    if (int rc = s->st_blob.ensure(n * 4)) return rc;
-    if (int rc = s->st_a.ensure(n * 4)) return rc;
-    if (int rc = s->st_b.ensure(n * 4)) return rc;
-    if (int rc = s->aff_c.ensure(n * sizeof(G1Affine))) return rc;
-    if (int rc = s->aff_p.ensure(n * sizeof(G1Affine))) return rc;
-    if (int rc = s->z.ensure(n * sizeof(Fr))) return rc;
-    CU(cudaMemsetAsync(s->st_blob.p, 0, n * 4, s->stream));
+// decode + decompress + challenge + evaluate for items [off, off + m) of a call whose workspace verify_reserve sized: d_blobs,
+// d_c48, d_p48, d_status point at item `off`; fills aff_c, aff_p, z, y at `off`.  Accumulates the first error of each class in e.
+static int verify_prepare(kb200_setup* s, const uint32_t* d_blobs, const uint32_t* d_c48, const uint32_t* d_p48, size_t m, size_t off, int32_t* d_status,
+                          VErr& e) {
+    int32_t *st_blob = s->st_blob.as<int32_t>() + off, *st_a = s->st_a.as<int32_t>() + off, *st_b = s->st_b.as<int32_t>() + off;
+    G1Affine *aff_c = s->aff_c.as<G1Affine>() + off, *aff_p = s->aff_p.as<G1Affine>() + off;
+    Fr *z = s->z.as<Fr>() + off, *y = s->y.as<Fr>() + off;
+    const int n = (int)m;
+    CU(cudaMemsetAsync(st_blob, 0, m * 4, s->stream));
     // Two latency-bound kernels that do not depend on each other run side by side: the point decompression (a 380-step
     // square-and-multiply chain per point) on the auxiliary stream, the blob check and the serial SHA-256 of each blob on the
     // main one.  The challenge only needs the blob's own status; items with a bad point are dropped after the join.
@@ -718,52 +761,56 @@ static int verify_prepare(kb200_setup* s, const uint32_t* d_blobs, const uint32_
     if (!s->fork_recorded) CU(cudaEventRecord(s->ev_fork, s->stream));
     s->fork_recorded = false;
     CU(cudaStreamWaitEvent(s->aux_stream, s->ev_fork, 0));
-    CU(cudaMemsetAsync(s->st_a.p, 0, n * 4, s->aux_stream));
-    CU(cudaMemsetAsync(s->st_b.p, 0, n * 4, s->aux_stream));
-    k_g1_decompress<<<blocks(2 * n, 64), 64, 0, s->aux_stream>>>(d_c48, d_p48, (int)n, s->aff_c.as<G1Affine>(), s->aff_p.as<G1Affine>(),
-                                                                  s->st_a.as<int32_t>(), s->st_b.as<int32_t>(), 0);
+    CU(cudaMemsetAsync(st_a, 0, m * 4, s->aux_stream));
+    CU(cudaMemsetAsync(st_b, 0, m * 4, s->aux_stream));
+    k_g1_decompress<<<blocks(2 * m, 64), 64, 0, s->aux_stream>>>(d_c48, d_p48, n, aff_c, aff_p, st_a, st_b, 0);
     s->launches++;
     CU(cudaEventRecord(s->ev_join, s->aux_stream));
-    LAUNCH(s, k_blob_check, blocks(n * KB_N, 256), 256, d_blobs, (int)n, s->st_blob.as<int32_t>());
-    if (!s->z_ready) LAUNCH(s, k_challenge, blocks(n, 32), 32, d_blobs, d_c48, (int)n, s->st_blob.as<int32_t>(), s->z.as<Fr>());
+    LAUNCH(s, k_blob_check, blocks(m * KB_N, 256), 256, d_blobs, n, st_blob);
+    if (!s->z_ready) LAUNCH(s, k_challenge, blocks(m, 32), 32, d_blobs, d_c48, n, st_blob, z);
     s->z_ready = false;
     CU(cudaStreamWaitEvent(s->stream, s->ev_join, 0));
-    LAUNCH(s, k_merge_status, blocks(n, 256), 256, s->st_blob.as<int32_t>(), s->st_a.as<int32_t>(), s->st_b.as<int32_t>(), (int)n, d_status);
-    if (int rc = run_eval<false>(s, d_blobs, n, d_status)) return rc;
+    LAUNCH(s, k_merge_status, blocks(m, 256), 256, st_blob, st_a, st_b, n, d_status);
+    if (int rc = run_eval<false>(s, d_blobs, m, d_status, z, y)) return rc;
     std::vector<int32_t> h0, h1, h2;
-    if (int rc = fetch_status(s, s->st_blob.as<int32_t>(), n, h0)) return rc;
-    if (int rc = fetch_status(s, s->st_a.as<int32_t>(), n, h1)) return rc;
-    if (int rc = fetch_status(s, s->st_b.as<int32_t>(), n, h2)) return rc;
-    if (int e = first_nonzero(h0)) return e;
-    if (int e = first_nonzero(h1)) return e;
-    return first_nonzero(h2);
+    if (int rc = fetch_status(s, st_blob, m, h0)) return rc;
+    if (int rc = fetch_status(s, st_a, m, h1)) return rc;
+    if (int rc = fetch_status(s, st_b, m, h2)) return rc;
+    if (!e.blob) e.blob = first_nonzero(h0);
+    if (!e.comm) e.comm = first_nonzero(h1);
+    if (!e.proof) e.proof = first_nonzero(h2);
+    return 0;
 }
 extern "C" int kb200_verify_blob_proof_batch_partial_device(kb200_setup* s, const void* d_blobs, const void* d_c48, const void* d_p48, size_t n,
                                                             size_t index_offset, size_t n_total, void* d_record, int32_t* d_status) {
     if (!s || !d_record || (n && (!d_blobs || !d_c48 || !d_p48 || !d_status))) return KB200_E_ARG;
+    LOCK(s);
     CU(cudaSetDevice(s->device));
-    int err = 0;
-    if (n) { err = verify_prepare(s, (const uint32_t*)d_blobs, (const uint32_t*)d_c48, (const uint32_t*)d_p48, n, d_status); if (err < 0) return err; }
-    else { if (int rc = s->aff_c.ensure(16)) return rc; if (int rc = s->aff_p.ensure(16)) return rc; if (int rc = s->z.ensure(32)) return rc; if (int rc = s->y.ensure(32)) return rc; }
-    if (int rc = run_rlc(s, n, index_offset, n_total, 0, (RlcRecord*)d_record, (const uint32_t*)d_c48, (const uint32_t*)d_p48)) return rc;
+    VErr e;
+    if (int rc = verify_reserve(s, n)) return rc;
+    if (n) if (int rc = verify_prepare(s, (const uint32_t*)d_blobs, (const uint32_t*)d_c48, (const uint32_t*)d_p48, n, 0, d_status, e)) return rc;
+    if (int rc = run_rlc(s, n, index_offset, n_total, 0, (RlcRecord*)d_record, n ? d_status : nullptr, (const uint32_t*)d_c48, (const uint32_t*)d_p48)) return rc;
+    if (int rc = set_record_err(s, (RlcRecord*)d_record, e)) return rc;
     CU(cudaStreamSynchronize(s->stream));
     CU(cudaGetLastError());
-    return err;
+    return e.first();
 }
 extern "C" int kb200_verify_batch_finish_device(kb200_setup* s, const void* d_records, size_t n_records, int* ok) {
     if (!s || !ok || (n_records && !d_records)) return KB200_E_ARG;
+    LOCK(s);
     CU(cudaSetDevice(s->device));
     return finish_records(s, (const RlcRecord*)d_records, n_records, ok);
 }
 extern "C" int kb200_verify_blob_proof_batch_device(kb200_setup* s, const void* d_blobs, const void* d_c48, const void* d_p48, size_t n, int* ok,
                                                     int32_t* d_status) {
     if (!s || !ok) return KB200_E_ARG;
+    LOCK(s);
     CU(cudaSetDevice(s->device));
     if (n == 0) { *ok = 1; return 0; }     // empty lincombs are the identity: e(O, .) e(O, .) == 1
     if (int rc = s->records.ensure(sizeof(RlcRecord))) return rc;
     int err = kb200_verify_blob_proof_batch_partial_device(s, d_blobs, d_c48, d_p48, n, 0, n, s->records.p, d_status);
-    if (err) return err;
-    return finish_records(s, s->records.as<RlcRecord>(), 1, ok);
+    if (err < 0) return err;
+    return finish_records(s, s->records.as<RlcRecord>(), 1, ok);     // returns the record's error, if any
 }
 
 // ------------------------------------------------------------------ host-buffer entry points (copy in, run, copy out)
@@ -804,20 +851,19 @@ static int h2d_split(kb200_setup* s, DBuf& b, const uint8_t* src, size_t bytes, 
 // SHA-256 stream per blob, ~4 ms per launch whatever the batch size, and it cannot start before the blob is there -- so the
 // blobs are copied in NCOL = 8 column pieces (bytes [j*W, (j+1)*W) of every blob, a strided 2-D copy) and the hash advances over
 // each piece while the next one is on the wire: the batch is hashed ~1 ms after its last byte arrives instead of ~4 ms.
-// Commitments must already be queued to d_c48 on the main stream.  Leaves the challenges in s->z and sets z_ready.
+// Commitments must already be queued to d_c48 on the main stream.  Leaves the challenges in d_z (n items) and sets z_ready.
 #ifndef KB_NCOL
 #define KB_NCOL 8
 #endif
 static const int NCOL = KB_NCOL;     // <= 8 (ev_col)
 static const size_t HASHED_UPLOAD_MIN = 1024;     // below this the upload is shorter than one hash launch
-static int h2d_blobs_hashed(kb200_setup* s, const uint8_t* blobs, size_t n, const uint32_t* d_c48) {
+static int h2d_blobs_hashed(kb200_setup* s, const uint8_t* blobs, size_t n, const uint32_t* d_c48, Fr* d_z) {
     if (int rc = s->blobs.ensure(n * KB_BLOB_BYTES)) return rc;
     if (!s->split_copy || n < HASHED_UPLOAD_MIN) {
         CU(cudaMemcpyAsync(s->blobs.p, blobs, n * KB_BLOB_BYTES, cudaMemcpyHostToDevice, s->stream));
         return 0;
     }
     if (int rc = s->sha_state.ensure(n * 32)) return rc;
-    if (int rc = s->z.ensure(n * sizeof(Fr))) return rc;
     const size_t W = KB_BLOB_BYTES / NCOL;
     CU(cudaEventRecord(s->ev_fork, s->stream));      // commitments and proofs are queued: their decompression need not wait for the blobs
     s->fork_recorded = true;
@@ -830,13 +876,14 @@ static int h2d_blobs_hashed(kb200_setup* s, const uint8_t* blobs, size_t n, cons
     for (int j = 0; j < NCOL; j++) {
         CU(cudaStreamWaitEvent(s->stream, s->ev_col[j], 0));
         const int blk0 = (int)(j * W / 64), blk1 = (j == NCOL - 1) ? 2050 : (int)((j + 1) * W / 64);
-        LAUNCH(s, k_challenge_range, blocks(n, 32), 32, s->blobs.as<uint32_t>(), d_c48, (int)n, s->sha_state.as<uint32_t>(), s->z.as<Fr>(), blk0, blk1);
+        LAUNCH(s, k_challenge_range, blocks(n, 32), 32, s->blobs.as<uint32_t>(), d_c48, (int)n, s->sha_state.as<uint32_t>(), d_z, blk0, blk1);
     }
     s->z_ready = true;
     return 0;
 }
 extern "C" int kb200_blob_to_commitment(kb200_setup* s, const uint8_t* blobs, size_t n, uint8_t* out48, int32_t* status) {
     if (!s || (n && (!blobs || !out48))) return KB200_E_ARG;
+    LOCK(s);
     CU(cudaSetDevice(s->device));
     CopyGuard guard{s};
     int first = 0;
@@ -856,11 +903,31 @@ extern "C" int kb200_blob_to_commitment(kb200_setup* s, const uint8_t* blobs, si
     }
     return first;
 }
+// Blob::from_slice alone (src/blob.rs:26-37) over n blobs: status[i] = 0 or InvalidFieldElement.  For callers that hold blobs of
+// unequal byte lengths and must report kateth's first error in blob order before the batch can be laid out contiguously.
+extern "C" int kb200_check_blobs(kb200_setup* s, const uint8_t* blobs, size_t n, int32_t* status) {
+    if (!s || (n && !blobs)) return KB200_E_ARG;
+    LOCK(s);
+    CU(cudaSetDevice(s->device));
+    int first = 0;
+    for (size_t off = 0; off < n; off += CHUNK) {
+        const size_t m = (n - off < CHUNK) ? n - off : CHUNK;
+        if (int rc = h2d(s, s->blobs, blobs + off * KB_BLOB_BYTES, m * KB_BLOB_BYTES)) return rc;
+        if (int rc = s->status.ensure(m * 4)) return rc;
+        CU(cudaMemsetAsync(s->status.p, 0, m * 4, s->stream));
+        LAUNCH(s, k_blob_check, blocks(m * KB_N, 256), 256, s->blobs.as<uint32_t>(), (int)m, s->status.as<int32_t>());
+        std::vector<int32_t> h; if (int rc = fetch_status(s, s->status.as<int32_t>(), m, h)) return rc;
+        if (status) memcpy(status + off, h.data(), m * 4);
+        if (!first) first = first_nonzero(h);
+    }
+    return first;
+}
 // (No head/rest copy here: the proof path runs latency-bound per-blob kernels in front of its MSM -- the serial SHA-256 of the
 // challenge takes ~4 ms whether it hashes 592 or 4096 blobs -- so running them twice costs what the hidden copy saves;
 // measured with tools/e2e_probe.py: 97.1 ms split against 95.9 ms in one piece for 4096 blobs.  Column pieces instead.)
 extern "C" int kb200_compute_blob_proof(kb200_setup* s, const uint8_t* blobs, const uint8_t* comm48, size_t n, uint8_t* out48, int32_t* status) {
     if (!s || (n && (!blobs || !comm48 || !out48))) return KB200_E_ARG;
+    LOCK(s);
     CU(cudaSetDevice(s->device));
     CopyGuard guard{s};
     // kateth's order within one call is blob first, then commitment; across a batch we report the first item's error
@@ -868,7 +935,8 @@ extern "C" int kb200_compute_blob_proof(kb200_setup* s, const uint8_t* blobs, co
     for (size_t off = 0; off < n; off += CHUNK) {
         size_t m = (n - off < CHUNK) ? n - off : CHUNK;
         if (int rc = h2d(s, s->c48, comm48 + off * 48, m * 48)) return rc;
-        if (int rc = h2d_blobs_hashed(s, blobs + off * KB_BLOB_BYTES, m, s->c48.as<uint32_t>())) return rc;
+        if (int rc = s->z.ensure(m * sizeof(Fr))) return rc;
+        if (int rc = h2d_blobs_hashed(s, blobs + off * KB_BLOB_BYTES, m, s->c48.as<uint32_t>(), s->z.as<Fr>())) return rc;
         if (int rc = s->out48.ensure(m * 48)) return rc;
         if (int rc = s->status.ensure(m * 4)) return rc;
         int e = kb200_compute_blob_proof_device(s, s->blobs.p, s->c48.p, m, s->out48.p, s->status.as<int32_t>());
@@ -881,6 +949,7 @@ extern "C" int kb200_compute_blob_proof(kb200_setup* s, const uint8_t* blobs, co
 }
 extern "C" int kb200_compute_proof(kb200_setup* s, const uint8_t* blobs, const uint8_t* z32, size_t n, uint8_t* out48, uint8_t* y32, int32_t* status) {
     if (!s || (n && (!blobs || !z32 || !out48 || !y32))) return KB200_E_ARG;
+    LOCK(s);
     CU(cudaSetDevice(s->device));
     int first = 0;
     for (size_t off = 0; off < n; off += CHUNK) {
@@ -899,74 +968,66 @@ extern "C" int kb200_compute_proof(kb200_setup* s, const uint8_t* blobs, const u
     }
     return first;
 }
+// A host-buffer shard of any size: commitments and proofs go up whole, the blobs in chunks of CHUNK (each chunk's challenge,
+// evaluation and point checks run as it lands); then ONE pass of RLC sums over all n items, so a batch larger than a chunk
+// still yields one record -- and, in consensus-spec challenge mode, one transcript.
+static int verify_host_shard(kb200_setup* s, const uint8_t* blobs, const uint8_t* comm48, const uint8_t* proofs48, size_t n, size_t index_offset,
+                             size_t n_total, RlcRecord* d_record, int32_t* status, VErr& e) {
+    if (int rc = verify_reserve(s, n)) return rc;
+    if (int rc = s->status.ensure(n ? n * 4 : 16)) return rc;
+    if (int rc = h2d(s, s->c48, comm48, n * 48)) return rc;
+    if (int rc = h2d(s, s->p48, proofs48, n * 48)) return rc;
+    for (size_t off = 0; off < n; off += CHUNK) {
+        const size_t m = (n - off < CHUNK) ? n - off : CHUNK;
+        if (int rc = h2d_blobs_hashed(s, blobs + off * KB_BLOB_BYTES, m, s->c48.as<uint32_t>() + off * 12, s->z.as<Fr>() + off)) return rc;
+        if (int rc = verify_prepare(s, s->blobs.as<uint32_t>(), s->c48.as<uint32_t>() + off * 12, s->p48.as<uint32_t>() + off * 12, m, off,
+                                    s->status.as<int32_t>() + off, e)) return rc;
+    }
+    if (status && n) if (int rc = d2h(s, status, s->status.p, n * 4)) return rc;
+    if (int rc = run_rlc(s, n, index_offset, n_total, 0, d_record, n ? s->status.as<int32_t>() : nullptr, s->c48.as<uint32_t>(), s->p48.as<uint32_t>())) return rc;
+    return set_record_err(s, d_record, e);
+}
 extern "C" int kb200_verify_blob_proof_batch(kb200_setup* s, const uint8_t* blobs, const uint8_t* comm48, const uint8_t* proofs48, size_t n, int* ok,
                                              int32_t* status) {
     if (!s || !ok || (n && (!blobs || !comm48 || !proofs48))) return KB200_E_ARG;
+    LOCK(s);
     CU(cudaSetDevice(s->device));
     if (n == 0) { *ok = 1; return 0; }
     CopyGuard guard{s};
-    size_t nch = (n + CHUNK - 1) / CHUNK;
-    if (int rc = s->records.ensure(nch * sizeof(RlcRecord))) return rc;
-    // kateth checks ALL blobs, then ALL commitments, then ALL proofs (src/kzg/setup.rs:259-271); with chunking we
-    // remember the first error of each class across chunks.
-    int e_blob = 0, e_comm = 0, e_proof = 0;
-    for (size_t c = 0; c < nch; c++) {
-        size_t off = c * CHUNK, m = (n - off < CHUNK) ? n - off : CHUNK;
-        if (int rc = h2d(s, s->c48, comm48 + off * 48, m * 48)) return rc;
-        if (int rc = h2d(s, s->p48, proofs48 + off * 48, m * 48)) return rc;
-        if (int rc = h2d_blobs_hashed(s, blobs + off * KB_BLOB_BYTES, m, s->c48.as<uint32_t>())) return rc;
-        if (int rc = s->status.ensure(m * 4)) return rc;
-        int e = kb200_verify_blob_proof_batch_partial_device(s, s->blobs.p, s->c48.p, s->p48.p, m, off, n, (char*)s->records.p + c * sizeof(RlcRecord),
-                                                             s->status.as<int32_t>());
-        if (e < 0) return e;
-        if (e) {
-            std::vector<int32_t> h0, h1, h2;
-            if (int rc = fetch_status(s, s->st_blob.as<int32_t>(), m, h0)) return rc;
-            if (int rc = fetch_status(s, s->st_a.as<int32_t>(), m, h1)) return rc;
-            if (int rc = fetch_status(s, s->st_b.as<int32_t>(), m, h2)) return rc;
-            if (!e_blob) e_blob = first_nonzero(h0);
-            if (!e_comm) e_comm = first_nonzero(h1);
-            if (!e_proof) e_proof = first_nonzero(h2);
-        }
-        if (status) if (int rc = d2h(s, status + off, s->status.p, m * 4)) return rc;
-    }
-    if (e_blob) return e_blob;
-    if (e_comm) return e_comm;
-    if (e_proof) return e_proof;
-    return finish_records(s, s->records.as<RlcRecord>(), nch, ok);
+    if (int rc = s->records.ensure(sizeof(RlcRecord))) return rc;
+    VErr e;
+    // kateth checks ALL blobs, then ALL commitments, then ALL proofs (src/kzg/setup.rs:259-271): e keeps the first error of each
+    // class across the chunks, the record carries them, finish_records returns them in that order
+    if (int rc = verify_host_shard(s, blobs, comm48, proofs48, n, 0, n, s->records.as<RlcRecord>(), status, e)) return rc;
+    return finish_records(s, s->records.as<RlcRecord>(), 1, ok);
 }
-// host-buffer shard of a multi-GPU batch: inputs in (pinned) host memory, the 320-byte record stays on the device
+// host-buffer shard of a multi-GPU batch: inputs in (pinned) host memory, the record stays on the device
 extern "C" int kb200_verify_blob_proof_batch_partial(kb200_setup* s, const uint8_t* blobs, const uint8_t* comm48, const uint8_t* proofs48, size_t n,
                                                      size_t index_offset, size_t n_total, void* d_record, int32_t* status) {
     if (!s || !d_record || (n && (!blobs || !comm48 || !proofs48))) return KB200_E_ARG;
+    LOCK(s);
     CU(cudaSetDevice(s->device));
-    if (n > CHUNK) { snprintf(g_err, sizeof g_err, "partial: at most %zu blobs per call", CHUNK); return KB200_E_ARG; }
     CopyGuard guard{s};
-    if (int rc = h2d(s, s->c48, comm48, n * 48)) return rc;
-    if (int rc = h2d(s, s->p48, proofs48, n * 48)) return rc;
-    if (int rc = h2d_blobs_hashed(s, blobs, n, s->c48.as<uint32_t>())) return rc;
-    if (int rc = s->status.ensure(n ? n * 4 : 16)) return rc;
-    int e = kb200_verify_blob_proof_batch_partial_device(s, s->blobs.p, s->c48.p, s->p48.p, n, index_offset, n_total, d_record, s->status.as<int32_t>());
-    if (e < 0) return e;
-    if (status && n) if (int rc = d2h(s, status, s->status.p, n * 4)) return rc;
-    return e;
+    VErr e;
+    if (int rc = verify_host_shard(s, blobs, comm48, proofs48, n, index_offset, n_total, (RlcRecord*)d_record, status, e)) return rc;
+    CU(cudaStreamSynchronize(s->stream));
+    CU(cudaGetLastError());
+    return e.first();
 }
 // points given directly: mirrors the private Setup::verify_proof_batch (raw = 0) and verify_proof_inner (raw = 1)
 static int verify_points(kb200_setup* s, const uint8_t* proofs48, const uint8_t* comm48, const uint8_t* z32, const uint8_t* y32, size_t n, int raw, int* ok,
                          int32_t* status) {
     if (!s || !ok || (n && (!proofs48 || !comm48 || !z32 || !y32))) return KB200_E_ARG;
+    LOCK(s);
     CU(cudaSetDevice(s->device));
     if (n == 0) { *ok = 1; return 0; }
     if (int rc = h2d(s, s->p48, proofs48, n * 48)) return rc;
     if (int rc = h2d(s, s->c48, comm48, n * 48)) return rc;
     if (int rc = h2d(s, s->zy32, z32, n * 32)) return rc;
     if (int rc = h2d(s, s->out32, y32, n * 32)) return rc;
-    DBuf* need[] = {&s->st_blob, &s->st_a, &s->st_b, &s->status};
-    for (DBuf* b : need) { if (int rc = b->ensure(n * 4)) return rc; CU(cudaMemsetAsync(b->p, 0, n * 4, s->stream)); }
-    if (int rc = s->aff_c.ensure(n * sizeof(G1Affine))) return rc;
-    if (int rc = s->aff_p.ensure(n * sizeof(G1Affine))) return rc;
-    if (int rc = s->z.ensure(n * sizeof(Fr))) return rc;
-    if (int rc = s->y.ensure(n * sizeof(Fr))) return rc;
+    if (int rc = verify_reserve(s, n)) return rc;
+    DBuf* need[] = {&s->st_blob, &s->st_a, &s->st_b};
+    for (DBuf* b : need) CU(cudaMemsetAsync(b->p, 0, n * 4, s->stream));
     if (int rc = s->prod.ensure(n * 4)) return rc;   // 4th status class (y)
     CU(cudaMemsetAsync(s->prod.p, 0, n * 4, s->stream));
     // kateth's order in verify_proof: proof, commitment, point, eval (src/kzg/setup.rs:103-110)
@@ -982,7 +1043,7 @@ static int verify_points(kb200_setup* s, const uint8_t* proofs48, const uint8_t*
     if (status) for (size_t i = 0; i < n; i++) status[i] = h[0][i] ? h[0][i] : h[1][i] ? h[1][i] : h[2][i] ? h[2][i] : h[3][i];
     for (int k = 0; k < 4; k++) if (int e = first_nonzero(h[k])) return e;
     if (int rc = s->records.ensure(sizeof(RlcRecord))) return rc;
-    if (int rc = run_rlc(s, n, 0, n, raw, s->records.as<RlcRecord>(), s->c48.as<uint32_t>(), s->p48.as<uint32_t>())) return rc;
+    if (int rc = run_rlc(s, n, 0, n, raw, s->records.as<RlcRecord>(), nullptr, s->c48.as<uint32_t>(), s->p48.as<uint32_t>())) return rc;
     return finish_records(s, s->records.as<RlcRecord>(), 1, ok);
 }
 extern "C" int kb200_verify_proof(kb200_setup* s, const uint8_t proof48[48], const uint8_t comm48[48], const uint8_t z32[32], const uint8_t y32[32], int* ok) {
@@ -994,37 +1055,43 @@ extern "C" int kb200_verify_proof_batch(kb200_setup* s, const uint8_t* proofs48,
 }
 extern "C" int kb200_verify_blob_proof(kb200_setup* s, const uint8_t* blob, const uint8_t comm48[48], const uint8_t proof48[48], int* ok) {
     if (!s || !ok || !blob || !comm48 || !proof48) return KB200_E_ARG;
+    LOCK(s);
     CU(cudaSetDevice(s->device));
     if (int rc = h2d(s, s->blobs, blob, KB_BLOB_BYTES)) return rc;
     if (int rc = h2d(s, s->c48, comm48, 48)) return rc;
     if (int rc = h2d(s, s->p48, proof48, 48)) return rc;
     if (int rc = s->status.ensure(4)) return rc;
-    int e = verify_prepare(s, s->blobs.as<uint32_t>(), s->c48.as<uint32_t>(), s->p48.as<uint32_t>(), 1, s->status.as<int32_t>());
-    if (e) return e;
+    if (int rc = verify_reserve(s, 1)) return rc;
+    VErr e;
+    if (int rc = verify_prepare(s, s->blobs.as<uint32_t>(), s->c48.as<uint32_t>(), s->p48.as<uint32_t>(), 1, 0, s->status.as<int32_t>(), e)) return rc;
+    if (e.first()) return e.first();
     if (int rc = s->records.ensure(sizeof(RlcRecord))) return rc;
-    if (int rc = run_rlc(s, 1, 0, 1, 1, s->records.as<RlcRecord>())) return rc;
+    if (int rc = run_rlc(s, 1, 0, 1, 1, s->records.as<RlcRecord>(), nullptr)) return rc;
     return finish_records(s, s->records.as<RlcRecord>(), 1, ok);
 }
 
 // ------------------------------------------------------------------ unit-test hooks
 extern "C" int kb200_test_fp_mul(const uint32_t* a, const uint32_t* b, uint32_t* out, size_t n) {
     if (int rc = init_consts()) return rc;
-    Fp *da, *db, *dout; CU(cudaMalloc(&da, n * 48)); CU(cudaMalloc(&db, n * 48)); CU(cudaMalloc(&dout, n * 48));
+    DevTmp ta, tb, to; CU(cudaMalloc(&ta.p, n * 48)); CU(cudaMalloc(&tb.p, n * 48)); CU(cudaMalloc(&to.p, n * 48));
+    Fp *da = ta.as<Fp>(), *db = tb.as<Fp>(), *dout = to.as<Fp>();
     CU(cudaMemcpy(da, a, n * 48, cudaMemcpyHostToDevice)); CU(cudaMemcpy(db, b, n * 48, cudaMemcpyHostToDevice));
     k_test_fp_mul<<<blocks(n, 128), 128>>>(da, db, dout, (int)n);
     CU(cudaMemcpy(out, dout, n * 48, cudaMemcpyDeviceToHost));
-    cudaFree(da); cudaFree(db); cudaFree(dout); return 0;
+    return 0;
 }
 extern "C" int kb200_test_fr_mul(const uint32_t* a, const uint32_t* b, uint32_t* out, size_t n) {
     if (int rc = init_consts()) return rc;
-    Fr *da, *db, *dout; CU(cudaMalloc(&da, n * 32)); CU(cudaMalloc(&db, n * 32)); CU(cudaMalloc(&dout, n * 32));
+    DevTmp ta, tb, to; CU(cudaMalloc(&ta.p, n * 32)); CU(cudaMalloc(&tb.p, n * 32)); CU(cudaMalloc(&to.p, n * 32));
+    Fr *da = ta.as<Fr>(), *db = tb.as<Fr>(), *dout = to.as<Fr>();
     CU(cudaMemcpy(da, a, n * 32, cudaMemcpyHostToDevice)); CU(cudaMemcpy(db, b, n * 32, cudaMemcpyHostToDevice));
     k_test_fr_mul<<<blocks(n, 128), 128>>>(da, db, dout, (int)n);
     CU(cudaMemcpy(out, dout, n * 32, cudaMemcpyDeviceToHost));
-    cudaFree(da); cudaFree(db); cudaFree(dout); return 0;
+    return 0;
 }
 extern "C" int kb200_test_g1_decompress(kb200_setup* s, const uint8_t* in48, size_t n, int32_t* status, uint8_t* re48, int by_order) {
     if (!s || !in48 || !status || !re48) return KB200_E_ARG;
+    LOCK(s);
     CU(cudaSetDevice(s->device));
     if (int rc = h2d(s, s->c48, in48, n * 48)) return rc;
     if (int rc = s->aff_c.ensure(n * sizeof(G1Affine))) return rc;
@@ -1040,8 +1107,11 @@ extern "C" int kb200_test_mac_peak(int iters, double* tmacs_wide, double* tmacs_
     if (int rc = init_consts()) return rc;
     cudaDeviceProp prop; CU(cudaGetDeviceProperties(&prop, 0));
     int grid = prop.multiProcessorCount * 8, block = 256;
-    void* buf; CU(cudaMalloc(&buf, (size_t)grid * block * 48));
-    cudaEvent_t e0, e1; CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
+    DevTmp tbuf; CU(cudaMalloc(&tbuf.p, (size_t)grid * block * 48));
+    void* buf = tbuf.p;
+    struct Ev { cudaEvent_t e = nullptr; ~Ev() { if (e) cudaEventDestroy(e); } } ev0, ev1;
+    CU(cudaEventCreate(&ev0.e)); CU(cudaEventCreate(&ev1.e));
+    cudaEvent_t e0 = ev0.e, e1 = ev1.e;
     float ms;
     k_mac_wide<<<grid, block>>>((uint64_t*)buf, 64, 1);   // warm-up
     CU(cudaEventRecord(e0)); k_mac_wide<<<grid, block>>>((uint64_t*)buf, iters, 7); CU(cudaEventRecord(e1)); CU(cudaEventSynchronize(e1));
@@ -1052,7 +1122,6 @@ extern "C" int kb200_test_mac_peak(int iters, double* tmacs_wide, double* tmacs_
     CU(cudaEventRecord(e0)); k_mac_fpmul<<<grid, block>>>((Fp*)buf, it2, 7); CU(cudaEventRecord(e1)); CU(cudaEventSynchronize(e1));
     CU(cudaEventElapsedTime(&ms, e0, e1));
     *tmacs_fpmul = (double)grid * block * it2 * 2.0 * 300.0 / (ms * 1e-3) / 1e12;
-    cudaFree(buf); cudaEventDestroy(e0); cudaEventDestroy(e1);
     return 0;
 }
 extern "C" int kb200_test_host_pairing(kb200_setup* s, const uint32_t* a_xy24, int a_inf, const uint32_t* b_xy24, int b_inf, int* ok) {

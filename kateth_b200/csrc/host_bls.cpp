@@ -2,6 +2,7 @@
 #include "host_bls.hpp"
 #include "constants.cuh"
 #include <string.h>
+#include <mutex>
 
 namespace kb200 { namespace host {
 
@@ -9,6 +10,7 @@ typedef unsigned __int128 u128;
 using namespace kb200::consts;
 
 // ------------------------------------------------------------------ Fp
+static void init();
 static Fp P_, ONE_, R2_, ZERO_;
 static uint64_t EXP_PM2[6], EXP_PM3D4[6], EXP_HALF[6], EXP_PM1D6[6];
 static void pack64(uint64_t* o, const uint32_t* w) { for (int i = 0; i < 6; i++) o[i] = (uint64_t)w[2 * i] | ((uint64_t)w[2 * i + 1] << 32); }
@@ -55,7 +57,7 @@ static bool fp_from_be48(Fp& r, const uint8_t* in) {
     if (geq(t, P_)) return false;
     fto_mont(r, t); return true;
 }
-void fp_from_plain_u32(Fp& r, const uint32_t* w) { Fp t; pack64(t.l, w); fto_mont(r, t); }
+void fp_from_plain_u32(Fp& r, const uint32_t* w) { init(); Fp t; pack64(t.l, w); fto_mont(r, t); }
 
 // ------------------------------------------------------------------ Fp2
 static inline void f2add(Fp2& r, const Fp2& a, const Fp2& b) { fadd(r.c0, a.c0, b.c0); fadd(r.c1, a.c1, b.c1); }
@@ -216,9 +218,9 @@ static bool g2_in_subgroup(const G2A& q) {
     return f2zero(acc.z);
 }
 
-static bool g_init = false;
-static void init() {
-    if (g_init) return;
+// the file-level constants are filled once, whichever thread gets here first (handles may be loaded from several threads)
+static std::once_flag g_once;
+static void init_once() {
     pack64(P_.l, H_FP_P); pack64(ONE_.l, H_FP_ONE); pack64(R2_.l, H_FP_R2); memset(&ZERO_, 0, sizeof ZERO_);
     pack64(EXP_PM2, H_FP_PM2); pack64(EXP_PM3D4, H_FP_PM3D4); pack64(EXP_HALF, H_FP_HALF); pack64(EXP_PM1D6, H_FP_PM1D6);
     F2ONE.c0 = ONE_; F2ONE.c1 = ZERO_; F2ZERO.c0 = ZERO_; F2ZERO.c1 = ZERO_;
@@ -227,8 +229,8 @@ static void init() {
     Fp2 gamma; f2pow(gamma, xi, EXP_PM1D6, 384);
     FROB1[0] = F2ONE; for (int k = 1; k < 6; k++) f2mul(FROB1[k], FROB1[k - 1], gamma);
     for (int k = 0; k < 6; k++) { Fp2 c, n; f2conj(c, FROB1[k]); f2mul(n, FROB1[k], c); FROB2[k] = n.c0; }   // norm: gamma^(p+1)
-    g_init = true;
 }
+static void init() { std::call_once(g_once, init_once); }
 
 int g2_decompress(G2A& out, const uint8_t in[96]) {
     init();

@@ -9,8 +9,12 @@
 // kateth's quirks are reproduced: r = SHA-256("RCKZGBATCH___V1_" | u128_be(4096) | u128_be(n)) mod r depends on n
 // only, and rpowers = [r, r, r^2, r^3, ...] because Fr::pow(x, 0) returns x (src/bls.rs:169-187).
 //
-// Per GPU the result is one 320-byte record {A, B, C as affine Montgomery points, s}:
+// Per GPU the result is one 336-byte record {A, B, C as affine Montgomery points, s, err[4]}:
 //   A = sum w_i pi_i,  B = sum w_i z_i pi_i,  C = sum w_i C_i,  s = sum w_i y_i        (w_i = rpowers[i])
+//   err = the shard's first error of each class (blob, commitment, proof; 0 = none): errors travel WITH the sums, so that every
+//   rank that finishes a sharded batch returns the error kateth would (all blobs, then all commitments, then all proofs,
+//   src/kzg/setup.rs:259-271) instead of a verdict computed from unvalidated terms.  Items with a non-zero status contribute
+//   nothing to the sums.
 // Records of several GPUs are exchanged with one all-gather, then k_rlc_combine forms the pairing operands
 //   lhs = sum_g A_g            rhs = sum_g C_g - (sum_g s_g) * G1 + sum_g B_g
 // and the host checks e(lhs, [tau]_2) == e(rhs, G2).
@@ -19,8 +23,8 @@
 
 namespace kb200 {
 
-struct RlcRecord { G1Affine a, b, c; Fr s; };   // 3*96 + 32 = 320 bytes
-static_assert(sizeof(RlcRecord) == 320, "record layout");
+struct RlcRecord { G1Affine a, b, c; Fr s; int32_t err[4]; };   // 3*96 + 32 + 16 = 336 bytes (err[3] unused)
+static_assert(sizeof(RlcRecord) == 336, "record layout");
 
 // Two arrays of n compressed points each (the second may be null) in ONE launch, one thread per point: out = affine
 // Montgomery; status[i] set to 3/4/5 on failure (kept if already non-zero).  by_order != 0 uses the [r]P definition of
@@ -85,7 +89,8 @@ __global__ void k_set_r(const uint32_t* plain, Fr* r_mont) {
 //   e(pi, [tau]_2) == e(C - y G1 + z pi, G2)).
 __global__ void __launch_bounds__(RLC_THREADS) k_rlc(const G1Affine* __restrict__ proofs, const G1Affine* __restrict__ comms,
                                                       const Fr* __restrict__ z_canon, const Fr* __restrict__ y_canon, int n, uint32_t index_offset,
-                                                      const Fr* __restrict__ r_mont, int raw, int spec, G1* __restrict__ partials, Fr* __restrict__ s_partials) {
+                                                      const Fr* __restrict__ r_mont, int raw, int spec, const int32_t* __restrict__ status,
+                                                      G1* __restrict__ partials, Fr* __restrict__ s_partials) {
     __shared__ G1 sm[RLC_THREADS / 2];
     __shared__ Fr sms[RLC_THREADS];
     const int tid = threadIdx.x, which = blockIdx.y;
@@ -95,7 +100,7 @@ __global__ void __launch_bounds__(RLC_THREADS) k_rlc(const G1Affine* __restrict_
     const int i = t >> 1, half = t & 1;
     G1 acc; g1_set_inf(acc);
     Fr s; fr_zero(s);
-    if (i < n) {
+    if (i < n && (status == nullptr || status[i] == 0)) {     // an item that failed validation contributes nothing
         Fr wgt;    // Montgomery
         if (raw) fr_set(wgt, c_k.fr_one);
         else {
@@ -163,7 +168,27 @@ __global__ void __launch_bounds__(RLC_FIN_THREADS) k_rlc_finish(const G1* __rest
             if (tid < stride) { Fr a = sms[tid], c = sms[tid + stride]; fr_add(a, a, c); sms[tid] = a; }
             __syncthreads();
         }
-        if (tid == 0) rec->s = sms[0];
+        if (tid == 0) { rec->s = sms[0]; for (int k = 0; k < 4; k++) rec->err[k] = 0; }
+    }
+}
+// Several records of ONE rank (the chunks of a host-buffer shard) -> one record: lane 0..2 sum A, B, C, lane 3 sums s and keeps
+// the first error of each class in chunk order.
+__global__ void __launch_bounds__(32) k_rlc_merge(const RlcRecord* __restrict__ recs, int nrec, RlcRecord* __restrict__ out) {
+    const int lane = threadIdx.x;
+    if (lane < 3) {
+        G1 acc; g1_set_inf(acc);
+        for (int g = 0; g < nrec; g++) { const G1Affine* p = lane == 0 ? &recs[g].a : (lane == 1 ? &recs[g].b : &recs[g].c); G1Affine t = *p; g1_madd_signed(acc, t, false); }
+        G1Affine a; g1_to_affine(a, acc);
+        if (lane == 0) out->a = a; else if (lane == 1) out->b = a; else out->c = a;
+    } else if (lane == 3) {
+        Fr s; fr_zero(s);
+        int32_t e[4] = {0, 0, 0, 0};
+        for (int g = 0; g < nrec; g++) {
+            Fr t = recs[g].s; fr_add(s, s, t);
+            for (int k = 0; k < 4; k++) if (e[k] == 0) e[k] = recs[g].err[k];
+        }
+        out->s = s;
+        for (int k = 0; k < 4; k++) out->err[k] = e[k];
     }
 }
 // neg_g_pow[w] = 2^(8w) * (-G1), affine, w = 0..31: fixed-base table for the [s](-G1) term of the combine step (built at setup)
@@ -178,7 +203,8 @@ __global__ void k_neg_g_table(G1Affine* __restrict__ neg_g_pow) {
     neg_g_pow[w] = a;
 }
 // Combine the records of all ranks into the two G1 pairing operands, as plain (non-Montgomery) affine coordinates:
-// out[0..11] = lhs.x, [12..23] = lhs.y, [24..35] = rhs.x, [36..47] = rhs.y, out[48] = lhs is infinity, out[49] = rhs is infinity.
+// out[0..11] = lhs.x, [12..23] = lhs.y, [24..35] = rhs.x, [36..47] = rhs.y, out[48] = lhs is infinity, out[49] = rhs is infinity,
+// out[50..52] = first blob / commitment / proof error over the records in rank order (0 = none).
 //   lhs = sum_g A_g        rhs = sum_g C_g + [sum_g s_g](-G1) + sum_g B_g
 // One warp: lane w multiplies the fixed point 2^(8w)(-G1) by byte w of s (8 double-and-add steps), the warp tree-sums the 32
 // terms, lane 0 adds the records, lanes 0 and 1 normalise one operand each.
@@ -201,6 +227,12 @@ __global__ void __launch_bounds__(32) k_rlc_combine(const RlcRecord* __restrict_
         __syncwarp();
         if (lane < stride) g1_add(acc, sm[lane]);
         __syncwarp();
+    }
+    if (lane == 2) {
+        int32_t e[3] = {0, 0, 0};
+        for (int g = 0; g < nrec; g++)
+            for (int k = 0; k < 3; k++) if (e[k] == 0) e[k] = recs[g].err[k];
+        for (int k = 0; k < 3; k++) out[50 + k] = (uint32_t)e[k];
     }
     if (lane == 0) {
         G1 A, B; g1_set_inf(A); g1_set_inf(B);

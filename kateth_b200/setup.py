@@ -3,7 +3,7 @@ import ctypes as C
 import os
 
 BYTES_PER_BLOB = 131072
-RECORD_BYTES = 320
+RECORD_BYTES = 336
 _HERE = os.path.dirname(os.path.abspath(__file__))
 
 _STATUS_NAMES = {
@@ -38,7 +38,7 @@ class _Info(C.Structure):
 # every symbol include/kateth_b200.h declares (tests/test_abi.py checks the header against this list and the .so)
 SYMBOLS = [
     "kb200_setup_load_json", "kb200_setup_load_txt", "kb200_setup_load_raw", "kb200_setup_free", "kb200_set_stream", "kb200_last_error", "kb200_alloc_pinned", "kb200_free_pinned",
-    "kb200_blob_to_commitment", "kb200_blob_to_commitment_device", "kb200_compute_blob_proof", "kb200_compute_blob_proof_device",
+    "kb200_blob_to_commitment", "kb200_blob_to_commitment_device", "kb200_check_blobs", "kb200_compute_blob_proof", "kb200_compute_blob_proof_device",
     "kb200_compute_proof", "kb200_compute_proof_device", "kb200_verify_proof", "kb200_verify_proof_batch", "kb200_verify_blob_proof",
     "kb200_verify_blob_proof_batch", "kb200_verify_blob_proof_batch_device", "kb200_verify_blob_proof_batch_partial_device",
     "kb200_verify_blob_proof_batch_partial", "kb200_verify_batch_finish_device", "kb200_set_profiling", "kb200_set_msm_mode", "kb200_set_batch_challenge", "kb200_get_msm_profile", "kb200_last_pairing_operands", "kb200_get_info", "kb200_test_fp_mul", "kb200_test_fr_mul",
@@ -167,15 +167,23 @@ class Setup:
     # -- Setup::verify_blob_proof_batch (src/kzg/setup.rs:247-275)
     def verify_blob_proof_batch(self, blobs, commitments, proofs):
         assert len(blobs) == len(commitments) == len(proofs)   # kateth: assert_eq! (panics)
-        for b in blobs:
-            if len(b) != BYTES_PER_BLOB:
-                raise KzgError(1)
+        blobs = [bytes(b) for b in blobs]
+        # kateth decodes blob by blob (src/kzg/setup.rs:259-262, src/blob.rs:26-37): the first error in BLOB order wins, so an
+        # element error of an earlier blob precedes the length error of a later one
+        short = next((i for i, b in enumerate(blobs) if len(b) != BYTES_PER_BLOB), None)
+        if short is not None:
+            if short:
+                st = (C.c_int32 * short)()
+                rc = lib().kb200_check_blobs(self._h, b"".join(blobs[:short]), C.c_size_t(short), st)
+                if rc:
+                    _check(rc)
+            raise KzgError(1)
         for c in list(commitments) + list(proofs):
             if len(c) != 48:
                 raise KzgError(3)
         n = len(blobs)
         ok = C.c_int(0)
-        _check(lib().kb200_verify_blob_proof_batch(self._h, b"".join(bytes(b) for b in blobs), b"".join(bytes(c) for c in commitments),
+        _check(lib().kb200_verify_blob_proof_batch(self._h, b"".join(blobs), b"".join(bytes(c) for c in commitments),
                                                    b"".join(bytes(p) for p in proofs), C.c_size_t(n), C.byref(ok), None))
         return bool(ok.value)
 
@@ -280,22 +288,43 @@ def shard_bounds(n_total, world_size, rank):
     return n_total * rank // world_size, n_total * (rank + 1) // world_size
 
 
+def batch_error_of_records(gathered):
+    """Host-side reading of what kb200_verify_batch_finish_device returns for a set of gathered records: each KB200_RECORD_BYTES
+    record ends in four little-endian int32 {first blob error, first commitment error, first proof error, 0} of its shard; the
+    batch's error is the first blob error in rank order, else the first commitment error, else the first proof error
+    (kateth: src/kzg/setup.rs:259-271).  `gathered`: bytes-like, world x RECORD_BYTES.  Returns 0 when no shard failed."""
+    import struct
+    buf = bytes(gathered)
+    errs = [struct.unpack_from("<4i", buf, g * RECORD_BYTES + 320) for g in range(len(buf) // RECORD_BYTES)]
+    for k in range(3):
+        for e in errs:
+            if e[k]:
+                return e[k]
+    return 0
+
+
 class BatchVerifier:
     """verify_blob_kzg_proof_batch sharded over the ranks of a torch.distributed process group: every rank computes the
-    320-byte partial record of its contiguous shard on its GPU, ONE all_gather (NCCL over NVLink) exchanges the
+    336-byte partial record (sums + first error of each class) of its contiguous shard on its GPU, ONE all_gather (NCCL over NVLink) exchanges the
     records, and every rank finishes (sum of records -> two-pairing check on the host)."""
 
     def __init__(self, setup, group=None):
         self.setup, self.group = setup, group
 
     def verify(self, d_blobs, d_comm48, d_proofs48, n_local, index_offset, n_total, d_status, record_tensor, gathered_tensor):
+        """Returns (rc, ok): rc is the batch's error on EVERY rank (kateth's order: first blob error in rank order, else first
+        commitment error, else first proof error -- the errors travel inside the records), ok the verdict when rc == 0."""
         import torch.distributed as dist
         rc = self.setup.verify_partial_device(d_blobs, d_comm48, d_proofs48, n_local, index_offset, n_total, record_tensor.data_ptr(), d_status)
         if rc < 0:
             _check(rc)
         dist.all_gather_into_tensor(gathered_tensor, record_tensor, group=self.group)
         world = gathered_tensor.numel() // RECORD_BYTES
-        return rc, self.setup.verify_finish_device(gathered_tensor.data_ptr(), world)
+        ok = C.c_int(0)
+        rc = lib().kb200_verify_batch_finish_device(self.setup._h, _vp(gathered_tensor.data_ptr()), C.c_size_t(world), C.byref(ok))
+        if rc < 0:
+            _check(rc)
+        return rc, bool(ok.value) if rc == 0 else None
 
 
 class test_hooks:

@@ -4,7 +4,9 @@ The multi-GPU algorithm of batch verification (kateth_b200.setup.B
 shard shard_bounds(n, world, g), reduces it to a record {A_g, B_g, C_g, s_g} with weights that use the GLOBAL index, the
 records are exchanged with ONE all-gather, every rank combines them into the two pairing operands.  Here the per-shard
 records are computed with the oracle's G1 arithmetic (the CUDA engine needs a GPU), exchanged over gloo in the engine's
-320-byte wire size, and the combined operands must equal the oracle's single-call sums."""
+336-byte wire size (sums + the shard's first error of each class), and the combined operands must equal the oracle's
+single-call sums.  A second exchange plants errors in the shards: every rank must read the SAME batch error off the records,
+in kateth's order (blob errors of any rank before commitment errors before proof errors)."""
 import hashlib, os, sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -13,7 +15,7 @@ import torch
 import torch.distributed as dist
 import reconstruct_vectors as RV
 from oracle import oracle as O
-from kateth_b200.setup import shard_bounds, RECORD_BYTES
+from kateth_b200.setup import shard_bounds, RECORD_BYTES, batch_error_of_records
 
 R = RV.R
 
@@ -40,7 +42,7 @@ def main():
     else:
         A = B = Cc = RV.INF; sg = 0
     rec = torch.zeros(RECORD_BYTES, dtype=torch.uint8)
-    rec[:176] = torch.frombuffer(bytearray(A + B + Cc + be(sg)), dtype=torch.uint8)     # 3 x 48 + 32 bytes inside the 320-byte slot
+    rec[:176] = torch.frombuffer(bytearray(A + B + Cc + be(sg)), dtype=torch.uint8)     # 3 x 48 + 32 bytes inside the record slot
     gathered = torch.zeros(world * RECORD_BYTES, dtype=torch.uint8)
     dist.all_gather_into_tensor(gathered, rec)                                         # the ONLY data-path collective
     lhs, rhs, ssum = RV.INF, RV.INF, 0
@@ -51,6 +53,16 @@ def main():
     rhs = O.g1_add(rhs, O.g1_lincomb([RV.G1], [be(R - ssum)]))
     want = s.verify_blob_proof_batch_sums(blobs, cs, ps)
     assert (lhs, rhs) == want, "rank %d: sharded operands differ from the single-call sums" % rank
+    assert batch_error_of_records(gathered.numpy().tobytes()) == 0
+    # errors travel with the records: rank 0's shard has a bad proof (class 2 of the record), the last rank's a bad blob (class 0)
+    import struct
+    rec2 = rec.clone()
+    if rank == 0:
+        rec2[320:336] = torch.frombuffer(bytearray(struct.pack("<4i", 0, 0, 4, 0)), dtype=torch.uint8)
+    if rank == world - 1:
+        rec2[320:336] = torch.frombuffer(bytearray(struct.pack("<4i", 2, 0, 4 if rank == 0 else 0, 0)), dtype=torch.uint8)
+    dist.all_gather_into_tensor(gathered, rec2)
+    assert batch_error_of_records(gathered.numpy().tobytes()) == 2, "rank %d: the blob error of the last rank must win" % rank
     ok = torch.tensor([1], dtype=torch.int32)
     dist.all_reduce(ok, op=dist.ReduceOp.MIN)
     assert int(ok) == 1

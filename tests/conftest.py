@@ -16,11 +16,54 @@ def oracle_setup():
     return O.Setup.load_json(SETUP_JSON)
 
 
-@pytest.fixture(scope="session")
-def engine_setup():
-    """The CUDA engine with its default (shipping) configuration.  Fails loudly without the built .so or a GPU."""
+# ---- the CUDA engine under test -----------------------------------------------------------------------------------------
+# Every engine test runs in BOTH configurations that ship: the library default (window_bits 0 -> c = 13, 28.6 GiB table) and the
+# one bench.py measures (window_bits 16 -> GLV, 8 shared windows, 100 GiB table).  One 100 GiB table and a second big one do not
+# fit in HBM together, so at most one engine is alive at a time: `engine(wb)` closes whatever else is loaded, and tests that load
+# their own setups take the `gpu_free` fixture first.
+_ENGINES = {}
+ENGINE_CONFIGS = [0, 16]
+
+
+def release_engines():
+    for k in list(_ENGINES):
+        _ENGINES.pop(k).close()
+
+
+def engine(wb):
     import kateth_b200 as K
-    wb = int(os.environ.get("KB200_WINDOW_BITS", "0"))
-    s = K.Setup.load_json(SETUP_JSON, device=0, window_bits=wb)
-    yield s
-    s.close()
+    if wb not in _ENGINES:
+        release_engines()
+        _ENGINES[wb] = K.Setup.load_json(SETUP_JSON, device=0, window_bits=wb)
+    return _ENGINES[wb]
+
+
+@pytest.fixture(scope="session", params=ENGINE_CONFIGS, ids=lambda wb: "c13" if wb == 0 else "glv%d" % wb)
+def engine_setup(request):
+    """The CUDA engine (fails loudly without the built .so or a GPU).  KB200_WINDOW_BITS pins one configuration."""
+    wb = request.param
+    if "KB200_WINDOW_BITS" in os.environ and int(os.environ["KB200_WINDOW_BITS"]) != wb:
+        pytest.skip("KB200_WINDOW_BITS pins another configuration")
+    yield _Proxy(wb)
+
+
+class _Proxy:
+    """Resolves to the live engine of one configuration on every use (another test may have released it in between)."""
+
+    def __init__(self, wb):
+        self._wb = wb
+
+    def __getattr__(self, name):
+        return getattr(engine(self._wb), name)
+
+
+@pytest.fixture
+def gpu_free():
+    """For tests that load their own setups: nothing else may hold HBM."""
+    release_engines()
+    yield
+    release_engines()
+
+
+def pytest_sessionfinish(session, exitstatus):
+    release_engines()

@@ -95,8 +95,9 @@ def test_golden_blob_proof_and_in_domain_proofs(engine_setup):
 
 
 # ---------------------------------------------------------------- all 253 vectors through the engine
-def test_all_253_vectors_through_engine():
-    counts, bad, missing = RV.check_all("engine")
+def test_all_253_vectors_through_engine(engine_setup):
+    engine_setup.set_msm_mode(0)
+    counts, bad, missing = RV.check_all("engine", setup=engine_setup)
     assert sum(counts.values()) == 253
     assert not bad, bad[:5]
     assert not missing
@@ -181,12 +182,14 @@ def test_sharded_partials_equal_single_call(engine_setup):
     d_b = torch.frombuffer(bytearray(cat), dtype=torch.uint8).to(dev)
     d_c = torch.frombuffer(bytearray(comm), dtype=torch.uint8).to(dev)
     d_p = torch.frombuffer(bytearray(proofs), dtype=torch.uint8).to(dev)
-    recs = torch.zeros(3 * 320, dtype=torch.uint8, device=dev)
+    import kateth_b200 as K
+    RB = K.RECORD_BYTES
+    recs = torch.zeros(3 * RB, dtype=torch.uint8, device=dev)
     st = torch.zeros(n, dtype=torch.int32, device=dev)
     bounds = [(0, 3), (3, 4), (4, 10)]
     for g, (lo, hi) in enumerate(bounds):
         rc = engine_setup.verify_partial_device(d_b.data_ptr() + lo * 131072, d_c.data_ptr() + lo * 48, d_p.data_ptr() + lo * 48, hi - lo, lo, n,
-                                                recs.data_ptr() + g * 320, st.data_ptr() + 4 * lo)
+                                                recs.data_ptr() + g * RB, st.data_ptr() + 4 * lo)
         assert rc == 0
     assert engine_setup.verify_finish_device(recs.data_ptr(), 3) is True
     assert engine_setup.last_pairing_operands() == single
@@ -204,7 +207,7 @@ GLV_N = 0xac45a4010001a4020000000100000000      # x^2; r = N^2 - N + 1 (kateth_b
 
 
 @pytest.mark.parametrize("wb,mode", [(9, 1), (15, 1), (9, 2), (13, 2), (15, 2), (109, 1), (109, 2), (111, 2), (16, 1), (16, 2)])
-def test_other_window_width_gives_same_bytes(wb, mode, oracle_setup):
+def test_other_window_width_gives_same_bytes(wb, mode, oracle_setup, gpu_free):
     """The window width is a tuning knob, not a semantic one.  15 is the widest plain table (17 windows, the top one unsigned
     and 15 bits wide, 107 GiB); 9 exercises a 3-bit top window; 16 and 100 + c are the GLV form (two 128-bit halves per scalar
     on ceil(128 / c) windows, the second half mapped through the endomorphism)."""
@@ -296,16 +299,20 @@ def test_subgroup_check_matches_definition(engine_setup):
 
 
 # ---------------------------------------------------------------- batch-affine MSM: all vectors, and a degenerate setup
-def test_all_253_vectors_through_batch_affine_msm(monkeypatch):
-    monkeypatch.setenv("KB200_MSM_MODE", "2")
-    counts, bad, missing = RV.check_all("engine")
+def test_all_253_vectors_through_batch_affine_msm(engine_setup):
+    engine_setup.set_msm_mode(2)
+    try:
+        counts, bad, missing = RV.check_all("engine", setup=engine_setup)
+        assert engine_setup.info()["last_msm_batch_affine"] == 1
+    finally:
+        engine_setup.set_msm_mode(0)
     assert sum(counts.values()) == 253
     assert not bad, bad[:5]
     assert not missing
 
 
-@pytest.mark.parametrize("mode,wb", [(1, 9), (2, 9), (1, 109), (2, 109)])
-def test_degenerate_setup_exercises_exceptional_additions(mode, wb, tmp_path):
+@pytest.mark.parametrize("mode,wb", [(1, 9), (2, 9), (1, 109), (2, 109), (2, 13), (2, 116), (2, 16)])
+def test_degenerate_setup_exercises_exceptional_additions(mode, wb, tmp_path, gpu_free):
     """A setup whose Lagrange points are small multiples of the generator makes gathered table points and partial sums
     collide all the time (P == Q, P == -Q, infinity): the complete-formula paths of both MSM shapes must still give the
     group element the oracle's Pippenger gives."""
@@ -368,7 +375,8 @@ def test_consensus_spec_batch_challenge(engine_setup, oracle_setup):
         import torch
         d = lambda b: torch.frombuffer(bytearray(b), dtype=torch.uint8).cuda()
         db, dc, dp = d(cat), d(comm), d(proofs)
-        rec = torch.zeros(320, dtype=torch.uint8, device="cuda"); st = torch.zeros(n, dtype=torch.int32, device="cuda")
+        import kateth_b200 as K
+        rec = torch.zeros(K.RECORD_BYTES, dtype=torch.uint8, device="cuda"); st = torch.zeros(n, dtype=torch.int32, device="cuda")
         assert s.verify_partial_device(db.data_ptr(), dc.data_ptr(), dp.data_ptr(), 2, 0, n, rec.data_ptr(), st.data_ptr()) == -20
     finally:
         s.set_batch_challenge(0)
@@ -445,7 +453,7 @@ def test_host_batches_copied_in_two_pieces(engine_setup, oracle_setup):
     assert [k for k in range(len(good)) if st3[k] != 0] == [1000]
 
 
-def test_txt_setup_gives_the_same_engine(tmp_path):
+def test_txt_setup_gives_the_same_engine(tmp_path, gpu_free):
     import json
     import kateth_b200 as K
     d = json.load(open(os.path.join(ROOT, "tests/golden/trusted_setup_4096.json")))
@@ -490,8 +498,164 @@ def test_full_size_batch_checksum_of_checksums(engine_setup, oracle_setup):
     assert engine_setup.verify_blob_proof_batch_concat(cat, comm, bytes(bad), n) is False
     gb = bytearray(cat); gb[131072 * 2048 + 131071] ^= 1
     assert engine_setup.verify_blob_proof_batch_concat(bytes(gb), comm, proofs, n) is False
-    # (3) sample against the oracle
-    for i in (0, 591, 592, 2047, 4095):
+    # (3) sample against the oracle: every position of the persistent loop of k_msm_ba (592 resident CTAs pull items from a counter:
+    # first wave, wave boundaries, later waves, the last item)
+    assert engine_setup.info()["ba_grid"] == 592
+    for i in (0, 1, 591, 592, 593, 1183, 1184, 1775, 1776, 2047, 2368, 2959, 2960, 3551, 3552, 4094, 4095):
         b = cat[131072 * i:131072 * (i + 1)]
         assert cs[i] == oracle_setup.blob_to_commitment(b), i
         assert proofs[48 * i:48 * i + 48] == oracle_setup.blob_proof(b, cs[i]), i
+
+
+# ---------------------------------------------------------------- sharded batches: errors travel with the records, empty shards
+def test_sharded_errors_reach_every_rank(engine_setup, oracle_setup):
+    """SURVEY 8e + kateth's error order (src/kzg/setup.rs:259-271: all blobs, then all commitments, then all proofs).  A shard with
+    an invalid item returns that error itself AND writes it into its record; whoever finishes the gathered records gets the
+    error kateth would return for the whole batch, never a verdict computed from unvalidated terms."""
+    import torch
+    import kateth_b200 as K
+    RB = K.RECORD_BYTES
+    n = 7
+    blobs = [rand_blob(7000 + i) for i in range(n)]
+    cat = b"".join(blobs)
+    comm, _ = engine_setup.blob_to_commitment_many(cat, n)
+    proofs, _ = engine_setup.blob_proof_many(cat, comm, n)
+    dev = torch.device("cuda:0")
+    up = lambda b: torch.frombuffer(bytearray(b), dtype=torch.uint8).to(dev)
+    bounds = [(0, 3), (3, 5), (5, 7)]
+
+    def run(cat_, comm_, proofs_, bounds_=bounds, total=n):
+        d_b, d_c, d_p = up(cat_), up(comm_), up(proofs_)
+        recs = torch.zeros(len(bounds_) * RB, dtype=torch.uint8, device=dev)
+        st = torch.zeros(max(total, 1), dtype=torch.int32, device=dev)
+        rcs = []
+        for g, (lo, hi) in enumerate(bounds_):
+            rcs.append(engine_setup.verify_partial_device(d_b.data_ptr() + lo * 131072, d_c.data_ptr() + lo * 48, d_p.data_ptr() + lo * 48, hi - lo, lo, total,
+                                                          recs.data_ptr() + g * RB, st.data_ptr() + 4 * lo))
+        ok = __import__("ctypes").c_int(-1)
+        rc = K.lib().kb200_verify_batch_finish_device(engine_setup._h, __import__("ctypes").c_void_p(recs.data_ptr()), len(bounds_), __import__("ctypes").byref(ok))
+        return rcs, rc, ok.value, st.cpu().tolist()
+
+    assert run(cat, comm, proofs) == ([0, 0, 0], 0, 1, [0] * n)
+    # a proof that is not a curve point in shard 1, a non-canonical blob in shard 2: every finisher reports the BLOB error
+    badp = bytearray(proofs); badp[48 * 4:48 * 5] = RV.INVALID_G1[3]
+    badb = bytearray(cat); badb[131072 * 6 + 32 * 9:131072 * 6 + 32 * 10] = RV.be32(R)
+    rcs, rc, ok, st = run(bytes(badb), comm, bytes(badp))
+    assert rcs == [0, 4, 2] and rc == 2 and ok == 0 and st == [0, 0, 0, 0, 4, 0, 2]
+    # only the bad proof: its class; and the single-call entry points agree
+    rcs, rc, ok, st = run(cat, comm, bytes(badp))
+    assert rcs == [0, 4, 0] and rc == 4 and ok == 0
+    with pytest.raises(K.KzgError) as e:
+        engine_setup.verify_blob_proof_batch_concat(cat, comm, bytes(badp), n)
+    assert e.value.status == 4
+    # a commitment outside G1 in shard 0 and the bad proof in shard 1: commitments come before proofs
+    badc = bytearray(comm); badc[0:48] = RV.INVALID_G1[2]
+    rcs, rc, ok, st = run(cat, bytes(badc), bytes(badp))
+    assert rcs == [5, 4, 0] and rc == 5
+    # the failing item is left out of the sums: dropping it from the batch by hand gives the same operands as ... nothing to
+    # compare (an error has no verdict), but a WRONG proof (valid point) still only flips the verdict
+    wrong = bytearray(proofs); wrong[48 * 4:48 * 5] = proofs[0:48]
+    assert run(cat, comm, bytes(wrong))[1:3] == (0, 0)
+    # empty shards: a batch of one over three ranks
+    rcs, rc, ok, st = run(cat[:131072], comm[:48], proofs[:48], [(0, 0), (0, 1), (1, 1)], 1)
+    assert rcs == [0, 0, 0] and rc == 0 and ok == 1
+    assert engine_setup.last_pairing_operands() == oracle_setup.verify_blob_proof_batch_sums(blobs[:1], [comm[:48]], [proofs[:48]])
+
+
+def test_batches_larger_than_a_chunk(engine_setup, oracle_setup):
+    """The host-buffer entry points work in chunks of 4096 blobs: outputs, statuses, error order and the batch verdict must not
+    depend on where the chunk boundary falls (4100 blobs: the second chunk holds 4), in either batch-challenge mode."""
+    import torch
+    import kateth_b200 as K
+    n = 4100
+    base = [rand_blob(8000 + i) for i in range(3)] + [b"".join(RV.fe(R - 2 - k) for k in range(4096))]
+    want_c = [oracle_setup.blob_to_commitment(b) for b in base]
+    want_p = [oracle_setup.blob_proof(b, c) for b, c in zip(base, want_c)]
+    idx = [(i * 7 + i // 5) % len(base) for i in range(n)]
+    bad_at = 4098                                      # second chunk
+    blobs = [base[k] for k in idx]
+    b = bytearray(blobs[bad_at]); b[32 * 17:32 * 18] = RV.be32(R + 1); blobs[bad_at] = bytes(b)
+    cat = b"".join(blobs)
+    comm, st = engine_setup.blob_to_commitment_many(cat, n)
+    assert [i for i in range(n) if st[i]] == [bad_at] and st[bad_at] == 2
+    assert all(comm[48 * i:48 * i + 48] == want_c[idx[i]] for i in range(n) if i != bad_at)
+    good = [i for i in range(n) if i != bad_at] + [0]                # 4100 again, all valid; the chunk boundary moved by one
+    gcat = b"".join(blobs[i] for i in good); gcomm = b"".join(want_c[idx[i]] for i in good)
+    proofs, st2 = engine_setup.blob_proof_many(gcat, gcomm, n)
+    assert st2 == [0] * n and all(proofs[48 * k:48 * k + 48] == want_p[idx[i]] for k, i in enumerate(good))
+    zs = b"".join(RV.fe(int.from_bytes(hashlib.sha256(b"zc%d" % (i % 5)).digest(), "big")) for i in range(n))
+    pr, ys, st3 = engine_setup.proof_many(gcat, zs, n)
+    assert st3 == [0] * n
+    for k in (0, 4095, 4096, 4099):
+        assert (pr[48 * k:48 * k + 48], ys[32 * k:32 * k + 32]) == oracle_setup.proof(blobs[good[k]], zs[32 * k:32 * k + 32]), k
+    for mode in (0, 1):
+        engine_setup.set_batch_challenge(mode)
+        try:
+            assert engine_setup.verify_blob_proof_batch_concat(gcat, gcomm, proofs, n) is True
+            if mode == 0:
+                single = engine_setup.last_pairing_operands()
+            wrong = bytearray(proofs); wrong[48 * 4097:48 * 4098] = proofs[48 * 4098:48 * 4099] if proofs[48 * 4097:48 * 4098] != proofs[48 * 4098:48 * 4099] else proofs[48 * 4099:48 * 4100]
+            assert engine_setup.verify_blob_proof_batch_concat(gcat, gcomm, bytes(wrong), n) is False
+            # error order across chunks: a bad proof in chunk 0 and a bad blob in chunk 1 -> the blob error
+            badp = bytearray(proofs); badp[0:48] = RV.INVALID_G1[3]
+            bb = bytearray(gcat); bb[131072 * 4097 + 64:131072 * 4097 + 96] = RV.be32(R)
+            with pytest.raises(K.KzgError) as e:
+                engine_setup.verify_blob_proof_batch_concat(bytes(bb), gcomm, bytes(badp), n)
+            assert e.value.status == 2
+            with pytest.raises(K.KzgError) as e:
+                engine_setup.verify_blob_proof_batch_concat(gcat, gcomm, bytes(badp), n)
+            assert e.value.status == 4
+        finally:
+            engine_setup.set_batch_challenge(0)
+    # the host-buffer shard call has no size limit either: one "rank" holding all 4100 blobs, finished from its record
+    rec = torch.zeros(K.RECORD_BYTES, dtype=torch.uint8, device="cuda")
+    assert engine_setup.verify_partial_host(gcat, gcomm, proofs, n, 0, n, rec.data_ptr()) == 0
+    assert engine_setup.verify_finish_device(rec.data_ptr(), 1) is True
+    assert engine_setup.last_pairing_operands() == single
+
+
+def test_concurrent_callers_share_one_handle(engine_setup, oracle_setup):
+    """kateth's Setup is Send + Sync and its tests share it through an Arc (src/kzg/setup.rs:323): four host threads hammer ONE
+    handle with commit / blob-proof / proof-at-z / verify calls on their own blobs; every output must equal the oracle's."""
+    import threading
+    blobs = [rand_blob(9000 + i) for i in range(4)]
+    want = []
+    for b in blobs:
+        c = oracle_setup.blob_to_commitment(b)
+        want.append((c, oracle_setup.blob_proof(b, c)))
+    errors = []
+
+    def worker(t):
+        try:
+            b, (c, p) = blobs[t], want[t]
+            for it in range(6):
+                assert engine_setup.blob_to_commitment(b) == c
+                assert engine_setup.blob_proof(b, c) == p
+                assert engine_setup.verify_blob_proof(b, c, p) is True
+                assert engine_setup.verify_blob_proof(b, c, want[(t + 1) % 4][1]) is False
+                k = 2 + (t + it) % 3
+                cat = b"".join(blobs[(t + j) % 4] for j in range(k))
+                comm, st = engine_setup.blob_to_commitment_many(cat, k)
+                assert st == [0] * k and comm == b"".join(want[(t + j) % 4][0] for j in range(k))
+                assert engine_setup.verify_blob_proof_batch_concat(cat, comm, b"".join(want[(t + j) % 4][1] for j in range(k)), k) is True
+        except BaseException as ex:                      # noqa: B036 -- reported by the main thread
+            errors.append((t, repr(ex)))
+
+    th = [threading.Thread(target=worker, args=(t,)) for t in range(4)]
+    for x in th: x.start()
+    for x in th: x.join()
+    assert not errors, errors
+
+
+def test_first_error_follows_blob_order(engine_setup):
+    """kateth decodes blob by blob (src/kzg/setup.rs:259-262): [blob with a non-canonical element, blob one byte short] is
+    InvalidFieldElement, the reverse order is InvalidLen."""
+    import kateth_b200 as K
+    good = rand_blob(9100)
+    bad_el = bytearray(good); bad_el[32 * 5:32 * 6] = RV.be32(R); bad_el = bytes(bad_el)
+    short = good[:-1]
+    c = engine_setup.blob_to_commitment(good); p = engine_setup.blob_proof(good, c)
+    for blobs, want in (([good, bad_el, short], 2), ([good, short, bad_el], 1), ([short], 1)):
+        with pytest.raises(K.KzgError) as e:
+            engine_setup.verify_blob_proof_batch(blobs, [c] * len(blobs), [p] * len(blobs))
+        assert e.value.status == want

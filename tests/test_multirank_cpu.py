@@ -1,4 +1,4 @@
-"""The N > 1 host logic on CPU (world_size 2, gloo): shard bounds + global-index weights + one all-gather of the 320-byte
+"""The N > 1 host logic on CPU (world_size 2, gloo): shard bounds + global-index weights + one all-gather of the 336-byte
 records reproduce the single-call pairing operands; and the reference arm of bench.py under torchrun prints exactly one
 JSON line from rank 0 while the other rank exits 0 without work."""
 import json, os, subprocess, sys

@@ -114,7 +114,11 @@ class Err(Exception):
     pass
 
 
-def get_backend(name):
+def get_backend(name, setup=None):
+    if name == "engine" and setup is not None:       # a live engine handed in by the caller (tests/: one engine at a time fits HBM)
+        import kateth_b200 as K
+        from oracle import oracle as O
+        return setup, K.KzgError, O.g1_add
     if name == "oracle":
         from oracle import oracle as O
         s = O.Setup.load_json(os.path.join(ROOT, "tests/golden/trusted_setup_4096.json"))
@@ -244,9 +248,9 @@ def cases(setup, errcls, g1_add):
     yield h, "verify_blob_kzg_proof_batch_case_proof_length_different", vbb(VB, comm, bproof[:-1])
 
 
-def check_all(backend="oracle", write=None, verbose=False):
+def check_all(backend="oracle", write=None, verbose=False, setup=None):
     oids = json.load(open(os.path.join(ROOT, "tests/golden/lfs_oids.json")))
-    setup, errcls, g1_add = get_backend(backend)
+    setup, errcls, g1_add = get_backend(backend, setup)
     seen, bad = {}, []
     for handler, case, data in cases(setup, errcls, g1_add):
         exp = oids.get(handler, {}).get(case)
