@@ -14,7 +14,7 @@
 
 #include "../../include/kateth_b200.h"
 #include "verify.cuh"
-#include "msm_ba.cuh"
+#include "msm_ba_api.hpp"
 #include "host_bls.hpp"
 
 using namespace kb200;
@@ -78,7 +78,6 @@ struct kb200_setup {
     DBuf sha_state;                         // chaining values between the pieces, [8][n] words
     bool z_ready = false;                   // the challenges of the next proof / verify pass are already in s->z
     bool fork_recorded = false;             // ev_fork already marks the point of the main stream the point decompression may start from
-    BaOffset ba_off{};
     uint8_t last_lhs[48], last_rhs[48];
     bool have_last = false;
     // optional CUDA-event timing of the dominant kernel (k_msm), for bench.py's roofline
@@ -295,13 +294,10 @@ static int build_setup(kb200_setup* s, const uint8_t* g1, const uint8_t* g2, int
     CU(cudaStreamSynchronize(s->stream));
     CU(cudaGetLastError());
     s->tab.data = s->d_table; s->tab.c = c; s->tab.nwin = nwin; s->tab.dlast = dlast; s->tab.glv = glv;
-    {   // batch-affine MSM: signed-digit offset, persistent grid, work counter
-        memset(&s->ba_off, 0, sizeof s->ba_off);
-        for (int j = 0; j < nwin - 1; j++) { int bit = c * j + c - 1; s->ba_off.l[bit >> 5] |= 1u << (bit & 31); }
-        int occ = 0;
-        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_msm_ba, BA_THREADS, 0));
-        if (occ < 1) occ = 1;
-        s->ba_grid = occ * s->sm_count;
+    {   // batch-affine MSM (its own translation unit, msm_ba.cu): persistent grid, work counter
+        BaPlan plan;
+        if (ba_init(&plan) != 0) { snprintf(g_err, sizeof g_err, "ba_init: %s", cudaGetErrorString(cudaGetLastError())); return KB200_E_CUDA; }
+        s->ba_grid = plan.ctas_per_sm * s->sm_count;
         CU(cudaMalloc(&s->d_counter, sizeof(unsigned int)));
         CU(cudaStreamCreateWithFlags(&s->aux_stream, cudaStreamNonBlocking));
         CU(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming));
@@ -481,11 +477,12 @@ static int run_msm(kb200_setup* s, const uint32_t* d_scalars, size_t n, const in
     if (int rc = s->partials.ensure(n * S * sizeof(G1))) return rc;
     unsigned grid = 0;
     if (ba) {
-        const size_t K1 = (size_t)BA_UB * s->tab.nwin * (s->tab.glv + 1) / 2;
         grid = (unsigned)((n < (size_t)s->ba_grid) ? n : (size_t)s->ba_grid);
-        if (int rc = s->dig.ensure(n * KB_N * (size_t)s->tab.nwin * (s->tab.glv + 1) * 4)) return rc;
-        if (int rc = s->scr_pts.ensure((size_t)s->ba_grid * K1 * 6 * BA_THREADS * sizeof(uint4))) return rc;
-        if (int rc = s->scr_pre.ensure((size_t)s->ba_grid * K1 * 3 * BA_THREADS * sizeof(uint4))) return rc;
+        size_t dig_b, pts_b, pre_b;
+        ba_workspace(s->tab, s->ba_grid, n, &dig_b, &pts_b, &pre_b);
+        if (int rc = s->dig.ensure(dig_b)) return rc;
+        if (int rc = s->scr_pts.ensure(pts_b)) return rc;
+        if (int rc = s->scr_pre.ensure(pre_b)) return rc;
     }
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (s->prof) {
@@ -495,11 +492,8 @@ static int run_msm(kb200_setup* s, const uint32_t* d_scalars, size_t n, const in
     }
     if (ba) {
         CU(cudaMemsetAsync(s->d_counter, 0, sizeof(unsigned int), s->stream));
-        LAUNCH(s, (k_msm_recode<FMT>), blocks(n * KB_N, 256), 256, s->tab, s->ba_off, d_scalars, d_status, s->dig.as<uint32_t>(), (int)n);
-        BaArgs a;
-        a.tab = s->tab; a.dig = s->dig.as<uint32_t>(); a.scr_pts = s->scr_pts.as<uint4>(); a.scr_pre = s->scr_pre.as<uint4>();
-        a.partials = s->partials.as<G1>(); a.status = d_status; a.counter = s->d_counter; a.n = (int)n;
-        LAUNCH(s, k_msm_ba, grid, BA_THREADS, a);
+        ba_launch(s->tab, FMT, d_scalars, d_status, s->dig.as<uint32_t>(), s->scr_pts.p, s->scr_pre.p, s->partials.as<G1>(), s->d_counter, (int)n, grid, s->stream);
+        s->launches += 2;      // k_msm_recode + k_msm_ba
     } else {
         LAUNCH(s, (k_msm<FMT>), (unsigned)(n * S), MSM_THREADS, s->tab, d_scalars, d_status, s->partials.as<G1>(), S);
     }

@@ -169,7 +169,7 @@ KB_HD int bg_inverse(uint32_t (&out)[12], const uint32_t (&x)[12]) {
 
 #if defined(__CUDACC__)
 // r = a^-1 in Montgomery form (a = x*R  ->  r = x^-1 * R):  (x*R)^-1 * R^3 * R^-1.  0 -> 0 like fp_inv.
-__device__ __noinline__ void fp_inv_bgcd(Fp& r, const Fp& a) {
+static __device__ __noinline__ void fp_inv_bgcd(Fp& r, const Fp& a) {
     const uint32_t r3[12] = {0xd94ca1e0u, 0xed48ac6bu, 0x03a7adf8u, 0x315f831eu, 0x615e29ddu, 0x9a53352au, 0x921e1761u, 0x34c04e5eu, 0x65724728u, 0x2512d435u, 0x91755d4du, 0x0aa63460u};
     uint32_t t[12];
     if (bg_inverse(t, a.l)) { fp_mul(r.l, t, r3); return; }

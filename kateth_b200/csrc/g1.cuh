@@ -25,7 +25,7 @@ __device__ __forceinline__ void g1_from_affine(G1& r, const G1Affine& p) {
 }
 
 // r = 2*(x, y) for an affine, finite point
-__device__ __noinline__ void g1_dbl_affine(G1& r, const Fp& x, const Fp& y) {
+static __device__ __noinline__ void g1_dbl_affine(G1& r, const Fp& x, const Fp& y) {
     Fp u, v, w, s, m, t;
     fp_dbl(u, y); fp_sqr(v, u); fp_mul(w, u, v); fp_mul(s, x, v);
     fp_sqr(m, x); fp_dbl(t, m); fp_add(m, m, t);
@@ -34,7 +34,7 @@ __device__ __noinline__ void g1_dbl_affine(G1& r, const Fp& x, const Fp& y) {
     r.zz = v; r.zzz = w;
 }
 // p = 2*p
-__device__ __noinline__ void g1_dbl(G1& p) {
+static __device__ __noinline__ void g1_dbl(G1& p) {
     if (g1_is_inf(p)) return;
     Fp u, v, w, s, m, t;
     fp_dbl(u, p.y); fp_sqr(v, u); fp_mul(w, u, v); fp_mul(s, p.x, v);
@@ -45,7 +45,7 @@ __device__ __noinline__ void g1_dbl(G1& p) {
     fp_mul(p.zz, v, p.zz); fp_mul(p.zzz, w, p.zzz);
 }
 // rare paths of the mixed addition, kept out of line so the hot loop stays small
-__device__ __noinline__ void g1_madd_rare(G1* acc, const Fp* x2, const Fp* y2, bool same_y) {
+static __device__ __noinline__ void g1_madd_rare(G1* acc, const Fp* x2, const Fp* y2, bool same_y) {
     if (same_y) { G1 t; g1_dbl_affine(t, *x2, *y2); *acc = t; } else g1_set_inf(*acc);
 }
 // acc += (x2, y2)   [affine, finite].  8M + 2S on the common path.
@@ -67,7 +67,7 @@ __device__ __forceinline__ void g1_madd_signed(G1& acc, const G1Affine& pt, bool
     g1_madd(acc, pt.x, y);
 }
 // acc += b   (both XYZZ).  12M + 2S on the common path.
-__device__ __noinline__ void g1_add(G1& acc, const G1& b) {
+static __device__ __noinline__ void g1_add(G1& acc, const G1& b) {
     if (g1_is_inf(b)) return;
     if (g1_is_inf(acc)) { acc = b; return; }
     Fp u1, u2, s1, s2, p, r, pp, ppp, q, t;
@@ -85,7 +85,7 @@ __device__ __noinline__ void g1_add(G1& acc, const G1& b) {
     fp_mul(acc.zzz, acc.zzz, b.zzz); fp_mul(acc.zzz, acc.zzz, ppp);
 }
 // XYZZ -> affine (one field inversion)
-__device__ __noinline__ void g1_to_affine(G1Affine& r, const G1& p) {
+static __device__ __noinline__ void g1_to_affine(G1Affine& r, const G1& p) {
     if (g1_is_inf(p)) { fp_zero(r.x); fp_zero(r.y); return; }
     Fp i3, zi, i2;
     fp_inv_bgcd(i3, p.zzz);                  // Z^-3 (branchless binary GCD, fp_bgcd.cuh; same value as a^(p-2))
@@ -93,7 +93,7 @@ __device__ __noinline__ void g1_to_affine(G1Affine& r, const G1& p) {
     fp_mul(r.x, p.x, i2); fp_mul(r.y, p.y, i3);
 }
 // r = [k]P for a plain 255-bit scalar (little-endian limbs); MSB-first double-and-add  (blst_p1_mult(..., 255))
-__device__ __noinline__ void g1_mul(G1& r, const G1Affine& p, const Fr& k, int nbits = 255) {
+static __device__ __noinline__ void g1_mul(G1& r, const G1Affine& p, const Fr& k, int nbits = 255) {
     G1 acc; g1_set_inf(acc);
     if (!g1a_is_inf(p)) {
 #pragma unroll 1
@@ -140,7 +140,7 @@ __device__ __forceinline__ void g1_compress(uint32_t* out12, const G1Affine& p) 
 #define KB_SCALAR_NOT_IN_FIELD 7
 
 // in12: the 48 bytes as 12 words (memory order).  Curve check only (blst_p1_uncompress).
-__device__ __noinline__ int g1_uncompress(G1Affine& r, const uint32_t* in12) {
+static __device__ __noinline__ int g1_uncompress(G1Affine& r, const uint32_t* in12) {
     uint32_t w0 = __byte_perm(in12[0], 0, 0x0123);
     if (!(w0 & 0x80000000u)) return KB_G1_INVALID_ENCODING;
     if (w0 & 0x40000000u) {
@@ -168,7 +168,7 @@ __device__ __noinline__ int g1_uncompress(G1Affine& r, const uint32_t* in12) {
 // acc = [|x|] base, |x| = 0xd201000000010000 (the BLS parameter; bits 63, 62, 60, 57, 48, 16), MSB-first double-and-add.
 // AFFINE = true: base is the affine point (bx, by); false: base is the XYZZ point *bz.
 template <bool AFFINE>
-__device__ __noinline__ void g1_mul_bls_x(G1& acc, const Fp& bx, const Fp& by, const G1* bz) {
+static __device__ __noinline__ void g1_mul_bls_x(G1& acc, const Fp& bx, const Fp& by, const G1* bz) {
     const uint64_t X = 0xd201000000010000ull;
     if (AFFINE) { acc.x = bx; acc.y = by; fp_set(acc.zz, c_k.fp_one); fp_set(acc.zzz, c_k.fp_one); } else acc = *bz;
 #pragma unroll 1
@@ -182,7 +182,7 @@ __device__ __noinline__ void g1_mul_bls_x(G1& acc, const Fp& bx, const Fp& by, c
 // curve is in G1 iff that holds (Scott, "A note on group membership tests for G1, G2 and GT on BLS pairing-friendly curves",
 // 2021 -- the test blst uses).  126 doublings + 10 additions instead of the 255 + 128 of [r]P == infinity; checked against the
 // definition on random curve points, cofactor-cleared points and small-order torsion points (tests/test_gpu_parity.py).
-__device__ __noinline__ bool g1_in_subgroup(const G1Affine& p) {
+static __device__ __noinline__ bool g1_in_subgroup(const G1Affine& p) {
     if (g1a_is_inf(p)) return true;
     G1 t1, t2;
     g1_mul_bls_x<true>(t1, p.x, p.y, nullptr);
@@ -197,7 +197,7 @@ __device__ __noinline__ bool g1_in_subgroup(const G1Affine& p) {
     return fp_eq(l, ry);
 }
 // the definition, kept for the unit test that pins the fast test: [r]P == infinity
-__device__ __noinline__ bool g1_in_subgroup_by_order(const G1Affine& p) {
+static __device__ __noinline__ bool g1_in_subgroup_by_order(const G1Affine& p) {
     if (g1a_is_inf(p)) return true;
     Fr k; fr_set(k, c_k.fr_mod);
     G1 t; g1_mul(t, p, k);

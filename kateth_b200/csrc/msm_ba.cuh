@@ -21,7 +21,7 @@
 // The scalars are recoded once per MSM by k_msm_recode into 32-bit table row references (signed digits: adding
 // 2^(c-1) to every window below the top one turns the unsigned window value v into the signed digit v - 2^(c-1)).
 #pragma once
-#include "msm.cuh"
+#include "msm_table.cuh"
 #include "fp_bgcd.cuh"
 
 namespace kb200 {
@@ -31,6 +31,14 @@ namespace kb200 {
 #define BA_UB (1 << BA_UB_LOG)     // bases per unit per thread; a unit is reduced by BA_UB_LOG halving rounds
 #define BA_UNITS (KB_N / (BA_THREADS * BA_UB))   // units per thread (one CTA = one blob)
 #define BA_ZERO 0xffffffffu        // digit 0: nothing to add
+// workspace shape (msm_ba.cu sizes the buffers from these): scratch points / prefix products per CTA, in units of K1 = pairs of round 1
+#ifndef BA_SMEM_BYTES
+#define BA_SMEM_BYTES 0            // dynamic shared memory of k_msm_ba
+#endif
+#define BA_PTS_SLOTS_NUM 1
+#define BA_PTS_SLOTS_DEN 1
+#define BA_PRE_SLOTS_NUM 1
+#define BA_PRE_SLOTS_DEN 1
 
 struct BaOffset { uint32_t l[8]; };     // sum_{j < nwin-1} 2^(c-1) * 2^(c*j)
 
@@ -38,7 +46,7 @@ struct BaOffset { uint32_t l[8]; };     // sum_{j < nwin-1} 2^(c-1) * 2^(c*j)
 // in different phases (prefix products, inversion, additions, final accumulation) at the same time; with the 400-
 // instruction product inlined at every call site the instruction working set is > 100 KB and the warps stall on
 // instruction fetch (ncu: no_instructions 28 %).  Arguments and result travel in registers (by-value structs: no stack).
-__device__ __noinline__ Fp fp_mulc(Fp a, Fp b) { Fp r; fp_mul(r, a, b); return r; }
+static __device__ __noinline__ Fp fp_mulc(Fp a, Fp b) { Fp r; fp_mul(r, a, b); return r; }
 #define BA_MUL(r, a, b) r = fp_mulc(a, b)
 #define BA_SQR(r, a) r = fp_mulc(a, a)
 
@@ -95,7 +103,7 @@ __device__ __forceinline__ void ba_add(G1& acc, const G1& b) {
     BA_MUL(acc.zzz, acc.zzz, b.zzz); BA_MUL(acc.zzz, acc.zzz, ppp);
 }
 // inversion on the shared product (fp_inv_bgcd, fp_bgcd.cuh)
-__device__ __noinline__ Fp ba_inv(Fp a) {
+static __device__ __noinline__ Fp ba_inv(Fp a) {
     Fp r3 = {{0xd94ca1e0u, 0xed48ac6bu, 0x03a7adf8u, 0x315f831eu, 0x615e29ddu, 0x9a53352au, 0x921e1761u, 0x34c04e5eu, 0x65724728u, 0x2512d435u, 0x91755d4du, 0x0aa63460u}};
     Fp t;
     if (bg_inverse(t.l, a.l)) return fp_mulc(t, r3);
@@ -259,7 +267,7 @@ __device__ __forceinline__ int ba_i1(int k, int Kh) { return k + (k >= Kh ? Kh :
 // Exceptional pairs (an operand at infinity, or x1 == x2) leave the hot loops through these two out-of-line functions;
 // they re-read their operands themselves so that nothing in the hot loops has its address taken.
 // Denominator: 2*y1 for a doubling, else 1 (nothing to invert).
-__device__ __noinline__ Fp ba_rare_den(BaCtx c, int round, int k, int Kh) {
+static __device__ __noinline__ Fp ba_rare_den(BaCtx c, int round, int k, int Kh) {
     const int i1 = ba_i1(k, Kh), i2 = i1 + Kh;
     BaRef r1 = ba_ref(c, round, i1, round == 0 ? ba_digit(c, i1) : 0u), r2 = ba_ref(c, round, i2, round == 0 ? ba_digit(c, i2) : 0u);
     Fp den, x1, x2;
@@ -272,7 +280,7 @@ __device__ __noinline__ Fp ba_rare_den(BaCtx c, int round, int k, int Kh) {
 }
 // Sum of an exceptional pair, written to scratch slot k; returns the running inverse advanced exactly as the forward pass
 // advanced the running product.
-__device__ __noinline__ Fp ba_rare_add(BaCtx c, int round, int k, int Kh, Fp inv, Fp pk) {
+static __device__ __noinline__ Fp ba_rare_add(BaCtx c, int round, int k, int Kh, Fp inv, Fp pk) {
     const int o1 = ba_i1(k, Kh), o2 = o1 + Kh;
     BaRef r1 = ba_ref(c, round, o1, round == 0 ? ba_digit(c, o1) : 0u), r2 = ba_ref(c, round, o2, round == 0 ? ba_digit(c, o2) : 0u);
     Fp x1, y1, x2, y2, x3, y3;

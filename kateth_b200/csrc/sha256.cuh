@@ -38,6 +38,5 @@ __device__ __forceinline__ void sha256_block(uint32_t h[8], uint32_t w[16]) {
     }
     h[0] += a; h[1] += b; h[2] += c; h[3] += d; h[4] += e; h[5] += f; h[6] += g; h[7] += hh;
 }
-__device__ __forceinline__ uint32_t bswap32(uint32_t x) { return __byte_perm(x, 0, 0x0123); }
 
 }  // namespace kb200

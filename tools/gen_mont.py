@@ -162,7 +162,7 @@ def gen_addsub(name, n, mod):
 def main():
     out = "// GENERATED by tools/gen_mont.py -- do not edit.\n#pragma once\n#include <stdint.h>\nnamespace kb200 {\n\n__device__ __forceinline__ uint32_t opaque_zero() { uint32_t l; asm volatile(\"mov.u32 %0, %%laneid;\" : \"=r\"(l)); return l >> 5; }\n\n"
     out += gen_addsub("fp", 12, P) + gen_mul("fp", 12, P, (-pow(P, -1, 1 << 32)) % (1 << 32))
-    out += "__device__ __constant__ uint32_t FR_MOD_C[8] = {%s};\n\n" % ", ".join("0x%08xu" % x for x in limbs(R, 8))
+    out += "static __device__ __constant__ uint32_t FR_MOD_C[8] = {%s};\n\n" % ", ".join("0x%08xu" % x for x in limbs(R, 8))
     out += gen_addsub("fr", 8, R) + gen_mul("fr", 8, R, (-pow(R, -1, 1 << 32)) % (1 << 32))
     out += "} // namespace kb200\n"
     with open(os.path.join(ROOT, "kateth_b200", "csrc", "mont_gen.cuh"), "w") as f:
