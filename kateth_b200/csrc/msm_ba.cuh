@@ -32,8 +32,19 @@ namespace kb200 {
 #define BA_UNITS (KB_N / (BA_THREADS * BA_UB))   // units per thread (one CTA = one blob)
 #define BA_ZERO 0xffffffffu        // digit 0: nothing to add
 // workspace shape (msm_ba.cu sizes the buffers from these): scratch points / prefix products per CTA, in units of K1 = pairs of round 1
+// BA_STAGE 1 (default): the operands of the next pair are copied into shared memory with cp.async while the current pair is being
+// added, and read from there (LDS) when they are needed -- nothing waits on HBM inside the loops, and the operands that an addition
+// needs again late (x1, x2, y1) are re-read from shared memory instead of being held in registers across the products (the kernel
+// sits at the 128-register cap: held, they spill).  Per thread: two buffers of {x1, x2, y1} (the next pair lands in the other
+// one), single slots for {prefix product, y2} (consumed before the next pair is requested) and one slot for the digits of the
+// pair after that: 25 x 16 bytes, 50 KiB per CTA; the forward pass uses the same bytes as a two-deep ring of (x1, x2).
+// BA_STAGE 0: round 1's kernel (operands loaded into registers at the top of each pair; A/B reference).
+#ifndef BA_STAGE
+#define BA_STAGE 1
+#endif
 #ifndef BA_SMEM_BYTES
-#define BA_SMEM_BYTES 0            // dynamic shared memory of k_msm_ba
+#define BA_STAGE_SLOTS 25
+#define BA_SMEM_BYTES (BA_STAGE ? BA_STAGE_SLOTS * BA_THREADS * 16 : 0)            // dynamic shared memory of k_msm_ba
 #endif
 #define BA_PTS_SLOTS_NUM 1
 #define BA_PTS_SLOTS_DEN 1
@@ -305,9 +316,74 @@ static __device__ __noinline__ Fp ba_rare_add(BaCtx c, int round, int k, int Kh,
     return inv;
 }
 
+
+#if BA_STAGE
+extern __shared__ uint4 ba_smem[];      // [15][BA_THREADS]: column `tid` belongs to thread tid alone (no barriers needed)
+// 16 bytes global -> shared, asynchronously; bytes == 0 writes zeros without touching the source (an operand at infinity)
+__device__ __forceinline__ void ba_cp16(uint4* sdst, const uint4* gsrc, int bytes) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"((uint32_t)__cvta_generic_to_shared(sdst)), "l"(gsrc), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void ba_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void ba_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+// one coordinate of operand r (q0 = 0: x, 3: y) -> slots [c0, c0 + 3) of this thread's column
+__device__ __forceinline__ void ba_stage_fp(uint4* st, int c0, const BaRef& r, int q0) {
+    const uint4* p = r.p + (size_t)q0 * r.stride;
+    const int bytes = r.zero ? 0 : 16;
+#pragma unroll
+    for (int q = 0; q < 3; q++) ba_cp16(st + (c0 + q) * BA_THREADS, p + (size_t)q * r.stride, bytes);
+}
+__device__ __forceinline__ void ba_lds(Fp& r, const uint4* st, int c0) {
+    const uint4 a = st[c0 * BA_THREADS], b = st[(c0 + 1) * BA_THREADS], c = st[(c0 + 2) * BA_THREADS];
+    r.l[0] = a.x; r.l[1] = a.y; r.l[2] = a.z; r.l[3] = a.w; r.l[4] = b.x; r.l[5] = b.y; r.l[6] = b.z; r.l[7] = b.w;
+    r.l[8] = c.x; r.l[9] = c.y; r.l[10] = c.z; r.l[11] = c.w;
+}
+// slot map of the backward pass: buffer b in {0, 1}: x1 -> 9b, x2 -> 9b + 3, y1 -> 9b + 6;  prefix product -> 18, y2 -> 21;  digits -> 24
+#define BA_SLOT_PK 18
+#define BA_SLOT_Y2 21
+#define BA_SLOT_DIG 24
+__device__ __forceinline__ void ba_sts(uint4* st, int c0, const Fp& r) {
+    st[c0 * BA_THREADS] = make_uint4(r.l[0], r.l[1], r.l[2], r.l[3]);
+    st[(c0 + 1) * BA_THREADS] = make_uint4(r.l[4], r.l[5], r.l[6], r.l[7]);
+    st[(c0 + 2) * BA_THREADS] = make_uint4(r.l[8], r.l[9], r.l[10], r.l[11]);
+}
+// the two digits of pair k (table round only) -> words w0, w0 + 1 of the digit slot
+__device__ __forceinline__ void ba_stage_digits(uint4* st, int w0, const BaCtx& C, int k, int Kh) {
+    const int i1 = ba_i1(k, Kh);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(st + BA_SLOT_DIG * BA_THREADS) + w0;
+    const uint32_t* g = C.dg + (size_t)i1 * BA_THREADS;
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(g) : "memory");
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst + 1)), "l"(g + (size_t)Kh * BA_THREADS) : "memory");
+}
+// backward pass: operands of pair k -> buffer b and the single slots (one commit group, together with whatever digits were
+// requested before); returns the sign bits of the two operands
+__device__ __forceinline__ uint32_t ba_stage_bwd(uint4* st, int b, const BaCtx& C, const uint4* pre, int round, int k, int Kh, uint32_t d1, uint32_t d2) {
+    const int i1 = ba_i1(k, Kh);
+    const BaRef r1 = ba_ref(C, round, i1, d1), r2 = ba_ref(C, round, i1 + Kh, d2);
+    ba_stage_fp(st, 9 * b, r1, 0); ba_stage_fp(st, 9 * b + 3, r2, 0);
+    const uint4* pp = pre + (size_t)k * 3 * BA_THREADS;
+#pragma unroll
+    for (int q = 0; q < 3; q++) ba_cp16(st + (BA_SLOT_PK + q) * BA_THREADS, pp + (size_t)q * BA_THREADS, 16);
+    ba_stage_fp(st, 9 * b + 6, r1, 3); ba_stage_fp(st, BA_SLOT_Y2, r2, 3);
+    ba_commit();
+    return (r1.neg ? 1u : 0u) | (r2.neg ? 2u : 0u);
+}
+// forward pass: x1, x2 of pair k -> slots [c0, c0 + 6)
+__device__ __forceinline__ void ba_stage_fwd(uint4* st, int c0, const BaCtx& C, int round, int k, int Kh, uint32_t d1, uint32_t d2) {
+    const int i1 = ba_i1(k, Kh);
+    const BaRef r1 = ba_ref(C, round, i1, d1), r2 = ba_ref(C, round, i1 + Kh, d2);
+    ba_stage_fp(st, c0, r1, 0); ba_stage_fp(st, c0 + 3, r2, 0);
+    ba_commit();
+}
+#endif
+
 __global__ void __launch_bounds__(BA_THREADS, 4) k_msm_ba(BaArgs A) {
     static_assert(BA_UNITS == 1, "the GLV map below is applied to the accumulator of one unit");
+#if BA_STAGE
+    G1* const sm = reinterpret_cast<G1*>(ba_smem);      // the tree reduction reuses the staging bytes (barriers on both sides)
+    static_assert(sizeof(G1) * (BA_THREADS / 2) <= BA_SMEM_BYTES, "reduction buffer");
+#else
     __shared__ G1 sm[BA_THREADS / 2];
+#endif
     __shared__ unsigned int s_item;
     const int tid = threadIdx.x;
     const int nwin = A.tab.nwin, halves = A.tab.glv + 1;
@@ -329,6 +405,96 @@ __global__ void __launch_bounds__(BA_THREADS, 4) k_msm_ba(BaArgs A) {
             for (int round = 0, Kh = (BA_UB / 2) * nwin; round < BA_UB_LOG; round++, Kh >>= 1) {
                 const bool tab = round == 0;
                 const int K = Kh * halves;
+#if BA_STAGE
+                uint4* const st = ba_smem + tid;
+                // ---- forward (k descending): prefix products of the denominators.  The x coordinates of pairs k-1 and k-2 are on
+                // their way into the two halves of the staging column while pair k is multiplied in.
+                Fp run; fp_set(run, c_k.fp_one);
+                {
+                    uint32_t dn1 = 0, dn2 = 0;          // digits of the pair that is staged next
+                    for (int q = 0; q < 2 && q < K; q++) {
+                        const int kk = K - 1 - q, i1 = ba_i1(kk, Kh);
+                        ba_stage_fwd(st, 6 * q, C, round, kk, Kh, tab ? ba_digit(C, i1) : 0u, tab ? ba_digit(C, i1 + Kh) : 0u);
+                    }
+                    if (tab && K > 2) { const int i1 = ba_i1(K - 3, Kh); dn1 = ba_digit(C, i1); dn2 = ba_digit(C, i1 + Kh); }
+#pragma unroll 1
+                    for (int k = K - 1; k >= 0; k--) {
+                        const int c0 = ((K - 1 - k) & 1) * 6;
+                        if (k > 0) ba_wait<1>(); else ba_wait<0>();
+                        Fp x1, x2, d;
+                        ba_lds(x1, st, c0); ba_lds(x2, st, c0 + 3);
+                        ba_st(pre + (size_t)k * 3 * BA_THREADS, run);
+                        fp_sub(d, x2, x1);
+                        if (fp_is_zero(x1) || fp_is_zero(x2) || fp_is_zero(d)) d = ba_rare_den(C, round, k, Kh);
+                        if (k >= 2) {
+                            ba_stage_fwd(st, c0, C, round, k - 2, Kh, dn1, dn2);
+                            if (tab && k >= 3) { const int i1 = ba_i1(k - 3, Kh); dn1 = ba_digit(C, i1); dn2 = ba_digit(C, i1 + Kh); }
+                        }
+                        fp_mul(run, run, d);
+                    }
+                }
+                Fp inv = ba_inv(run);
+                // ---- backward (k ascending): the additions.  Pair k+1 is requested as soon as the single slots of pair k are consumed
+                // (after the first product); x1, x2 and y1 of pair k stay in their buffer and are read again where the formulas use them.
+                {
+                    uint32_t negs_next;
+                    uint32_t* const sdig = reinterpret_cast<uint32_t*>(st + BA_SLOT_DIG * BA_THREADS);
+                    {
+                        const int i1 = ba_i1(0, Kh);
+                        if (tab && K > 1) ba_stage_digits(st, 2, C, 1, Kh);       // digits of pair 1 -> words 2, 3 (same group as pair 0)
+                        negs_next = ba_stage_bwd(st, 0, C, pre, round, 0, Kh, tab ? ba_digit(C, i1) : 0u, tab ? ba_digit(C, i1 + Kh) : 0u);
+                    }
+#pragma unroll 1
+                    for (int k = 0; k < K; k++) {
+                        const int b = k & 1;
+                        ba_wait<0>();
+                        const uint32_t negs = negs_next;
+                        // Order of work: what is live across a product call must fit the registers the product leaves alone, so
+                        // values are read from the staging column right where the formulas use them.
+                        Fp d, pk;
+                        bool rare;
+                        {
+                            Fp x1, x2;
+                            ba_lds(x1, st, 9 * b); ba_lds(x2, st, 9 * b + 3);
+                            fp_sub(d, x2, x1);
+                            rare = fp_is_zero(x1) || fp_is_zero(x2) || fp_is_zero(d);
+                            ba_lds(pk, st, BA_SLOT_PK);
+                        }
+                        const uint32_t dn1 = sdig[2 * (b ^ 1)], dn2 = sdig[2 * (b ^ 1) + 1];     // digits of pair k + 1 (requested one pair ago)
+                        if (rare) {
+                            inv = ba_rare_add(C, round, k, Kh, inv, pk);
+                            if (k + 1 < K) {
+                                if (tab && k + 2 < K) ba_stage_digits(st, 2 * b, C, k + 2, Kh);
+                                negs_next = ba_stage_bwd(st, b ^ 1, C, pre, round, k + 1, Kh, dn1, dn2);
+                            }
+                        } else {
+                            Fp dinv, t, lam, x3, y3;
+                            BA_MUL(dinv, inv, pk);
+                            BA_MUL(inv, inv, d);
+                            {
+                                Fp y1, y2;
+                                { Fp r; ba_lds(r, st, 9 * b + 6); fp_cneg(y1, r, (negs & 1u) != 0); }
+                                { Fp r; ba_lds(r, st, BA_SLOT_Y2); fp_cneg(y2, r, (negs & 2u) != 0); }
+                                ba_sts(st, 9 * b + 6, y1);                               // the signed y1 is needed again for y3
+                                fp_sub(t, y2, y1);
+                            }
+                            // the single slots (prefix product, y2) and the digit words are consumed: request pair k + 1 into the other
+                            // buffer; three products remain to cover its way from HBM
+                            if (k + 1 < K) {
+                                if (tab && k + 2 < K) ba_stage_digits(st, 2 * b, C, k + 2, Kh);
+                                negs_next = ba_stage_bwd(st, b ^ 1, C, pre, round, k + 1, Kh, dn1, dn2);
+                            }
+                            BA_MUL(lam, t, dinv);
+                            BA_SQR(x3, lam);
+                            { Fp x1, x2; ba_lds(x1, st, 9 * b); ba_lds(x2, st, 9 * b + 3); fp_sub(x3, x3, x1); fp_sub(x3, x3, x2); fp_sub(t, x1, x3); }
+                            BA_MUL(t, lam, t);
+                            { Fp y1; ba_lds(y1, st, 9 * b + 6); fp_sub(y3, t, y1); }
+                            uint4* o = pts + (size_t)k * 6 * BA_THREADS;
+                            ba_st(o, x3); ba_st(o + 3 * BA_THREADS, y3);
+                        }
+                    }
+                }
+#else
                 // ---- forward (k descending): prefix products of the denominators.  Operands of the next pair are loaded
                 // before the product of this pair is issued, the digits of the pair after that before that.
                 Fp run; fp_set(run, c_k.fp_one);
@@ -384,6 +550,7 @@ __global__ void __launch_bounds__(BA_THREADS, 4) k_msm_ba(BaArgs A) {
                         }
                     }
                 }
+#endif
             }
             // the nwin sums of each half -> XYZZ accumulator; the k2 half first, mapped through Q = (beta x, -y) as one sum
 #pragma unroll 1
@@ -399,6 +566,9 @@ __global__ void __launch_bounds__(BA_THREADS, 4) k_msm_ba(BaArgs A) {
             }
         }
         // CTA tree reduction through shared memory
+#if BA_STAGE
+        __syncthreads();        // every warp is out of its loops: the staging columns are free
+#endif
 #pragma unroll 1
         for (int stride = BA_THREADS / 2; stride >= 1; stride >>= 1) {
             if (tid >= stride && tid < 2 * stride) sm[tid - stride] = acc;
