@@ -11,8 +11,11 @@ One "step" = one pass of the hot path over one batch of synthetic canonical-fiel
     host two-pairing check).
 `value` times the step with inputs resident in HBM; `e2e` times the same step through the host-buffer C-ABI calls with the
 blobs in pinned host memory (H2D of the blobs and D2H of commitments/proofs/verdict inside the timed region).
-Under torchrun every rank owns `--blobs` blobs (weak scaling); the only collective is the all-gather of the batch-verify records.
-Prints ONE JSON line on rank 0.
+Under torchrun every rank owns `--blobs` blobs (weak scaling, the default) or `--global-blobs` / N of them (`--scaling strong`:
+BASELINE configs[3]'s 16,384-blob batch cut over the GPUs).  The multi-GPU path is the C ABI's own: every rank joins the library's
+group (kb200_group_create_rank; the unique id travels over torch.distributed), and batch verification is ONE
+kb200_group_verify_blob_proof_batch* call per rank -- shard partial, ncclAllGather of the 336-byte records, host pairing, all inside
+the library.  Prints ONE JSON line on rank 0.
 """
 import argparse, json, os, subprocess, sys, threading, time
 
@@ -156,8 +159,17 @@ def run_engine(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     n = args.blobs
+    if args.scaling == "strong":
+        if args.global_blobs % world:
+            raise SystemExit("bench.py: --global-blobs must be a multiple of the number of GPUs")
+        n = args.global_blobs // world
     s = K.Setup.load_json(SETUP_JSON, device=local, window_bits=args.window_bits)
     s.set_stream(torch.cuda.current_stream().cuda_stream)
+    # the library's own multi-GPU group: rank 0's NCCL unique id goes to the other ranks over the torch process group
+    uid = [K.Group.unique_id() if (rank == 0 and world > 1) else None]
+    if world > 1:
+        dist.broadcast_object_list(uid, src=0)
+    g = K.Group.join(s, rank, world, uid[0])
     info0 = s.info()
     peak_wide, peak_fp = K.test_hooks.mac_peak(16384) if rank == 0 else (0.0, 0.0)
 
@@ -168,23 +180,17 @@ def run_engine(args):
     d_comm = torch.empty(n * 48, dtype=torch.uint8, device=dev)
     d_proof = torch.empty(n * 48, dtype=torch.uint8, device=dev)
     d_status = torch.zeros(n, dtype=torch.int32, device=dev)
-    d_rec = torch.zeros(K.RECORD_BYTES, dtype=torch.uint8, device=dev)
-    d_all = torch.zeros(world * K.RECORD_BYTES, dtype=torch.uint8, device=dev)
 
     def check(rc, what):
         if rc != 0:
             raise SystemExit("bench.py: %s returned status %d (%s)" % (what, rc, K.lib().kb200_last_error().decode()))
 
-    def finish():
-        if world > 1:
-            dist.all_gather_into_tensor(d_all, d_rec)          # the ONLY data-path collective: 336 bytes per rank over NVLink
-            ok = s.verify_finish_device(d_all.data_ptr(), world)
-        else:
-            ok = s.verify_finish_device(d_rec.data_ptr(), 1)
-        if not ok:
-            raise SystemExit("bench.py: batch verification of the engine's own proofs returned false")
-
     stage_ev = []
+
+    def verdict(rc, ok, what, want=True):
+        check(rc, what)
+        if ok is not want:
+            raise SystemExit("bench.py: %s returned %s, expected %s" % (what, ok, want))
 
     def step_resident(record):
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)] if record else None
@@ -193,17 +199,15 @@ def run_engine(args):
         if record: ev[1].record()
         check(s.blob_proof_device(d_blobs.data_ptr(), d_comm.data_ptr(), n, d_proof.data_ptr(), d_status.data_ptr()), "compute_blob_proof")
         if record: ev[2].record()
-        check(s.verify_partial_device(d_blobs.data_ptr(), d_comm.data_ptr(), d_proof.data_ptr(), n, rank * n, world * n, d_rec.data_ptr(),
-                                      d_status.data_ptr()), "verify_blob_proof_batch(partial)")
-        finish()
+        # shard partial + the ONLY data-path collective (ncclAllGather of 336 bytes per rank over NVLink) + pairing: one C-ABI call
+        verdict(*g.verify_device([d_blobs.data_ptr()], [d_comm.data_ptr()], [d_proof.data_ptr()], [n], rank * n, world * n, [d_status.data_ptr()]),
+                "group_verify_blob_proof_batch_device")
         if record: ev[3].record(); stage_ev.append(ev)
 
     def step_e2e():
         check(s.blob_to_commitment_host(h_blobs.data_ptr(), n, h_comm.data_ptr()), "blob_to_commitment(host)")
         check(s.blob_proof_host(h_blobs.data_ptr(), h_comm.data_ptr(), n, h_proof.data_ptr()), "compute_blob_proof(host)")
-        check(s.verify_partial_host(h_blobs.data_ptr(), h_comm.data_ptr(), h_proof.data_ptr(), n, rank * n, world * n, d_rec.data_ptr()),
-              "verify_blob_proof_batch(host, partial)")
-        finish()
+        verdict(*g.verify_host(h_blobs.data_ptr(), h_comm.data_ptr(), h_proof.data_ptr(), n, rank * n, world * n), "group_verify_blob_proof_batch(host)")
 
     def barrier():
         if world > 1:
@@ -246,19 +250,14 @@ def run_engine(args):
     d_bad = d_proof.clone()
     if rank == 0 and n > 1:
         d_bad[48:96] = d_proof[0:48]
-    check(s.verify_partial_device(d_blobs.data_ptr(), d_comm.data_ptr(), d_bad.data_ptr(), n, rank * n, world * n, d_rec.data_ptr(), d_status.data_ptr()),
-          "verify_blob_proof_batch(partial, corrupted)")
-    if world > 1:
-        dist.all_gather_into_tensor(d_all, d_rec)
-        corrupted_verdict = s.verify_finish_device(d_all.data_ptr(), world)
-    else:
-        corrupted_verdict = s.verify_finish_device(d_rec.data_ptr(), 1)
-    if corrupted_verdict is not False:
-        raise SystemExit("bench.py: a batch with one corrupted proof verified as true")
+    verdict(*g.verify_device([d_blobs.data_ptr()], [d_comm.data_ptr()], [d_bad.data_ptr()], [n], rank * n, world * n, [d_status.data_ptr()]),
+            "group_verify_blob_proof_batch_device(one corrupted proof)", want=False)
     # parity guard inside the bench: the host-buffer path and the resident path must agree byte for byte
     if not (torch.equal(h_comm, d_comm.cpu()) and torch.equal(h_proof, d_proof.cpu())):
         raise SystemExit("bench.py: host-buffer and resident outputs differ")
-    return dict(rank=rank, world=world, n=n, s=s, ms_res=ms_res, ms_e2e=ms_e2e, e2e_steps=e2e_steps, clocks=clocks, launches=launches, prof=prof,
+    ginfo = g.info()
+    g.close()
+    return dict(rank=rank, world=world, n=n, s=s, ginfo=ginfo, ms_res=ms_res, ms_e2e=ms_e2e, e2e_steps=e2e_steps, clocks=clocks, launches=launches, prof=prof,
                 stage_ev=stage_ev, info=info0, peak=(peak_wide, peak_fp), h_blobs=h_blobs, h_comm=h_comm, h_proof=h_proof)
 
 
@@ -295,6 +294,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="engine", choices=["engine", "reference"])
     ap.add_argument("--blobs", type=int, default=4096, help="blobs per GPU per step (BASELINE configs[2]: 4096)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"], help="strong: --global-blobs are cut over the GPUs (north_star's scaling target)")
+    ap.add_argument("--global-blobs", type=int, default=16384, help="batch size of --scaling strong (BASELINE configs[3]: 16384)")
     ap.add_argument("--window-bits", type=int, default=int(os.environ.get("KB200_WINDOW_BITS", "16")),
                     help="fixed-base table window width: 15 = 17 windows, 107 GiB table; 16 = GLV form, 2 x 8 windows on a 100 GiB table; library default 13 = 28.6 GiB")
     ap.add_argument("--e2e-steps", type=int, default=3)
@@ -394,16 +395,16 @@ def main():
                         "caveat": "portable-C restatement of kateth's algorithm (oracle/), not blst's assembly with its thread-pooled Pippenger: kateth itself would be "
                                   "faster per core; Rust and blst are absent from this image, so it is the only CPU baseline obtainable here"}
     line = {"metric": METRIC, "value": value, "unit": "blobs/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32 limbs (Fp 12x32, Fr 8x32 Montgomery, IMAD.WIDE)",
+            "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "u32 limbs (Fp 12x32, Fr 8x32 Montgomery, IMAD.WIDE)",
             "data": "synthetic canonical field elements, uniform in [0, r)",
             "config": {"workload": "commit + compute_blob_kzg_proof + verify_blob_kzg_proof_batch over %d blobs per GPU (BASELINE configs[2] size; configs[3] sharding)" % n,
                        "blobs_per_gpu": n, "global_blobs": total, "window_bits": info["window_bits"], "windows": info["windows"], "glv": bool(info.get("glv", 0)), "points_per_scalar": W, "msm_shape": "batch-affine (k_msm_ba)" if ba else "xyzz (k_msm)",
-                       "table_gb": round(info["table_bytes"] / 2 ** 30, 2), "parallelism": "blob shards x%d, replicated tables, 1 all-gather of %d B" % (world, K_RECORD),
+                       "table_gb": round(info["table_bytes"] / 2 ** 30, 2), "parallelism": "blob shards x%d, replicated tables, 1 ncclAllGather of %d B per rank inside the C ABI (kb200_group_*, NCCL %s)" % (world, K_RECORD, r["ginfo"]["nccl_version"] or "not needed"),
                        "l2": "inputs (%d MiB of blobs + multi-GB table) exceed the 126 MB L2; no flush needed" % (n * BLOB >> 20)},
             "stages_ms": {"commit": stage[0], "prove": stage[1], "verify": stage[2]},
             "stage_blobs_per_s_per_gpu": {"commit": n / stage[0] * 1e3, "prove": n / stage[1] * 1e3, "verify": n / stage[2] * 1e3},
             "e2e": {"value": total / (ms_e2e * 1e-3), "unit": "blobs/s", "h2d_bytes_per_step": 3 * n * BLOB + 3 * n * 48, "d2h_bytes_per_step": 2 * n * 48 + 200 + 8 * n,
-                    "ms_per_step": ms_e2e, "steps": r["e2e_steps"], "api": "kb200_blob_to_commitment + kb200_compute_blob_proof + kb200_verify_blob_proof_batch_partial (pinned host buffers)"},
+                    "ms_per_step": ms_e2e, "steps": r["e2e_steps"], "api": "kb200_blob_to_commitment + kb200_compute_blob_proof + kb200_group_verify_blob_proof_batch (pinned host buffers)"},
             "gpu_launches": int(r["launches"]), "roofline": roofline, "cpu_baseline": cpu_baseline, "clocks": r["clocks"],
             "setup_seconds": info["setup_seconds"],
             "checks": {"valid_batch_verdict": True, "one_corrupted_proof_verdict": False, "host_buffer_outputs_equal_resident": True,

@@ -56,6 +56,7 @@ extern "C" {
 #define KB200_E_SETUP_G1_LEN (-10)         /* LoadSetupError::InvalidLenG1Lagrange */
 #define KB200_E_SETUP_G2_LEN (-11)         /* LoadSetupError::InvalidLenG2Monomial */
 #define KB200_E_ARG (-20)                  /* null pointer / bad argument */
+#define KB200_E_NCCL (-30)                 /* NCCL missing (dlopen libnccl.so.2) or a collective failed (kb200_last_error has the text) */
 
 typedef struct kb200_setup kb200_setup;
 
@@ -130,6 +131,43 @@ int kb200_verify_blob_proof_batch_partial(kb200_setup* s, const uint8_t* blobs, 
 int kb200_verify_batch_finish_device(kb200_setup* s, const void* d_records, size_t n_records, int* ok);
 /* The two compressed G1 operands of the final pairing check of the last finish call (for diffing intermediate sums). */
 int kb200_last_pairing_operands(kb200_setup* s, uint8_t lhs48[48], uint8_t rhs48[48]);
+
+/* ---- the same surface over several B200s (SURVEY.md 8b "Setup: devices, ndev", 8e): one replica of the setup per GPU, batches cut
+ *      into contiguous shards, one host thread + stream per GPU inside the library.  commit / prove need no communication; batch
+ *      verification has ONE exchange step, an ncclAllGather of the KB200_RECORD_BYTES records over NVLink done here (NCCL is bound at
+ *      run time with dlopen("libnccl.so.2"); a single-GPU caller never needs it), then ONE host pairing per process: one call,
+ *      one verdict, as Setup::verify_blob_proof_batch (src/kzg/setup.rs:247-275).  A group is safe for concurrent callers (calls on
+ *      one group are serialised: every rank must issue its collectives in the same order).
+ *      Two ways to form a group:
+ *        kb200_group_create_json   one process drives the `ndev` GPUs it names (devices == NULL: 0 .. ndev-1); the replicas are loaded
+ *                                  concurrently (Setup::load_json per device) and owned by the group; ncclCommInitAll.
+ *        kb200_group_create_rank   one process per GPU (torchrun / MPI / one service per device): rank 0 calls kb200_group_unique_id and
+ *                                  ships the 128 bytes to the other ranks by any means; every rank passes its own loaded handle
+ *                                  (not owned by the group) and joins with ncclCommInitRank. ---- */
+typedef struct kb200_group kb200_group;
+#define KB200_GROUP_ID_BYTES 128
+int kb200_group_create_json(const char* path, const int* devices, int ndev, int window_bits, kb200_group** out);
+int kb200_group_unique_id(uint8_t id128[KB200_GROUP_ID_BYTES]);
+int kb200_group_create_rank(kb200_setup* local, int rank, int world, const uint8_t id128[KB200_GROUP_ID_BYTES], kb200_group** out);
+void kb200_group_free(kb200_group* g);
+/* local_replicas: GPUs driven by this process; world: ranks of the whole group; first_rank: rank of local replica 0; nccl_version: 0 when
+ * the group has one rank (no communicator).  Any out pointer may be NULL. */
+int kb200_group_info(kb200_group* g, int* local_replicas, int* world, int* first_rank, int* nccl_version);
+kb200_setup* kb200_group_replica(kb200_group* g, int i); /* the i-th local handle (still owned by the group when it loaded it) */
+/* Host-buffer calls: n items, cut contiguously over the replicas of THIS process; outputs and statuses in item order. */
+int kb200_group_blob_to_commitment(kb200_group* g, const uint8_t* blobs, size_t n, uint8_t* out48, int32_t* status);
+int kb200_group_compute_blob_proof(kb200_group* g, const uint8_t* blobs, const uint8_t* commitments48, size_t n, uint8_t* out48, int32_t* status);
+int kb200_group_compute_proof(kb200_group* g, const uint8_t* blobs, const uint8_t* z32, size_t n, uint8_t* out_proof48, uint8_t* out_y32, int32_t* status);
+/* One batch of n_total items over the whole group: this process holds items [index_offset, index_offset + n_local) (a one-process group:
+ * index_offset = 0, n_local = n_total).  Every rank must make the call; every rank gets the verdict, or the batch's error in kateth's
+ * order (the errors travel inside the records). */
+int kb200_group_verify_blob_proof_batch(kb200_group* g, const uint8_t* blobs, const uint8_t* commitments48, const uint8_t* proofs48, size_t n_local,
+                                        size_t index_offset, size_t n_total, int* ok, int32_t* status);
+/* The same with the shards already in HBM: entry i of each array belongs to local replica i (device pointers on that replica's GPU),
+ * n_per_replica[i] items each, laid out one after the other from index_offset on. */
+int kb200_group_verify_blob_proof_batch_device(kb200_group* g, const void* const* d_blobs, const void* const* d_commitments48,
+                                               const void* const* d_proofs48, const size_t* n_per_replica, size_t index_offset, size_t n_total, int* ok,
+                                               int32_t* const* d_status);
 
 /* ---- random challenge of the batch checks.  0 (default) = kateth's: r = SHA-256("RCKZGBATCH___V1_" | u128(4096) | u128(n))
  *      mod r and weights [r, r, r^2, ...] (src/kzg/setup.rs:127-136, src/bls.rs:169-187) -- bit-for-bit parity with the reference.

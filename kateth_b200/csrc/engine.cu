@@ -21,6 +21,8 @@ using namespace kb200;
 
 static thread_local char g_err[512] = "";
 extern "C" const char* kb200_last_error(void) { return g_err; }
+// group.cpp reports through the same per-thread buffer (not part of the public header)
+extern "C" void kb200_internal_set_error(const char* msg) { snprintf(g_err, sizeof g_err, "%s", msg ? msg : ""); }
 #define CU(call)                                                                                          \
     do {                                                                                                  \
         cudaError_t e_ = (call);                                                                          \

@@ -317,6 +317,30 @@ static __device__ __noinline__ Fp ba_rare_add(BaCtx c, int round, int k, int Kh,
 }
 
 
+// r = neg ? p - a : a.  For a != 0 this is -a in one borrow chain (fp_cneg goes through 0 - a + p: two chains); a == 0 only occurs
+// for the (0, 0) infinity sentinel, whose pair leaves the hot loop through the rare path before y is used (no finite point of the
+// curve has y == 0: its group order is odd).
+__device__ __forceinline__ void ba_cneg_nz(Fp& r, const Fp& a, bool neg) {
+    uint32_t t[12];
+    asm volatile(
+        "sub.cc.u32 %0, 0xffffaaab, %12;\n\t"
+        "subc.cc.u32 %1, 0xb9feffff, %13;\n\t"
+        "subc.cc.u32 %2, 0xb153ffff, %14;\n\t"
+        "subc.cc.u32 %3, 0x1eabfffe, %15;\n\t"
+        "subc.cc.u32 %4, 0xf6b0f624, %16;\n\t"
+        "subc.cc.u32 %5, 0x6730d2a0, %17;\n\t"
+        "subc.cc.u32 %6, 0xf38512bf, %18;\n\t"
+        "subc.cc.u32 %7, 0x64774b84, %19;\n\t"
+        "subc.cc.u32 %8, 0x434bacd7, %20;\n\t"
+        "subc.cc.u32 %9, 0x4b1ba7b6, %21;\n\t"
+        "subc.cc.u32 %10, 0x397fe69a, %22;\n\t"
+        "subc.u32 %11, 0x1a0111ea, %23;\n\t"
+        : "=&r"(t[0]), "=&r"(t[1]), "=&r"(t[2]), "=&r"(t[3]), "=&r"(t[4]), "=&r"(t[5]), "=&r"(t[6]), "=&r"(t[7]), "=&r"(t[8]), "=&r"(t[9]), "=&r"(t[10]), "=&r"(t[11])
+        : "r"(a.l[0]), "r"(a.l[1]), "r"(a.l[2]), "r"(a.l[3]), "r"(a.l[4]), "r"(a.l[5]), "r"(a.l[6]), "r"(a.l[7]), "r"(a.l[8]), "r"(a.l[9]), "r"(a.l[10]), "r"(a.l[11]));
+#pragma unroll
+    for (int i = 0; i < 12; i++) r.l[i] = neg ? t[i] : a.l[i];
+}
+
 #if BA_STAGE
 extern __shared__ uint4 ba_smem[];      // [15][BA_THREADS]: column `tid` belongs to thread tid alone (no barriers needed)
 // 16 bytes global -> shared, asynchronously; bytes == 0 writes zeros without touching the source (an operand at infinity)
@@ -473,8 +497,8 @@ __global__ void __launch_bounds__(BA_THREADS, 4) k_msm_ba(BaArgs A) {
                             BA_MUL(inv, inv, d);
                             {
                                 Fp y1, y2;
-                                { Fp r; ba_lds(r, st, 9 * b + 6); fp_cneg(y1, r, (negs & 1u) != 0); }
-                                { Fp r; ba_lds(r, st, BA_SLOT_Y2); fp_cneg(y2, r, (negs & 2u) != 0); }
+                                { Fp r; ba_lds(r, st, 9 * b + 6); ba_cneg_nz(y1, r, (negs & 1u) != 0); }
+                                { Fp r; ba_lds(r, st, BA_SLOT_Y2); ba_cneg_nz(y2, r, (negs & 2u) != 0); }
                                 ba_sts(st, 9 * b + 6, y1);                               // the signed y1 is needed again for y3
                                 fp_sub(t, y2, y1);
                             }

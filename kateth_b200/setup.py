@@ -43,6 +43,9 @@ SYMBOLS = [
     "kb200_verify_blob_proof_batch", "kb200_verify_blob_proof_batch_device", "kb200_verify_blob_proof_batch_partial_device",
     "kb200_verify_blob_proof_batch_partial", "kb200_verify_batch_finish_device", "kb200_set_profiling", "kb200_set_msm_mode", "kb200_set_batch_challenge", "kb200_get_msm_profile", "kb200_last_pairing_operands", "kb200_get_info", "kb200_test_fp_mul", "kb200_test_fr_mul",
     "kb200_test_g1_decompress", "kb200_test_mac_peak", "kb200_test_host_pairing",
+    "kb200_group_create_json", "kb200_group_unique_id", "kb200_group_create_rank", "kb200_group_free", "kb200_group_info", "kb200_group_replica",
+    "kb200_group_blob_to_commitment", "kb200_group_compute_blob_proof", "kb200_group_compute_proof", "kb200_group_verify_blob_proof_batch",
+    "kb200_group_verify_blob_proof_batch_device",
 ]
 
 
@@ -56,10 +59,14 @@ def lib():
         _lib = C.CDLL(p)
         _lib.kb200_last_error.restype = C.c_char_p
         for name in SYMBOLS:
-            if name not in ("kb200_last_error", "kb200_setup_free"):
+            if name not in ("kb200_last_error", "kb200_setup_free", "kb200_group_free", "kb200_group_replica"):
                 getattr(_lib, name).restype = C.c_int
         _lib.kb200_setup_free.restype = None
         _lib.kb200_setup_free.argtypes = [C.c_void_p]
+        _lib.kb200_group_free.restype = None
+        _lib.kb200_group_free.argtypes = [C.c_void_p]
+        _lib.kb200_group_replica.restype = C.c_void_p
+        _lib.kb200_group_replica.argtypes = [C.c_void_p, C.c_int]
     return _lib
 
 
@@ -281,6 +288,115 @@ class Setup:
         ok = C.c_int(0)
         _check(lib().kb200_verify_batch_finish_device(self._h, _vp(d_records), C.c_size_t(n_records), C.byref(ok)))
         return bool(ok.value)
+
+
+class Group:
+    """kateth's Setup over several B200s, driven through the C ABI's kb200_group_* entry points (one replica per GPU, contiguous
+    shards, the all-gather of batch verification inside the library).  Two constructors: `load_json` (this process drives all the
+    listed devices) and `join` (one process per GPU: rank 0 makes `unique_id()`, every rank joins with its own Setup)."""
+
+    def __init__(self, handle, keep=None):
+        self._g, self._keep = handle, keep
+
+    @classmethod
+    def load_json(cls, path, devices=None, window_bits=0):
+        import torch
+        devs = list(range(torch.cuda.device_count())) if devices is None else list(devices)
+        arr = (C.c_int * len(devs))(*devs)
+        g = C.c_void_p()
+        _check(lib().kb200_group_create_json(os.fsencode(path), arr, len(devs), int(window_bits), C.byref(g)))
+        return cls(g)
+
+    @staticmethod
+    def unique_id():
+        buf = C.create_string_buffer(128)
+        _check(lib().kb200_group_unique_id(buf))
+        return buf.raw
+
+    @classmethod
+    def join(cls, setup, rank, world, unique_id):
+        g = C.c_void_p()
+        _check(lib().kb200_group_create_rank(setup._h, int(rank), int(world), bytes(unique_id) if unique_id else None, C.byref(g)))
+        return cls(g, keep=setup)
+
+    def close(self):
+        if self._g:
+            lib().kb200_group_free(self._g)
+            self._g = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def info(self):
+        a, b, c, d = C.c_int(0), C.c_int(0), C.c_int(0), C.c_int(0)
+        _check(lib().kb200_group_info(self._g, C.byref(a), C.byref(b), C.byref(c), C.byref(d)))
+        return {"local_replicas": a.value, "world": b.value, "first_rank": c.value, "nccl_version": d.value}
+
+    def replica(self, i):
+        """The i-th local handle as a (non-owning) Setup."""
+        h = lib().kb200_group_replica(self._g, int(i))
+        if not h:
+            raise IndexError(i)
+        s = Setup(C.c_void_p(h))
+        s.close = lambda: None        # owned by the group (or by the caller who passed it to join)
+        return s
+
+    @staticmethod
+    def _p(x):
+        return x if isinstance(x, (bytes, bytearray)) or x is None else _vp(x)
+
+    def blob_to_commitment_many(self, blobs, n):
+        out, st = C.create_string_buffer(48 * n), (C.c_int32 * n)()
+        rc = lib().kb200_group_blob_to_commitment(self._g, self._p(blobs), C.c_size_t(n), out, st)
+        if rc < 0:
+            _check(rc)
+        return out.raw, list(st)
+
+    def blob_proof_many(self, blobs, commitments, n):
+        out, st = C.create_string_buffer(48 * n), (C.c_int32 * n)()
+        rc = lib().kb200_group_compute_blob_proof(self._g, self._p(blobs), self._p(commitments), C.c_size_t(n), out, st)
+        if rc < 0:
+            _check(rc)
+        return out.raw, list(st)
+
+    def proof_many(self, blobs, zs, n):
+        out, y, st = C.create_string_buffer(48 * n), C.create_string_buffer(32 * n), (C.c_int32 * n)()
+        rc = lib().kb200_group_compute_proof(self._g, self._p(blobs), self._p(zs), C.c_size_t(n), out, y, st)
+        if rc < 0:
+            _check(rc)
+        return out.raw, y.raw, list(st)
+
+    def verify_blob_proof_batch(self, blobs, commitments, proofs, n_local, index_offset=0, n_total=None):
+        """Raises KzgError with the batch's error (the same on every rank), else returns the verdict."""
+        ok = C.c_int(0)
+        _check(lib().kb200_group_verify_blob_proof_batch(self._g, self._p(blobs), self._p(commitments), self._p(proofs), C.c_size_t(n_local),
+                                                         C.c_size_t(index_offset), C.c_size_t(n_local if n_total is None else n_total), C.byref(ok), None))
+        return bool(ok.value)
+
+    # raw-address forms for the bench (pinned host buffers / device pointers); return (rc, ok)
+    def blob_to_commitment_host(self, blobs_ptr, n, out48_ptr):
+        return lib().kb200_group_blob_to_commitment(self._g, _vp(blobs_ptr), C.c_size_t(n), _vp(out48_ptr), None)
+
+    def blob_proof_host(self, blobs_ptr, comm48_ptr, n, out48_ptr):
+        return lib().kb200_group_compute_blob_proof(self._g, _vp(blobs_ptr), _vp(comm48_ptr), C.c_size_t(n), _vp(out48_ptr), None)
+
+    def verify_host(self, blobs_ptr, comm48_ptr, proofs48_ptr, n_local, index_offset, n_total):
+        ok = C.c_int(0)
+        rc = lib().kb200_group_verify_blob_proof_batch(self._g, _vp(blobs_ptr), _vp(comm48_ptr), _vp(proofs48_ptr), C.c_size_t(n_local), C.c_size_t(index_offset),
+                                                       C.c_size_t(n_total), C.byref(ok), None)
+        return rc, bool(ok.value)
+
+    def verify_device(self, d_blobs, d_comm48, d_proofs48, n_per_replica, index_offset, n_total, d_status):
+        """Each argument: one entry per local replica (device addresses on that replica's GPU / item counts)."""
+        k = len(n_per_replica)
+        vp = lambda xs: (C.c_void_p * k)(*[int(x) for x in xs])
+        ok = C.c_int(0)
+        rc = lib().kb200_group_verify_blob_proof_batch_device(self._g, vp(d_blobs), vp(d_comm48), vp(d_proofs48), (C.c_size_t * k)(*n_per_replica),
+                                                              C.c_size_t(index_offset), C.c_size_t(n_total), C.byref(ok), vp(d_status))
+        return rc, bool(ok.value)
 
 
 def shard_bounds(n_total, world_size, rank):

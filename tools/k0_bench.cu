@@ -183,6 +183,65 @@ __global__ void __launch_bounds__(256) k_dfma_imad(double* out, int iters, doubl
     out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
+// 8b. co-issue, corrected: eight DFMA chains and eight IMAD.WIDE chains that share NO register (round 1's version fed the
+// multiplier from the accumulators of other chains, so its streams were not independent).  NI IMAD.WIDE per DFMA.
+template <int NI>
+__global__ void __launch_bounds__(256) k_dfma_imad_indep(double* out, int iters, double a, double b, uint32_t x, uint32_t y) {
+    double acc[8];
+    uint64_t w[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) { acc[k] = threadIdx.x + k; w[k] = threadIdx.x * 7 + k; }
+#pragma unroll 1
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            asm volatile("fma.rz.f64 %0, %0, %1, %2;" : "+d"(acc[k]) : "d"(a), "d"(b));
+#pragma unroll
+            for (int q = 0; q < NI; q++) asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(w[(k + 4 * q) & 7]) : "r"(x), "r"(y));
+        }
+    }
+    double s = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) s += acc[k] + (double)w[k];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+// 8c. the same eight IMAD.WIDE chains alone (the reference rate of 8b's integer stream)
+__global__ void __launch_bounds__(256) k_imad_indep8(uint64_t* out, int iters, uint32_t x, uint32_t y) {
+    uint64_t w[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) w[k] = threadIdx.x * 7 + k;
+#pragma unroll 1
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int k = 0; k < 8; k++) asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(w[k]) : "r"(x), "r"(y));
+    }
+    uint64_t s = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) s += w[k];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+// 8d. IADD3 stream beside DFMA (the integer adds a DFMA-based product would need): 1 DFMA + NA IADD3, no shared registers
+template <int NA>
+__global__ void __launch_bounds__(256) k_dfma_iadd(double* out, int iters, double a, double b, uint32_t x) {
+    double acc[8];
+    uint32_t w[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) { acc[k] = threadIdx.x + k; w[k] = threadIdx.x * 7 + k; }
+#pragma unroll 1
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            asm volatile("fma.rz.f64 %0, %0, %1, %2;" : "+d"(acc[k]) : "d"(a), "d"(b));
+#pragma unroll
+            for (int q = 0; q < NA; q++) asm volatile("add.u32 %0, %0, %1;" : "+r"(w[(k + 3 * q) & 7]) : "r"(x));
+        }
+    }
+    double s = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) s += acc[k] + (double)w[k];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
 template <class F>
 static int run(const char* name, F launch, double ops_per_thread_iter, int iters, int grid, int block, int sms, double clock_ghz) {
     cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
@@ -208,6 +267,16 @@ int main(int argc, char** argv) {
     printf("%s: %d SMs, clockRate %.3f GHz\n", p.name, sms, ghz);
     void* buf; CK(cudaMalloc(&buf, (size_t)sms * 8 * 256 * 8));
     int iters = 20000;
+    {   // ONE warp per SM sub-partition (1 CTA of 128 threads per SM): what a single warp can pull through the multiplier on its own
+        int grid = sms, block = 128;
+        printf("--- 1 CTA x 128 threads per SM (one warp per scheduler)\n");
+        run("imad.wide.x 1 chain of 6", [&](int it) { k_wide_x<1><<<grid, block>>>((uint64_t*)buf, it, 3, 5); }, 6, iters, grid, block, sms, ghz);
+        run("imad.wide.x 2 chains of 6", [&](int it) { k_wide_x<2><<<grid, block>>>((uint64_t*)buf, it, 3, 5); }, 12, iters, grid, block, sms, ghz);
+        run("imad.wide.x 4 chains of 6", [&](int it) { k_wide_x<4><<<grid, block>>>((uint64_t*)buf, it, 3, 5); }, 24, iters, grid, block, sms, ghz);
+        run("imad.wide 8 indep chains", [&](int it) { k_imad_indep8<<<grid, block>>>((uint64_t*)buf, it, 3, 5); }, 8, iters, grid, block, sms, ghz);
+        run("fp_mul chain ILP1 (x300 MAC)", [&](int it) { k_fpmul<1><<<grid, block>>>((uint32_t*)buf, it / 16, 3); }, 300.0 / 16, iters, grid, block, sms, ghz);
+        run("fp_mul chain ILP2 (x300 MAC)", [&](int it) { k_fpmul<2><<<grid, block>>>((uint32_t*)buf, it / 16, 3); }, 600.0 / 16, iters, grid, block, sms, ghz);
+    }
     for (int wps = 1; wps <= 8; wps *= 2) {    // CTAs of 256 threads per SM: 8 / 16 / 32 / 64 warps per SM
         int grid = sms * wps, block = 256;
         printf("--- %d CTAs x 256 threads per SM\n", wps);
@@ -224,6 +293,12 @@ int main(int argc, char** argv) {
         run("dfma + 1 imad.wide (pairs)", [&](int it) { k_dfma_imad<1><<<grid, block>>>((double*)buf, it, 1.0000001, 0.5, 3, 5); }, 8, iters, grid, block, sms, ghz);
         run("dfma + 2 imad.wide (triples)", [&](int it) { k_dfma_imad<2><<<grid, block>>>((double*)buf, it, 1.0000001, 0.5, 3, 5); }, 8, iters, grid, block, sms, ghz);
         run("mul.wide dependent", [&](int it) { k_mulwide<<<grid, block>>>((uint64_t*)buf, it, 3, 5); }, 16, iters, grid, block, sms, ghz);
+        // round 2: the co-issue question with independent streams (ops counted: DFMA only, so "pairs/s" compares with the dfma line)
+        run("imad.wide 8 indep chains", [&](int it) { k_imad_indep8<<<grid, block>>>((uint64_t*)buf, it, 3, 5); }, 8, iters, grid, block, sms, ghz);
+        run("dfma || 1 imad.wide indep", [&](int it) { k_dfma_imad_indep<1><<<grid, block>>>((double*)buf, it, 1.0000001, 0.5, 3, 5); }, 8, iters, grid, block, sms, ghz);
+        run("dfma || 2 imad.wide indep", [&](int it) { k_dfma_imad_indep<2><<<grid, block>>>((double*)buf, it, 1.0000001, 0.5, 3, 5); }, 8, iters, grid, block, sms, ghz);
+        run("dfma || 2 iadd indep", [&](int it) { k_dfma_iadd<2><<<grid, block>>>((double*)buf, it, 1.0000001, 0.5, 3); }, 8, iters, grid, block, sms, ghz);
+        run("dfma || 4 iadd indep", [&](int it) { k_dfma_iadd<4><<<grid, block>>>((double*)buf, it, 1.0000001, 0.5, 3); }, 8, iters, grid, block, sms, ghz);
     }
     return 0;
 }
