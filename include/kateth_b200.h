@@ -107,6 +107,12 @@ int kb200_verify_proof(kb200_setup* s, const uint8_t proof48[48], const uint8_t 
 /* ---- private Setup::verify_proof_batch (src/kzg/setup.rs:115-161): one RLC check over n (proof, commitment, z, y) ---- */
 int kb200_verify_proof_batch(kb200_setup* s, const uint8_t* proofs48, const uint8_t* commitments48, const uint8_t* z32, const uint8_t* y32, size_t n,
                              int* ok, int32_t* status);
+/* ---- n independent Setup::verify_proof calls in one launch: PER-ITEM verdicts from a two-pairing check run on the device (one thread
+ *      per item: Miller loops against the line-precomputed [tau]_2 and G2, final exponentiation; bls::verify_pairings, src/bls.rs:572-598,
+ *      rearranged to e(-proof, [tau]_2) e(C - [y]G1 + [z]proof, G2) == 1).  ok[i] = 1 / 0; status[i] = that item's decoding error (proof,
+ *      commitment, point, eval order) with ok[i] = 0.  The return value is 0 unless the call itself failed. ---- */
+int kb200_verify_proof_many(kb200_setup* s, const uint8_t* proofs48, const uint8_t* commitments48, const uint8_t* z32, const uint8_t* y32, size_t n,
+                            int32_t* ok, int32_t* status);
 /* ---- Setup::verify_blob_proof (src/kzg/setup.rs:208-221) ---- */
 int kb200_verify_blob_proof(kb200_setup* s, const uint8_t* blob, const uint8_t commitment48[48], const uint8_t proof48[48], int* ok);
 /* ---- Setup::verify_blob_proof_batch (src/kzg/setup.rs:247-275); n = 0 -> *ok = 1 ---- */

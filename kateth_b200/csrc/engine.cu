@@ -14,6 +14,7 @@
 
 #include "../../include/kateth_b200.h"
 #include "verify.cuh"
+#include "pairing.cuh"
 #include "msm_ba_api.hpp"
 #include "host_bls.hpp"
 
@@ -57,6 +58,8 @@ struct kb200_setup {
     G1Affine* d_bases = nullptr;     // g1_lagrange_brp, affine Montgomery   (src/kzg/setup.rs:39)
     Fr* d_roots = nullptr;           // roots_of_unity_brp, Montgomery       (src/kzg/setup.rs:41)
     G1Affine* d_neg_g_pow = nullptr; // 2^(8w) * (-G1), w = 0..31 (verify.cuh, k_rlc_combine)
+    G1Affine* d_neg_g_bits = nullptr; // 2^k * (-G1), k = 0..254 (pairing.cuh, k_verify_proof_many)
+    PairConsts* d_pair = nullptr;    // Miller-loop lines of [tau]_2 and G2 + Frobenius constants, device copy (pairing.cuh)
     uint4* d_table = nullptr;        // fixed-base window table (msm.cuh)
     MsmTable tab{};
     uint64_t table_bytes = 0;
@@ -255,6 +258,21 @@ static int build_setup(kb200_setup* s, const uint8_t* g1, const uint8_t* g2, int
     LAUNCH(s, k_roots, KB_N / 256, 256, s->d_roots);
     CU(cudaMalloc(&s->d_neg_g_pow, 32 * sizeof(G1Affine)));
     LAUNCH(s, k_neg_g_table, 1, 32, s->d_neg_g_pow);
+    {   // device copy of what the per-item pairing check needs (pairing.cuh): the host module's prepared lines, bit for bit
+        static_assert(sizeof(PairLine) == sizeof(host::Line) && sizeof(Fp2) == sizeof(host::Fp2) && sizeof(Fp) == sizeof(host::Fp), "host and device field layouts");
+        if (s->tau_prep.inf || s->g2_prep.inf || s->tau_prep.n != s->g2_prep.n || s->tau_prep.n > 68) { snprintf(g_err, sizeof g_err, "setup: degenerate G2 points"); return KB200_E_ARG; }
+        std::vector<uint8_t> hb(sizeof(PairConsts), 0);
+        PairConsts* hp = reinterpret_cast<PairConsts*>(hb.data());
+        memcpy(hp->tau, s->tau_prep.lines, sizeof(host::Line) * s->tau_prep.n);
+        memcpy(hp->g2, s->g2_prep.lines, sizeof(host::Line) * s->g2_prep.n);
+        host::Fp2 f1[6]; host::Fp f2[6]; host::frobenius_consts(f1, f2);
+        memcpy(hp->frob1, f1, sizeof f1); memcpy(hp->frob2, f2, sizeof f2);
+        hp->nlines = s->tau_prep.n;
+        CU(cudaMalloc(&s->d_pair, sizeof(PairConsts)));
+        CU(cudaMemcpy(s->d_pair, hp, sizeof(PairConsts), cudaMemcpyHostToDevice));
+        CU(cudaMalloc(&s->d_neg_g_bits, 255 * sizeof(G1Affine)));
+        LAUNCH(s, k_neg_g_bits, 4, 64, s->d_neg_g_bits);
+    }
     // fixed-base window table: nwin = ceil(255 / c) windows; windows below the top hold the 2^(c-1) signed-digit magnitudes, the top
     // window is unsigned and holds (r >> c*(nwin-1)) + 1 magnitudes (scalars are canonical, so its digit never exceeds that)
     // GLV form (window_bits 16, or 100 + c for any c): the windows cover one 128-bit half of the scalar split k = k1 + k2*N
@@ -393,6 +411,8 @@ extern "C" void kb200_setup_free(kb200_setup* s) {
     if (s->d_bases) cudaFree(s->d_bases);
     if (s->d_roots) cudaFree(s->d_roots);
     if (s->d_neg_g_pow) cudaFree(s->d_neg_g_pow);
+    if (s->d_neg_g_bits) cudaFree(s->d_neg_g_bits);
+    if (s->d_pair) cudaFree(s->d_pair);
     if (s->d_table) cudaFree(s->d_table);
     if (s->d_counter) cudaFree(s->d_counter);
     if (s->aux_stream) cudaStreamDestroy(s->aux_stream);
@@ -1048,6 +1068,39 @@ extern "C" int kb200_verify_proof(kb200_setup* s, const uint8_t proof48[48], con
 extern "C" int kb200_verify_proof_batch(kb200_setup* s, const uint8_t* proofs48, const uint8_t* comm48, const uint8_t* z32, const uint8_t* y32, size_t n,
                                         int* ok, int32_t* status) {
     return verify_points(s, proofs48, comm48, z32, y32, n, 0, ok, status);
+}
+// n independent Setup::verify_proof calls (src/kzg/setup.rs:96-113) in one launch: per-item verdicts from the device pairing
+// (pairing.cuh).  ok[i] = 1 / 0; status[i] = the item's decoding error in kateth's order (proof, commitment, point, eval) or 0, and
+// ok[i] = 0 for such an item.  Returns 0 unless the call itself failed: an invalid item is that item's Err, not the batch's.
+extern "C" int kb200_verify_proof_many(kb200_setup* s, const uint8_t* proofs48, const uint8_t* comm48, const uint8_t* z32, const uint8_t* y32, size_t n,
+                                       int32_t* ok, int32_t* status) {
+    if (!s || (n && (!proofs48 || !comm48 || !z32 || !y32 || !ok))) return KB200_E_ARG;
+    LOCK(s);
+    CU(cudaSetDevice(s->device));
+    if (n == 0) return 0;
+    if (int rc = h2d(s, s->p48, proofs48, n * 48)) return rc;
+    if (int rc = h2d(s, s->c48, comm48, n * 48)) return rc;
+    if (int rc = h2d(s, s->zy32, z32, n * 32)) return rc;
+    if (int rc = h2d(s, s->out32, y32, n * 32)) return rc;
+    if (int rc = verify_reserve(s, n)) return rc;
+    if (int rc = s->prod.ensure(n * 4)) return rc;
+    if (int rc = s->status.ensure(n * 4)) return rc;
+    if (int rc = s->indom.ensure(n * 4)) return rc;
+    DBuf* cls[] = {&s->st_blob, &s->st_a, &s->st_b, &s->prod};
+    for (DBuf* b : cls) CU(cudaMemsetAsync(b->p, 0, n * 4, s->stream));
+    LAUNCH(s, k_g1_decompress, blocks(2 * n, 64), 64, s->p48.as<uint32_t>(), s->c48.as<uint32_t>(), (int)n, s->aff_p.as<G1Affine>(), s->aff_c.as<G1Affine>(),
+           s->st_blob.as<int32_t>(), s->st_a.as<int32_t>(), 0);
+    LAUNCH(s, k_scalar_check, blocks(n, 128), 128, s->zy32.as<uint32_t>(), (int)n, s->z.as<Fr>(), s->st_b.as<int32_t>());
+    LAUNCH(s, k_scalar_check, blocks(n, 128), 128, s->out32.as<uint32_t>(), (int)n, s->y.as<Fr>(), s->prod.as<int32_t>());
+    // merged status in kateth's order: proof, commitment, z, y
+    LAUNCH(s, k_merge_status, blocks(n, 256), 256, s->st_blob.as<int32_t>(), s->st_a.as<int32_t>(), s->st_b.as<int32_t>(), (int)n, s->status.as<int32_t>());
+    LAUNCH(s, k_merge_status, blocks(n, 256), 256, s->status.as<int32_t>(), s->prod.as<int32_t>(), (const int32_t*)nullptr, (int)n, s->status.as<int32_t>());
+    LAUNCH(s, k_verify_proof_many, blocks(n, PAIR_THREADS), PAIR_THREADS, s->aff_p.as<G1Affine>(), s->aff_c.as<G1Affine>(), s->z.as<Fr>(), s->y.as<Fr>(),
+           s->status.as<int32_t>(), s->d_neg_g_bits, s->d_pair, (int)n, s->indom.as<int32_t>());
+    if (int rc = d2h(s, ok, s->indom.p, n * 4)) return rc;
+    if (status) if (int rc = d2h(s, status, s->status.p, n * 4)) return rc;
+    CU(cudaGetLastError());
+    return 0;
 }
 extern "C" int kb200_verify_blob_proof(kb200_setup* s, const uint8_t* blob, const uint8_t comm48[48], const uint8_t proof48[48], int* ok) {
     if (!s || !ok || !blob || !comm48 || !proof48) return KB200_E_ARG;

@@ -232,6 +232,11 @@ static void init_once() {
 }
 static void init() { std::call_once(g_once, init_once); }
 
+void frobenius_consts(Fp2 frob1[6], Fp frob2[6]) {
+    init();
+    for (int k = 0; k < 6; k++) { frob1[k] = FROB1[k]; frob2[k] = FROB2[k]; }
+}
+
 int g2_decompress(G2A& out, const uint8_t in[96]) {
     init();
     uint8_t b0 = in[0];

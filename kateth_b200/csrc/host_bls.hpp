@@ -34,6 +34,9 @@ int g2_decompress(G2A& out, const uint8_t in[96]);
 void g2_generator(G2A& out);
 void g2_prepare(G2Prepared& out, const G2A& q);
 
+// Frobenius constants of the tower (gamma^k in Fp2, (gamma conj(gamma))^k in Fp, k = 0..5) for the device copy of the pairing
+void frobenius_consts(Fp2 frob1[6], Fp frob2[6]);
+
 // e(-a1, q1) * e(b1, q2) == 1 ?
 bool verify_pairings(const G1A& a1, const G2Prepared& q1, const G1A& b1, const G2Prepared& q2);
 

@@ -39,7 +39,7 @@ class _Info(C.Structure):
 SYMBOLS = [
     "kb200_setup_load_json", "kb200_setup_load_txt", "kb200_setup_load_raw", "kb200_setup_free", "kb200_set_stream", "kb200_last_error", "kb200_alloc_pinned", "kb200_free_pinned",
     "kb200_blob_to_commitment", "kb200_blob_to_commitment_device", "kb200_check_blobs", "kb200_compute_blob_proof", "kb200_compute_blob_proof_device",
-    "kb200_compute_proof", "kb200_compute_proof_device", "kb200_verify_proof", "kb200_verify_proof_batch", "kb200_verify_blob_proof",
+    "kb200_compute_proof", "kb200_compute_proof_device", "kb200_verify_proof", "kb200_verify_proof_batch", "kb200_verify_proof_many", "kb200_verify_blob_proof",
     "kb200_verify_blob_proof_batch", "kb200_verify_blob_proof_batch_device", "kb200_verify_blob_proof_batch_partial_device",
     "kb200_verify_blob_proof_batch_partial", "kb200_verify_batch_finish_device", "kb200_set_profiling", "kb200_set_msm_mode", "kb200_set_batch_challenge", "kb200_get_msm_profile", "kb200_last_pairing_operands", "kb200_get_info", "kb200_test_fp_mul", "kb200_test_fr_mul",
     "kb200_test_g1_decompress", "kb200_test_mac_peak", "kb200_test_host_pairing",
@@ -225,6 +225,12 @@ class Setup:
         ok = C.c_int(0)
         _check(lib().kb200_verify_proof_batch(self._h, proofs_concat, commitments_concat, z_concat, y_concat, C.c_size_t(n), C.byref(ok), None))
         return bool(ok.value)
+
+    def verify_proof_many(self, proofs_concat, commitments_concat, z_concat, y_concat, n):
+        """n independent verify_proof calls, verdicts from the device pairing: returns (ok list of bool, status list)."""
+        ok, st = (C.c_int32 * n)(), (C.c_int32 * n)()
+        _check(lib().kb200_verify_proof_many(self._h, proofs_concat, commitments_concat, z_concat, y_concat, C.c_size_t(n), ok, st))
+        return [bool(v) for v in ok], list(st)
 
     def verify_blob_proof_batch_concat(self, blobs_concat, commitments_concat, proofs_concat, n):
         ok = C.c_int(0)

@@ -659,3 +659,87 @@ def test_first_error_follows_blob_order(engine_setup):
         with pytest.raises(K.KzgError) as e:
             engine_setup.verify_blob_proof_batch(blobs, [c] * len(blobs), [p] * len(blobs))
         assert e.value.status == want
+
+
+# ---------------------------------------------------------------- per-item verdicts from the device pairing
+def test_device_pairing_matches_host_pairing_on_the_verify_vectors(engine_setup):
+    """kb200_verify_proof_many runs the two-pairing check on the GPU, one item per thread (pairing.cuh).  Its verdicts and statuses must
+    equal Setup::verify_proof's -- the host pairing, itself pinned by the 122 sha-checked verify_kzg_proof vectors -- on exactly
+    those cases: correct and incorrect proofs for 7 blobs x 6 points (3 of them in the domain), proofs at infinity for the zero and
+    the constant polynomial, invalid commitments / proofs / z / y."""
+    import kateth_b200 as K
+    from oracle import oracle as O
+    s = engine_setup
+    VB = RV.valid_blobs()
+    comm = [s.blob_to_commitment(b) for b in VB]
+    items = []          # (proof, commitment, z, y)
+    for bi, b in enumerate(VB):
+        for z in RV.FE_VALID:
+            pr, y = s.proof(b, z)
+            items.append((pr, comm[bi], z, y))
+            items.append((O.g1_add(pr, RV.G1), comm[bi], z, y))
+    for z in RV.FE_VALID:
+        _, y = s.proof(VB[2], z)
+        items.append((RV.INF, comm[2], z, y))                 # incorrect: proof at infinity
+        items.append((RV.INF, RV.INF, z, RV.fe(0)))           # correct: zero polynomial
+        items.append((RV.INF, comm[1], z, RV.fe(2)))          # correct: constant polynomial
+    pr1, y1 = s.proof(VB[2], RV.FE_VALID[1])
+    for g in RV.INVALID_G1[2:]:                               # full-length encodings (the shorter ones never reach the ABI)
+        items.append((pr1, g, RV.FE_VALID[1], y1)); items.append((g, comm[2], RV.FE_VALID[1], y1))
+    for f in RV.FE_INVALID[:4]:
+        items.append((pr1, comm[2], f, y1)); items.append((pr1, comm[2], RV.FE_VALID[1], f))
+    n = len(items)
+    ok, st = s.verify_proof_many(b"".join(i[0] for i in items), b"".join(i[1] for i in items), b"".join(i[2] for i in items), b"".join(i[3] for i in items), n)
+    seen = {True: 0, False: 0, "err": 0}
+    for k, (p, c, z, y) in enumerate(items):
+        try:
+            want = s.verify_proof(p, c, z, y)
+            assert st[k] == 0 and ok[k] is want, (k, ok[k], want)
+            seen[want] += 1
+        except K.KzgError as e:
+            assert st[k] == e.status and ok[k] is False, (k, st[k], e.status)
+            seen["err"] += 1
+    assert seen[True] >= 42 + 12 and seen[False] >= 42 + 6 and seen["err"] == 12
+
+
+def test_device_pairing_at_scale_with_planted_failures(engine_setup):
+    """4,000 (proof, commitment, z, y) tuples built from real proofs with failures planted at seeded positions (a wrong y, a proof of
+    another item, a swapped commitment): every per-item verdict must be the planted one, and the RLC batch check over the good items
+    (one host pairing) must agree."""
+    s = engine_setup
+    rng = random.Random(99)
+    nb, nz = 4, 25
+    blobs = [rand_blob(14000 + i) for i in range(nb)]
+    cat = b"".join(blobs)
+    comm, _ = s.blob_to_commitment_many(cat, nb)
+    base = []
+    for j in range(nz):
+        zs = b"".join(RV.fe(rng.randrange(R)) for _ in range(nb))
+        pr, ys, st = s.proof_many(cat, zs, nb)
+        assert st == [0] * nb
+        for i in range(nb):
+            base.append((pr[48 * i:48 * i + 48], comm[48 * i:48 * i + 48], zs[32 * i:32 * i + 32], ys[32 * i:32 * i + 32]))
+    n = 4000
+    items, want = [], []
+    for k in range(n):
+        p, c, z, y = base[rng.randrange(len(base))]
+        kind = rng.randrange(8)
+        if kind == 0:
+            y = RV.fe(int.from_bytes(y, "big") + 1); want.append(False)
+        elif kind == 1:
+            q = base[rng.randrange(len(base))]
+            want.append(q[0] == p and True); p = q[0]
+        elif kind == 2:
+            q = base[rng.randrange(len(base))]
+            want.append(q[1] == c); c = q[1]
+        else:
+            want.append(True)
+        items.append((p, c, z, y))
+    cols = [b"".join(i[j] for i in items) for j in range(4)]
+    ok, st = s.verify_proof_many(cols[0], cols[1], cols[2], cols[3], n)
+    assert st == [0] * n
+    assert ok == want, [k for k in range(n) if ok[k] != want[k]][:10]
+    good = [k for k in range(n) if want[k]]
+    gcols = [b"".join(items[k][j] for k in good) for j in range(4)]
+    assert s.verify_proof_batch(gcols[0], gcols[1], gcols[2], gcols[3], len(good)) is True
+    assert s.verify_proof_batch(cols[0], cols[1], cols[2], cols[3], n) is False
