@@ -133,6 +133,12 @@ int kb200_verify_blob_proof_batch_partial_device(kb200_setup* s, const void* d_b
 /* Same with the shard's inputs in host memory (any n_local; blobs are uploaded in chunks); the record is still written to device memory. */
 int kb200_verify_blob_proof_batch_partial(kb200_setup* s, const uint8_t* blobs, const uint8_t* commitments48, const uint8_t* proofs48, size_t n_local,
                                           size_t index_offset, size_t n_total, void* d_record, int32_t* status);
+/* The same exchange for batches of (proof, commitment, z, y) tuples (private Setup::verify_proof_batch, src/kzg/setup.rs:115-161): one record per
+ * shard, error classes proof / commitment / z / y. */
+int kb200_verify_proof_batch_partial_device(kb200_setup* s, const void* d_proofs48, const void* d_commitments48, const void* d_z32, const void* d_y32,
+                                            size_t n_local, size_t index_offset, size_t n_total, void* d_record, int32_t* d_status);
+int kb200_verify_proof_batch_partial(kb200_setup* s, const uint8_t* proofs48, const uint8_t* commitments48, const uint8_t* z32, const uint8_t* y32,
+                                     size_t n_local, size_t index_offset, size_t n_total, void* d_record, int32_t* status);
 /* d_records: n_records x KB200_RECORD_BYTES in device memory. */
 int kb200_verify_batch_finish_device(kb200_setup* s, const void* d_records, size_t n_records, int* ok);
 /* The two compressed G1 operands of the final pairing check of the last finish call (for diffing intermediate sums). */
@@ -169,6 +175,12 @@ int kb200_group_compute_proof(kb200_group* g, const uint8_t* blobs, const uint8_
  * order (the errors travel inside the records). */
 int kb200_group_verify_blob_proof_batch(kb200_group* g, const uint8_t* blobs, const uint8_t* commitments48, const uint8_t* proofs48, size_t n_local,
                                         size_t index_offset, size_t n_total, int* ok, int32_t* status);
+/* Setup::verify_proof_batch over the whole group (tuples instead of blobs), and n independent verify_proof calls with per-item verdicts from the
+ * device pairing, cut over this process's replicas. */
+int kb200_group_verify_proof_batch(kb200_group* g, const uint8_t* proofs48, const uint8_t* commitments48, const uint8_t* z32, const uint8_t* y32,
+                                   size_t n_local, size_t index_offset, size_t n_total, int* ok, int32_t* status);
+int kb200_group_verify_proof_many(kb200_group* g, const uint8_t* proofs48, const uint8_t* commitments48, const uint8_t* z32, const uint8_t* y32, size_t n,
+                                  int32_t* ok, int32_t* status);
 /* The same with the shards already in HBM: entry i of each array belongs to local replica i (device pointers on that replica's GPU),
  * n_per_replica[i] items each, laid out one after the other from index_offset on. */
 int kb200_group_verify_blob_proof_batch_device(kb200_group* g, const void* const* d_blobs, const void* const* d_commitments48,

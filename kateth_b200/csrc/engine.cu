@@ -666,8 +666,8 @@ static void host_sha256(const uint8_t* data, size_t len, uint8_t out[32]) {
 
 // first error of each class over the items of a call, in kateth's order (src/kzg/setup.rs:259-271)
 struct VErr {
-    int blob = 0, comm = 0, proof = 0;
-    int first() const { return blob ? blob : (comm ? comm : proof); }
+    int blob = 0, comm = 0, proof = 0, fourth = 0;     // point batches (verify_proof_batch): proof, commitment, z, y in these four
+    int first() const { return blob ? blob : (comm ? comm : (proof ? proof : fourth)); }
 };
 // workspace of a verification call over n items (must precede verify_prepare: growing a buffer drops its contents)
 static int verify_reserve(kb200_setup* s, size_t n) {
@@ -719,7 +719,7 @@ static int run_rlc(kb200_setup* s, size_t n, size_t index_offset, size_t n_total
 // the shard's errors travel with its sums (k_rlc_finish wrote zeros)
 static int set_record_err(kb200_setup* s, RlcRecord* d_record, const VErr& e) {
     if (!e.first()) return 0;
-    const int32_t h[4] = {e.blob, e.comm, e.proof, 0};
+    const int32_t h[4] = {e.blob, e.comm, e.proof, e.fourth};
     CU(cudaMemcpyAsync(d_record->err, h, sizeof h, cudaMemcpyHostToDevice, s->stream));
     CU(cudaStreamSynchronize(s->stream));
     return 0;
@@ -739,12 +739,12 @@ static void compress_plain(uint8_t out[48], const uint32_t* xy24, bool inf) {
 static int finish_records(kb200_setup* s, const RlcRecord* d_records, size_t nrec, int* ok) {
     if (int rc = s->combine.ensure(64 * 4)) return rc;
     LAUNCH(s, k_rlc_combine, 1, 32, d_records, (int)nrec, s->d_neg_g_pow, s->combine.as<uint32_t>());
-    uint32_t h[53];
+    uint32_t h[54];
     CU(cudaMemcpyAsync(h, s->combine.p, sizeof h, cudaMemcpyDeviceToHost, s->stream));
     CU(cudaStreamSynchronize(s->stream));
     CU(cudaGetLastError());
     *ok = 0;
-    for (int k = 50; k < 53; k++) if (h[k]) return (int)h[k];      // Err(..): no verdict (src/kzg/setup.rs:259-271)
+    for (int k = 50; k < 54; k++) if (h[k]) return (int)h[k];      // Err(..): no verdict (src/kzg/setup.rs:259-271)
     host::G1A a, b;
     a.inf = h[48] != 0; b.inf = h[49] != 0;
     host::fp_from_plain_u32(a.x, h); host::fp_from_plain_u32(a.y, h + 12);
@@ -1030,7 +1030,57 @@ extern "C" int kb200_verify_blob_proof_batch_partial(kb200_setup* s, const uint8
     CU(cudaGetLastError());
     return e.first();
 }
-// points given directly: mirrors the private Setup::verify_proof_batch (raw = 0) and verify_proof_inner (raw = 1)
+// ---- (proof, commitment, z, y) tuples given directly: the private Setup::verify_proof_batch (src/kzg/setup.rs:115-161) ----
+// decode the n tuples at the device pointers into s->aff_p / aff_c / z / y (workspace sized by verify_reserve); merged per-item
+// status in kateth's order (proof, commitment, point, eval: src/kzg/setup.rs:103-110) -> d_status; first error of each class -> e
+static int points_prepare(kb200_setup* s, const uint32_t* d_p48, const uint32_t* d_c48, const uint32_t* d_z32, const uint32_t* d_y32, size_t n, int32_t* d_status,
+                          VErr& e, std::vector<int32_t>* host_status = nullptr) {
+    if (int rc = s->prod.ensure(n * 4)) return rc;   // 4th status class (y)
+    DBuf* cls[] = {&s->st_blob, &s->st_a, &s->st_b, &s->prod};
+    for (DBuf* b : cls) CU(cudaMemsetAsync(b->p, 0, n * 4, s->stream));
+    LAUNCH(s, k_g1_decompress, blocks(2 * n, 64), 64, d_p48, d_c48, (int)n, s->aff_p.as<G1Affine>(), s->aff_c.as<G1Affine>(), s->st_blob.as<int32_t>(), s->st_a.as<int32_t>(), 0);
+    LAUNCH(s, k_scalar_check, blocks(n, 128), 128, d_z32, (int)n, s->z.as<Fr>(), s->st_b.as<int32_t>());
+    LAUNCH(s, k_scalar_check, blocks(n, 128), 128, d_y32, (int)n, s->y.as<Fr>(), s->prod.as<int32_t>());
+    LAUNCH(s, k_merge_status, blocks(n, 256), 256, s->st_blob.as<int32_t>(), s->st_a.as<int32_t>(), s->st_b.as<int32_t>(), (int)n, d_status);
+    LAUNCH(s, k_merge_status, blocks(n, 256), 256, d_status, s->prod.as<int32_t>(), (const int32_t*)nullptr, (int)n, d_status);
+    std::vector<int32_t> h[4];
+    for (int k = 0; k < 4; k++) if (int rc = fetch_status(s, cls[k]->as<int32_t>(), n, h[k])) return rc;
+    e.blob = first_nonzero(h[0]); e.comm = first_nonzero(h[1]); e.proof = first_nonzero(h[2]); e.fourth = first_nonzero(h[3]);
+    if (host_status) { host_status->resize(n); for (size_t i = 0; i < n; i++) (*host_status)[i] = h[0][i] ? h[0][i] : h[1][i] ? h[1][i] : h[2][i] ? h[2][i] : h[3][i]; }
+    return 0;
+}
+// one shard of a sharded point batch, inputs in HBM: record (with the shard's errors) -> d_record
+extern "C" int kb200_verify_proof_batch_partial_device(kb200_setup* s, const void* d_proofs48, const void* d_c48, const void* d_z32, const void* d_y32, size_t n,
+                                                       size_t index_offset, size_t n_total, void* d_record, int32_t* d_status) {
+    if (!s || !d_record || (n && (!d_proofs48 || !d_c48 || !d_z32 || !d_y32 || !d_status))) return KB200_E_ARG;
+    LOCK(s);
+    CU(cudaSetDevice(s->device));
+    VErr e;
+    if (int rc = verify_reserve(s, n)) return rc;
+    if (n) if (int rc = points_prepare(s, (const uint32_t*)d_proofs48, (const uint32_t*)d_c48, (const uint32_t*)d_z32, (const uint32_t*)d_y32, n, d_status, e)) return rc;
+    if (int rc = run_rlc(s, n, index_offset, n_total, 0, (RlcRecord*)d_record, n ? d_status : nullptr, (const uint32_t*)d_c48, (const uint32_t*)d_proofs48)) return rc;
+    if (int rc = set_record_err(s, (RlcRecord*)d_record, e)) return rc;
+    CU(cudaStreamSynchronize(s->stream));
+    CU(cudaGetLastError());
+    return e.first();
+}
+// the same with the shard's inputs in host memory
+extern "C" int kb200_verify_proof_batch_partial(kb200_setup* s, const uint8_t* proofs48, const uint8_t* comm48, const uint8_t* z32, const uint8_t* y32, size_t n,
+                                                size_t index_offset, size_t n_total, void* d_record, int32_t* status) {
+    if (!s || !d_record || (n && (!proofs48 || !comm48 || !z32 || !y32))) return KB200_E_ARG;
+    LOCK(s);
+    CU(cudaSetDevice(s->device));
+    if (int rc = h2d(s, s->p48, proofs48, n * 48)) return rc;
+    if (int rc = h2d(s, s->c48, comm48, n * 48)) return rc;
+    if (int rc = h2d(s, s->zy32, z32, n * 32)) return rc;
+    if (int rc = h2d(s, s->out32, y32, n * 32)) return rc;
+    if (int rc = s->status.ensure(n ? n * 4 : 16)) return rc;
+    int e = kb200_verify_proof_batch_partial_device(s, s->p48.p, s->c48.p, s->zy32.p, s->out32.p, n, index_offset, n_total, d_record, s->status.as<int32_t>());
+    if (e < 0) return e;
+    if (status && n) if (int rc = d2h(s, status, s->status.p, n * 4)) return rc;
+    return e;
+}
+// single call: mirrors Setup::verify_proof_batch (raw = 0) and verify_proof_inner (raw = 1)
 static int verify_points(kb200_setup* s, const uint8_t* proofs48, const uint8_t* comm48, const uint8_t* z32, const uint8_t* y32, size_t n, int raw, int* ok,
                          int32_t* status) {
     if (!s || !ok || (n && (!proofs48 || !comm48 || !z32 || !y32))) return KB200_E_ARG;
@@ -1042,22 +1092,12 @@ static int verify_points(kb200_setup* s, const uint8_t* proofs48, const uint8_t*
     if (int rc = h2d(s, s->zy32, z32, n * 32)) return rc;
     if (int rc = h2d(s, s->out32, y32, n * 32)) return rc;
     if (int rc = verify_reserve(s, n)) return rc;
-    DBuf* need[] = {&s->st_blob, &s->st_a, &s->st_b};
-    for (DBuf* b : need) CU(cudaMemsetAsync(b->p, 0, n * 4, s->stream));
-    if (int rc = s->prod.ensure(n * 4)) return rc;   // 4th status class (y)
-    CU(cudaMemsetAsync(s->prod.p, 0, n * 4, s->stream));
-    // kateth's order in verify_proof: proof, commitment, point, eval (src/kzg/setup.rs:103-110)
-    LAUNCH(s, k_g1_decompress, blocks(2 * n, 64), 64, s->p48.as<uint32_t>(), s->c48.as<uint32_t>(), (int)n, s->aff_p.as<G1Affine>(), s->aff_c.as<G1Affine>(),
-           s->st_blob.as<int32_t>(), s->st_a.as<int32_t>(), 0);
-    LAUNCH(s, k_scalar_check, blocks(n, 128), 128, s->zy32.as<uint32_t>(), (int)n, s->z.as<Fr>(), s->st_b.as<int32_t>());
-    LAUNCH(s, k_scalar_check, blocks(n, 128), 128, s->out32.as<uint32_t>(), (int)n, s->y.as<Fr>(), s->prod.as<int32_t>());
-    std::vector<int32_t> h[4];
-    if (int rc = fetch_status(s, s->st_blob.as<int32_t>(), n, h[0])) return rc;
-    if (int rc = fetch_status(s, s->st_a.as<int32_t>(), n, h[1])) return rc;
-    if (int rc = fetch_status(s, s->st_b.as<int32_t>(), n, h[2])) return rc;
-    if (int rc = fetch_status(s, s->prod.as<int32_t>(), n, h[3])) return rc;
-    if (status) for (size_t i = 0; i < n; i++) status[i] = h[0][i] ? h[0][i] : h[1][i] ? h[1][i] : h[2][i] ? h[2][i] : h[3][i];
-    for (int k = 0; k < 4; k++) if (int e = first_nonzero(h[k])) return e;
+    if (int rc = s->status.ensure(n * 4)) return rc;
+    VErr e;
+    std::vector<int32_t> hs;
+    if (int rc = points_prepare(s, s->p48.as<uint32_t>(), s->c48.as<uint32_t>(), s->zy32.as<uint32_t>(), s->out32.as<uint32_t>(), n, s->status.as<int32_t>(), e, &hs)) return rc;
+    if (status) memcpy(status, hs.data(), n * 4);
+    if (e.first()) return e.first();
     if (int rc = s->records.ensure(sizeof(RlcRecord))) return rc;
     if (int rc = run_rlc(s, n, 0, n, raw, s->records.as<RlcRecord>(), nullptr, s->c48.as<uint32_t>(), s->p48.as<uint32_t>())) return rc;
     return finish_records(s, s->records.as<RlcRecord>(), 1, ok);
@@ -1083,18 +1123,10 @@ extern "C" int kb200_verify_proof_many(kb200_setup* s, const uint8_t* proofs48, 
     if (int rc = h2d(s, s->zy32, z32, n * 32)) return rc;
     if (int rc = h2d(s, s->out32, y32, n * 32)) return rc;
     if (int rc = verify_reserve(s, n)) return rc;
-    if (int rc = s->prod.ensure(n * 4)) return rc;
     if (int rc = s->status.ensure(n * 4)) return rc;
     if (int rc = s->indom.ensure(n * 4)) return rc;
-    DBuf* cls[] = {&s->st_blob, &s->st_a, &s->st_b, &s->prod};
-    for (DBuf* b : cls) CU(cudaMemsetAsync(b->p, 0, n * 4, s->stream));
-    LAUNCH(s, k_g1_decompress, blocks(2 * n, 64), 64, s->p48.as<uint32_t>(), s->c48.as<uint32_t>(), (int)n, s->aff_p.as<G1Affine>(), s->aff_c.as<G1Affine>(),
-           s->st_blob.as<int32_t>(), s->st_a.as<int32_t>(), 0);
-    LAUNCH(s, k_scalar_check, blocks(n, 128), 128, s->zy32.as<uint32_t>(), (int)n, s->z.as<Fr>(), s->st_b.as<int32_t>());
-    LAUNCH(s, k_scalar_check, blocks(n, 128), 128, s->out32.as<uint32_t>(), (int)n, s->y.as<Fr>(), s->prod.as<int32_t>());
-    // merged status in kateth's order: proof, commitment, z, y
-    LAUNCH(s, k_merge_status, blocks(n, 256), 256, s->st_blob.as<int32_t>(), s->st_a.as<int32_t>(), s->st_b.as<int32_t>(), (int)n, s->status.as<int32_t>());
-    LAUNCH(s, k_merge_status, blocks(n, 256), 256, s->status.as<int32_t>(), s->prod.as<int32_t>(), (const int32_t*)nullptr, (int)n, s->status.as<int32_t>());
+    VErr e;
+    if (int rc = points_prepare(s, s->p48.as<uint32_t>(), s->c48.as<uint32_t>(), s->zy32.as<uint32_t>(), s->out32.as<uint32_t>(), n, s->status.as<int32_t>(), e)) return rc;
     LAUNCH(s, k_verify_proof_many, blocks(n, PAIR_THREADS), PAIR_THREADS, s->aff_p.as<G1Affine>(), s->aff_c.as<G1Affine>(), s->z.as<Fr>(), s->y.as<Fr>(),
            s->status.as<int32_t>(), s->d_neg_g_bits, s->d_pair, (int)n, s->indom.as<int32_t>());
     if (int rc = d2h(s, ok, s->indom.p, n * 4)) return rc;

@@ -268,6 +268,33 @@ extern "C" int kb200_group_verify_blob_proof_batch(kb200_group* g, const uint8_t
     if (rc < 0) return rc;
     return exchange_and_finish(g, ok);
 }
+// Setup::verify_proof_batch over the group: (proof, commitment, z, y) tuples, this process holds [index_offset, index_offset + n_local)
+extern "C" int kb200_group_verify_proof_batch(kb200_group* g, const uint8_t* proofs48, const uint8_t* commitments48, const uint8_t* z32, const uint8_t* y32,
+                                              size_t n_local, size_t index_offset, size_t n_total, int* ok, int32_t* status) {
+    if (!g || !ok || (n_local && (!proofs48 || !commitments48 || !z32 || !y32)) || index_offset + n_local > n_total) return KB200_E_ARG;
+    std::lock_guard<std::mutex> lk(g->mu);
+    if (n_total == 0) { *ok = 1; return 0; }
+    std::vector<size_t> lo; split(n_local, g->reps.size(), lo);
+    int rc = for_replicas(g, [&](size_t i) {
+        const size_t a = lo[i], m = lo[i + 1] - a;
+        int r = kb200_verify_proof_batch_partial(g->reps[i], proofs48 + a * 48, commitments48 + a * 48, z32 + a * 32, y32 + a * 32, m, index_offset + a, n_total,
+                                                 g->d_rec[i], status ? status + a : nullptr);
+        return r < 0 ? r : 0;
+    });
+    if (rc < 0) return rc;
+    return exchange_and_finish(g, ok);
+}
+// n independent verify_proof calls, per-item verdicts from the device pairing, cut over the local replicas (no communication)
+extern "C" int kb200_group_verify_proof_many(kb200_group* g, const uint8_t* proofs48, const uint8_t* commitments48, const uint8_t* z32, const uint8_t* y32, size_t n,
+                                             int32_t* ok, int32_t* status) {
+    if (!g || (n && (!proofs48 || !commitments48 || !z32 || !y32 || !ok))) return KB200_E_ARG;
+    std::lock_guard<std::mutex> lk(g->mu);
+    std::vector<size_t> lo; split(n, g->reps.size(), lo);
+    return for_replicas(g, [&](size_t i) {
+        const size_t a = lo[i], m = lo[i + 1] - a;
+        return m ? kb200_verify_proof_many(g->reps[i], proofs48 + a * 48, commitments48 + a * 48, z32 + a * 32, y32 + a * 32, m, ok + a, status ? status + a : nullptr) : 0;
+    });
+}
 // The same for shards that already sit in HBM: replica i's pointers at index i, its items follow those of replica i - 1.
 extern "C" int kb200_group_verify_blob_proof_batch_device(kb200_group* g, const void* const* d_blobs, const void* const* d_commitments48, const void* const* d_proofs48,
                                                           const size_t* n_per_replica, size_t index_offset, size_t n_total, int* ok, int32_t* const* d_status) {

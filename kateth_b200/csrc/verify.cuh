@@ -11,7 +11,8 @@
 //
 // Per GPU the result is one 336-byte record {A, B, C as affine Montgomery points, s, err[4]}:
 //   A = sum w_i pi_i,  B = sum w_i z_i pi_i,  C = sum w_i C_i,  s = sum w_i y_i        (w_i = rpowers[i])
-//   err = the shard's first error of each class (blob, commitment, proof; 0 = none): errors travel WITH the sums, so that every
+//   err = the shard's first error of each class (blob batches: blob, commitment, proof; point batches: proof, commitment, z, y;
+//   0 = none): errors travel WITH the sums, so that every
 //   rank that finishes a sharded batch returns the error kateth would (all blobs, then all commitments, then all proofs,
 //   src/kzg/setup.rs:259-271) instead of a verdict computed from unvalidated terms.  Items with a non-zero status contribute
 //   nothing to the sums.
@@ -23,7 +24,7 @@
 
 namespace kb200 {
 
-struct RlcRecord { G1Affine a, b, c; Fr s; int32_t err[4]; };   // 3*96 + 32 + 16 = 336 bytes (err[3] unused)
+struct RlcRecord { G1Affine a, b, c; Fr s; int32_t err[4]; };   // 3*96 + 32 + 16 = 336 bytes
 static_assert(sizeof(RlcRecord) == 336, "record layout");
 
 // Two arrays of n compressed points each (the second may be null) in ONE launch, one thread per point: out = affine
@@ -204,7 +205,7 @@ __global__ void k_neg_g_table(G1Affine* __restrict__ neg_g_pow) {
 }
 // Combine the records of all ranks into the two G1 pairing operands, as plain (non-Montgomery) affine coordinates:
 // out[0..11] = lhs.x, [12..23] = lhs.y, [24..35] = rhs.x, [36..47] = rhs.y, out[48] = lhs is infinity, out[49] = rhs is infinity,
-// out[50..52] = first blob / commitment / proof error over the records in rank order (0 = none).
+// out[50..53] = first error of each of the four classes over the records in rank order (0 = none).
 //   lhs = sum_g A_g        rhs = sum_g C_g + [sum_g s_g](-G1) + sum_g B_g
 // One warp: lane w multiplies the fixed point 2^(8w)(-G1) by byte w of s (8 double-and-add steps), the warp tree-sums the 32
 // terms, lane 0 adds the records, lanes 0 and 1 normalise one operand each.
@@ -229,10 +230,10 @@ __global__ void __launch_bounds__(32) k_rlc_combine(const RlcRecord* __restrict_
         __syncwarp();
     }
     if (lane == 2) {
-        int32_t e[3] = {0, 0, 0};
+        int32_t e[4] = {0, 0, 0, 0};
         for (int g = 0; g < nrec; g++)
-            for (int k = 0; k < 3; k++) if (e[k] == 0) e[k] = recs[g].err[k];
-        for (int k = 0; k < 3; k++) out[50 + k] = (uint32_t)e[k];
+            for (int k = 0; k < 4; k++) if (e[k] == 0) e[k] = recs[g].err[k];
+        for (int k = 0; k < 4; k++) out[50 + k] = (uint32_t)e[k];
     }
     if (lane == 0) {
         G1 A, B; g1_set_inf(A); g1_set_inf(B);

@@ -41,11 +41,11 @@ SYMBOLS = [
     "kb200_blob_to_commitment", "kb200_blob_to_commitment_device", "kb200_check_blobs", "kb200_compute_blob_proof", "kb200_compute_blob_proof_device",
     "kb200_compute_proof", "kb200_compute_proof_device", "kb200_verify_proof", "kb200_verify_proof_batch", "kb200_verify_proof_many", "kb200_verify_blob_proof",
     "kb200_verify_blob_proof_batch", "kb200_verify_blob_proof_batch_device", "kb200_verify_blob_proof_batch_partial_device",
-    "kb200_verify_blob_proof_batch_partial", "kb200_verify_batch_finish_device", "kb200_set_profiling", "kb200_set_msm_mode", "kb200_set_batch_challenge", "kb200_get_msm_profile", "kb200_last_pairing_operands", "kb200_get_info", "kb200_test_fp_mul", "kb200_test_fr_mul",
+    "kb200_verify_blob_proof_batch_partial", "kb200_verify_proof_batch_partial_device", "kb200_verify_proof_batch_partial", "kb200_verify_batch_finish_device", "kb200_set_profiling", "kb200_set_msm_mode", "kb200_set_batch_challenge", "kb200_get_msm_profile", "kb200_last_pairing_operands", "kb200_get_info", "kb200_test_fp_mul", "kb200_test_fr_mul",
     "kb200_test_g1_decompress", "kb200_test_mac_peak", "kb200_test_host_pairing",
     "kb200_group_create_json", "kb200_group_unique_id", "kb200_group_create_rank", "kb200_group_free", "kb200_group_info", "kb200_group_replica",
     "kb200_group_blob_to_commitment", "kb200_group_compute_blob_proof", "kb200_group_compute_proof", "kb200_group_verify_blob_proof_batch",
-    "kb200_group_verify_blob_proof_batch_device",
+    "kb200_group_verify_blob_proof_batch_device", "kb200_group_verify_proof_batch", "kb200_group_verify_proof_many",
 ]
 
 
@@ -262,6 +262,11 @@ class Setup:
         return lib().kb200_verify_blob_proof_batch_partial(self._h, conv(blobs), conv(comm48), conv(proofs48), C.c_size_t(n_local),
                                                            C.c_size_t(index_offset), C.c_size_t(n_total), _vp(d_record), None)
 
+    def verify_proof_partial_host(self, proofs, comm48, z32, y32, n_local, index_offset, n_total, d_record):
+        """One shard of a sharded batch of (proof, commitment, z, y) tuples (host bytes); the record goes to device memory."""
+        return lib().kb200_verify_proof_batch_partial(self._h, proofs, comm48, z32, y32, C.c_size_t(n_local), C.c_size_t(index_offset), C.c_size_t(n_total),
+                                                      _vp(d_record), None)
+
     def set_msm_mode(self, mode):
         """0 = automatic, 1 = XYZZ accumulation (k_msm), 2 = batch-affine summation (k_msm_ba); same bytes either way."""
         _check(lib().kb200_set_msm_mode(self._h, int(mode)))
@@ -381,6 +386,17 @@ class Group:
         _check(lib().kb200_group_verify_blob_proof_batch(self._g, self._p(blobs), self._p(commitments), self._p(proofs), C.c_size_t(n_local),
                                                          C.c_size_t(index_offset), C.c_size_t(n_local if n_total is None else n_total), C.byref(ok), None))
         return bool(ok.value)
+
+    def verify_proof_batch(self, proofs, commitments, zs, ys, n_local, index_offset=0, n_total=None):
+        ok = C.c_int(0)
+        _check(lib().kb200_group_verify_proof_batch(self._g, self._p(proofs), self._p(commitments), self._p(zs), self._p(ys), C.c_size_t(n_local),
+                                                    C.c_size_t(index_offset), C.c_size_t(n_local if n_total is None else n_total), C.byref(ok), None))
+        return bool(ok.value)
+
+    def verify_proof_many(self, proofs, commitments, zs, ys, n):
+        ok, st = (C.c_int32 * n)(), (C.c_int32 * n)()
+        _check(lib().kb200_group_verify_proof_many(self._g, self._p(proofs), self._p(commitments), self._p(zs), self._p(ys), C.c_size_t(n), ok, st))
+        return [bool(v) for v in ok], list(st)
 
     # raw-address forms for the bench (pinned host buffers / device pointers); return (rc, ok)
     def blob_to_commitment_host(self, blobs_ptr, n, out48_ptr):

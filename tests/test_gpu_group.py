@@ -31,6 +31,13 @@ def _check_group(g, oracle_setup, n):
     assert st == [0] * n
     for i in (0, n - 1):
         assert (pr[48 * i:48 * i + 48], ys[32 * i:32 * i + 32]) == oracle_setup.proof(base[idx[i]], zs[32 * i:32 * i + 32])
+    assert g.verify_proof_batch(pr, comm, zs, ys, n) is True
+    ok, st = g.verify_proof_many(pr, comm, zs, ys, n)
+    assert ok == [True] * n and st == [0] * n
+    bad_y = bytearray(ys); bad_y[32 * (n - 1):32 * n] = RV.fe(int.from_bytes(ys[32 * (n - 1):32 * n], "big") + 1)
+    assert g.verify_proof_batch(pr, comm, zs, bytes(bad_y), n) is False
+    ok, st = g.verify_proof_many(pr, comm, zs, bytes(bad_y), n)
+    assert ok == [True] * (n - 1) + [False] and st == [0] * n
     assert g.verify_blob_proof_batch(cat, comm, proofs, n) is True
     # the operands of the one pairing check equal the oracle's single-call sums, however the batch was sharded
     blobs = [base[k] for k in idx]

@@ -743,3 +743,41 @@ def test_device_pairing_at_scale_with_planted_failures(engine_setup):
     gcols = [b"".join(items[k][j] for k in good) for j in range(4)]
     assert s.verify_proof_batch(gcols[0], gcols[1], gcols[2], gcols[3], len(good)) is True
     assert s.verify_proof_batch(cols[0], cols[1], cols[2], cols[3], n) is False
+
+
+def test_sharded_point_batches_equal_single_call(engine_setup):
+    """Setup::verify_proof_batch over shards (config 5's sweep is cut over the GPUs): records of contiguous shards with global
+    index offsets, finished together, give the operands and the verdict of the single call; a shard's decoding error reaches the
+    finisher in kateth's class order (proof, commitment, z, y)."""
+    import ctypes as C
+    import torch
+    import kateth_b200 as K
+    s = engine_setup
+    n = 9
+    blobs = [rand_blob(15000 + i) for i in range(3)]
+    cat = b"".join(blobs[i % 3] for i in range(n))
+    comm, _ = s.blob_to_commitment_many(cat, n)
+    zs = b"".join(RV.fe(int.from_bytes(hashlib.sha256(b"sp%d" % i).digest(), "big")) for i in range(n))
+    pr, ys, st = s.proof_many(cat, zs, n)
+    assert st == [0] * n and s.verify_proof_batch(pr, comm, zs, ys, n) is True
+    single = s.last_pairing_operands()
+    RB = K.RECORD_BYTES
+    recs = torch.zeros(3 * RB, dtype=torch.uint8, device="cuda")
+
+    def run(pr_, comm_, zs_, ys_):
+        rcs = []
+        for g, (lo, hi) in enumerate([(0, 4), (4, 4), (4, 9)]):
+            rcs.append(s.verify_proof_partial_host(pr_[48 * lo:48 * hi], comm_[48 * lo:48 * hi], zs_[32 * lo:32 * hi], ys_[32 * lo:32 * hi], hi - lo, lo, n,
+                                                   recs.data_ptr() + g * RB))
+        ok = C.c_int(-1)
+        rc = K.lib().kb200_verify_batch_finish_device(s._h, C.c_void_p(recs.data_ptr()), 3, C.byref(ok))
+        return rcs, rc, ok.value
+
+    assert run(pr, comm, zs, ys) == ([0, 0, 0], 0, 1) and s.last_pairing_operands() == single
+    bad_y = bytearray(ys); bad_y[32 * 7:32 * 8] = RV.fe(int.from_bytes(ys[32 * 7:32 * 8], "big") + 1)
+    assert run(pr, comm, zs, bytes(bad_y)) == ([0, 0, 0], 0, 0)
+    # a non-canonical y in shard 0 and a proof off the curve in shard 2: the proof class comes first
+    ny = bytearray(ys); ny[0:32] = RV.be32(R)
+    bp = bytearray(pr); bp[48 * 8:48 * 9] = RV.INVALID_G1[3]
+    assert run(bytes(bp), comm, zs, bytes(ny)) == ([7, 0, 4], 4, 0)
+    assert run(pr, comm, zs, bytes(ny)) == ([7, 0, 0], 7, 0)
