@@ -28,6 +28,7 @@ R_MOD = 0x73eda753299d7d483339d80809a1d80553bda402fffe5bfeffffffff00000001
 # an Fp product = 300 MAC32.  The table MSM gathers 4096 * windows affine points of 96 bytes.
 MAC32_PER_MSM = 2.80e8
 METRIC = "blobs/sec commit+prove+batch-verify"
+METRIC_PAZ = "blobs/sec compute_kzg_proof+verify_kzg_proof (random points)"
 
 
 def synth_blobs(n, seed):
@@ -186,13 +187,37 @@ def run_engine(args):
             raise SystemExit("bench.py: %s returned status %d (%s)" % (what, rc, K.lib().kb200_last_error().decode()))
 
     stage_ev = []
+    paz = args.workload == "proof_at_z"
+    if paz:
+        # evaluation points: canonical scalars from the blob generator's stream 1; commitments are computed once, untimed
+        h_z = torch.from_numpy(synth_blobs((n + 4095) // 4096, 0x4b5a4700 + 5 + 1000 * rank)[: n * 32].copy()).pin_memory()
+        h_y = torch.empty(n * 32, dtype=torch.uint8).pin_memory()
+        d_z = h_z.to(dev)
+        d_y = torch.empty(n * 32, dtype=torch.uint8, device=dev)
+        check(s.blob_to_commitment_device(d_blobs.data_ptr(), n, d_comm.data_ptr(), d_status.data_ptr()), "blob_to_commitment")
+        h_comm.copy_(d_comm)
 
     def verdict(rc, ok, what, want=True):
         check(rc, what)
         if ok is not want:
             raise SystemExit("bench.py: %s returned %s, expected %s" % (what, ok, want))
 
+    def step_resident_paz(record):
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)] if record else None
+        if record: ev[0].record()
+        check(s.proof_device(d_blobs.data_ptr(), d_z.data_ptr(), n, d_proof.data_ptr(), d_y.data_ptr(), d_status.data_ptr()), "compute_proof")
+        if record: ev[1].record()
+        verdict(*g.verify_points_device([d_proof.data_ptr()], [d_comm.data_ptr()], [d_z.data_ptr()], [d_y.data_ptr()], [n], rank * n, world * n, [d_status.data_ptr()]),
+                "group_verify_proof_batch_device")
+        if record: ev[2].record(); stage_ev.append(ev)
+
+    def step_e2e_paz():
+        check(s.proof_host(h_blobs.data_ptr(), h_z.data_ptr(), n, h_proof.data_ptr(), h_y.data_ptr()), "compute_proof(host)")
+        verdict(*g.verify_points_host(h_proof.data_ptr(), h_comm.data_ptr(), h_z.data_ptr(), h_y.data_ptr(), n, rank * n, world * n), "group_verify_proof_batch(host)")
+
     def step_resident(record):
+        if paz:
+            return step_resident_paz(record)
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)] if record else None
         if record: ev[0].record()
         check(s.blob_to_commitment_device(d_blobs.data_ptr(), n, d_comm.data_ptr(), d_status.data_ptr()), "blob_to_commitment")
@@ -205,6 +230,8 @@ def run_engine(args):
         if record: ev[3].record(); stage_ev.append(ev)
 
     def step_e2e():
+        if paz:
+            return step_e2e_paz()
         check(s.blob_to_commitment_host(h_blobs.data_ptr(), n, h_comm.data_ptr()), "blob_to_commitment(host)")
         check(s.blob_proof_host(h_blobs.data_ptr(), h_comm.data_ptr(), n, h_proof.data_ptr()), "compute_blob_proof(host)")
         verdict(*g.verify_host(h_blobs.data_ptr(), h_comm.data_ptr(), h_proof.data_ptr(), n, rank * n, world * n), "group_verify_blob_proof_batch(host)")
@@ -245,19 +272,42 @@ def run_engine(args):
     # ---- end-to-end arm (host buffers)
     e2e_steps = max(1, min(args.steps, args.e2e_steps))
     ms_e2e = timed(step_e2e, e2e_steps, 1)
-    # config 4's second run: one corrupted proof (rank 0, item 1 gets item 0's proof) must flip the verdict of the
-    # whole sharded batch on every rank.  Untimed.
-    d_bad = d_proof.clone()
-    if rank == 0 and n > 1:
-        d_bad[48:96] = d_proof[0:48]
-    verdict(*g.verify_device([d_blobs.data_ptr()], [d_comm.data_ptr()], [d_bad.data_ptr()], [n], rank * n, world * n, [d_status.data_ptr()]),
-            "group_verify_blob_proof_batch_device(one corrupted proof)", want=False)
-    # parity guard inside the bench: the host-buffer path and the resident path must agree byte for byte
-    if not (torch.equal(h_comm, d_comm.cpu()) and torch.equal(h_proof, d_proof.cpu())):
-        raise SystemExit("bench.py: host-buffer and resident outputs differ")
+    per_item = None
+    if paz:
+        # one wrong y on rank 0 must flip the RLC verdict on every rank; then PER-ITEM verdicts from the device pairing (kb200_verify_proof_many),
+        # timed on their own: the wrong item, and only it, must come out false
+        d_bad = d_y.clone()
+        if rank == 0:
+            d_bad[31] ^= 1
+        verdict(*g.verify_points_device([d_proof.data_ptr()], [d_comm.data_ptr()], [d_z.data_ptr()], [d_bad.data_ptr()], [n], rank * n, world * n, [d_status.data_ptr()]),
+                "group_verify_proof_batch_device(one wrong y)", want=False)
+        h_bad = d_bad.cpu().numpy().tobytes()
+        m = min(n, args.per_item)
+        hp, hc, hz = bytes(h_proof.numpy()[: 48 * m]), bytes(h_comm.numpy()[: 48 * m]), bytes(h_z.numpy()[: 32 * m])
+        s.verify_proof_many(hp, hc, hz, h_bad[: 32 * m], min(m, 64))             # warm-up (first-launch local-memory allocation)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        ok, st = s.verify_proof_many(hp, hc, hz, h_bad[: 32 * m], m)
+        dt = time.perf_counter() - t0
+        if any(st) or ok != [not (rank == 0 and k == 0) for k in range(m)]:
+            raise SystemExit("bench.py: per-item verdicts of the device pairing are wrong")
+        per_item = {"items": m, "seconds": dt, "verdicts_per_s_per_gpu": m / dt, "api": "kb200_verify_proof_many (host buffers in, verdicts out)"}
+        if not (torch.equal(h_proof, d_proof.cpu()) and torch.equal(h_y, d_y.cpu())):
+            raise SystemExit("bench.py: host-buffer and resident outputs differ")
+    else:
+        # config 4's second run: one corrupted proof (rank 0, item 1 gets item 0's proof) must flip the verdict of the
+        # whole sharded batch on every rank.  Untimed.
+        d_bad = d_proof.clone()
+        if rank == 0 and n > 1:
+            d_bad[48:96] = d_proof[0:48]
+        verdict(*g.verify_device([d_blobs.data_ptr()], [d_comm.data_ptr()], [d_bad.data_ptr()], [n], rank * n, world * n, [d_status.data_ptr()]),
+                "group_verify_blob_proof_batch_device(one corrupted proof)", want=False)
+        # parity guard inside the bench: the host-buffer path and the resident path must agree byte for byte
+        if not (torch.equal(h_comm, d_comm.cpu()) and torch.equal(h_proof, d_proof.cpu())):
+            raise SystemExit("bench.py: host-buffer and resident outputs differ")
     ginfo = g.info()
     g.close()
-    return dict(rank=rank, world=world, n=n, s=s, ginfo=ginfo, ms_res=ms_res, ms_e2e=ms_e2e, e2e_steps=e2e_steps, clocks=clocks, launches=launches, prof=prof,
+    return dict(rank=rank, world=world, n=n, s=s, ginfo=ginfo, per_item=per_item, h_z=(h_z if paz else None), h_y=(h_y if paz else None), ms_res=ms_res, ms_e2e=ms_e2e, e2e_steps=e2e_steps, clocks=clocks, launches=launches, prof=prof,
                 stage_ev=stage_ev, info=info0, peak=(peak_wide, peak_fp), h_blobs=h_blobs, h_comm=h_comm, h_proof=h_proof)
 
 
@@ -294,13 +344,18 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="engine", choices=["engine", "reference"])
     ap.add_argument("--blobs", type=int, default=4096, help="blobs per GPU per step (BASELINE configs[2]: 4096)")
+    ap.add_argument("--workload", default="commit_prove_verify", choices=["commit_prove_verify", "proof_at_z"],
+                    help="proof_at_z = BASELINE configs[4]: compute_kzg_proof at random points + verify_kzg_proof (RLC batch; per-item device pairing reported beside it)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"], help="strong: --global-blobs are cut over the GPUs (north_star's scaling target)")
     ap.add_argument("--global-blobs", type=int, default=16384, help="batch size of --scaling strong (BASELINE configs[3]: 16384)")
     ap.add_argument("--window-bits", type=int, default=int(os.environ.get("KB200_WINDOW_BITS", "16")),
                     help="fixed-base table window width: 15 = 17 windows, 107 GiB table; 16 = GLV form, 2 x 8 windows on a 100 GiB table; library default 13 = 28.6 GiB")
     ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--per-item", type=int, default=8192, help="proof_at_z: items per GPU checked with the device pairing (per-item verdicts)")
     ap.add_argument("--ref-blobs", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-verify-max", type=int, default=128, help="largest batch of the CPU baseline's batch-verify sweep (benches/kzg.rs:14: 1..128)")
+    ap.add_argument("--no-cpu-breadth", action="store_true", help="skip the 1-core figure and the batch-verify sizes 1..128 of the CPU baseline")
     args = ap.parse_args()
     keep_stdout_clean()
     if args.impl == "reference":
@@ -322,8 +377,11 @@ def main():
     value = total / (ms_step * 1e-3)
     ms_e2e = r["ms_e2e"] / r["e2e_steps"]
     # per-stage device times (rank 0), averaged over the timed steps
-    st = [[ev[i].elapsed_time(ev[i + 1]) for i in range(3)] for ev in r["stage_ev"]]
-    stage = [sum(x[i] for x in st) / len(st) for i in range(3)]
+    paz = args.workload == "proof_at_z"
+    nst = 2 if paz else 3
+    st = [[ev[i].elapsed_time(ev[i + 1]) for i in range(nst)] for ev in r["stage_ev"]]
+    stage = [sum(x[i] for x in st) / len(st) for i in range(nst)]
+    stage_names = ["prove_at_z", "verify_rlc"] if paz else ["commit", "prove", "verify"]
     # roofline of the dominant kernel (k_msm): SURVEY 8(d) yardstick MAC32 per MSM x MSMs per launch / CUDA-event launch duration
     prof, info = r["prof"], r["info"]
     peak_chain, peak_fp = r["peak"]
@@ -378,6 +436,7 @@ def main():
                         "algorithmic": "table sectors gathered per MSM (4096 x %d windows%s); scratch traffic of the affine rounds not counted" % (W, ", twice" if ba else "")}}
     cpu_baseline = None
     if world == 1 and not args.no_cpu_baseline:
+        from oracle import oracle as O
         threads = host_threads()
         m = min(n, max(threads, 8))
         # the sample strides across the whole batch (first wave of the persistent MSM grid, later waves, the last item), and the
@@ -385,29 +444,69 @@ def main():
         idx = sorted(set(int(round(k * (n - 1) / max(1, m - 1))) for k in range(m)))
         hb = r["h_blobs"].numpy()
         sample = b"".join(bytes(hb[i * BLOB:(i + 1) * BLOB]) for i in idx)
-        a, b, comm, proofs = cpu_leg(sample, len(idx), threads)
         hc, hp = r["h_comm"].numpy(), r["h_proof"].numpy()
-        if comm != b"".join(bytes(hc[48 * i:48 * i + 48]) for i in idx) or proofs != b"".join(bytes(hp[48 * i:48 * i + 48]) for i in idx):
-            raise SystemExit("bench.py: engine output differs from the oracle on the CPU-baseline sample")
-        cpu_baseline = {"value": len(idx) / (a + b), "unit": "blobs/s", "cores": threads, "kind": "port",
-                        "sample": "%d blobs strided across the step's batch (items %s), %d threads (commit+prove %.2f s, batch-verify %.2f s); outputs equal the engine's"
-                                  % (len(idx), ",".join(str(i) for i in idx), threads, a, b),
-                        "caveat": "portable-C restatement of kateth's algorithm (oracle/), not blst's assembly with its thread-pooled Pippenger: kateth itself would be "
-                                  "faster per core; Rust and blst are absent from this image, so it is the only CPU baseline obtainable here"}
-    line = {"metric": METRIC, "value": value, "unit": "blobs/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
+        caveat = ("portable-C restatement of kateth's algorithm (oracle/), not blst's assembly with its thread-pooled Pippenger: kateth itself would be "
+                  "faster per core; Rust and blst are absent from this image, so it is the only CPU baseline obtainable here")
+        if paz:
+            o = cpu_leg.setup = getattr(cpu_leg, "setup", None) or O.Setup.load_json(SETUP_JSON)
+            hz, hy = r["h_z"].numpy(), r["h_y"].numpy()
+            t0 = time.perf_counter()
+            for k, i in enumerate(idx[:4]):           # Setup::proof + Setup::verify_proof per item, one core (oracle.proof has no threaded leg)
+                pr, y = o.proof(sample[k * BLOB:(k + 1) * BLOB], bytes(hz[32 * i:32 * i + 32]))
+                if pr != bytes(hp[48 * i:48 * i + 48]) or y != bytes(hy[32 * i:32 * i + 32]):
+                    raise SystemExit("bench.py: engine (proof, y) differs from the oracle on the CPU-baseline sample")
+                if not o.verify_proof(pr, bytes(hc[48 * i:48 * i + 48]), bytes(hz[32 * i:32 * i + 32]), y):
+                    raise SystemExit("bench.py: oracle rejects its own proof")
+            dt = time.perf_counter() - t0
+            cpu_baseline = {"value": min(4, len(idx)) / dt, "unit": "blobs/s", "cores": 1, "kind": "port",
+                            "sample": "%d blobs strided across the step's batch, Setup::proof + Setup::verify_proof (one pairing each) on one core, %.2f s; outputs equal the engine's" % (min(4, len(idx)), dt),
+                            "caveat": caveat}
+        else:
+            a, b, comm, proofs = cpu_leg(sample, len(idx), threads)
+            if comm != b"".join(bytes(hc[48 * i:48 * i + 48]) for i in idx) or proofs != b"".join(bytes(hp[48 * i:48 * i + 48]) for i in idx):
+                raise SystemExit("bench.py: engine output differs from the oracle on the CPU-baseline sample")
+            cpu_baseline = {"value": len(idx) / (a + b), "unit": "blobs/s", "cores": threads, "kind": "port",
+                            "sample": "%d blobs strided across the step's batch (items %s), %d threads (commit+prove %.2f s, batch-verify %.2f s); outputs equal the engine's"
+                                      % (len(idx), ",".join(str(i) for i in idx), threads, a, b),
+                            "caveat": caveat}
+            if not args.no_cpu_breadth:
+                # the 1-core figure, and kateth's own bench shape -- one verify_blob_kzg_proof_batch call per size 1..128
+                # (benches/kzg.rs:14,45-64; kateth's batch verification is single-threaded: naive lincombs + one pairing)
+                a1, b1, _, _ = cpu_leg(sample[: 2 * BLOB], 2, 1)
+                cpu_baseline["one_core"] = {"value": 2 / (a1 + b1), "unit": "blobs/s", "cores": 1, "sample": "2 blobs: commit+prove %.2f s, batch-verify %.2f s" % (a1, b1),
+                                            "commit_prove_blobs_per_s": 2 / a1, "batch_verify_blobs_per_s": 2 / b1}
+                o = cpu_leg.setup
+                sizes, cur = {}, 1
+                nb = min(n, args.cpu_verify_max)
+                vb, vc, vp = bytes(hb[: nb * BLOB]), bytes(hc[: 48 * nb]), bytes(hp[: 48 * nb])     # the engine's own commitments / proofs as inputs
+                while cur <= nb:
+                    t0 = time.perf_counter()
+                    ok = o.verify_many(vb[: cur * BLOB], vc[: 48 * cur], vp[: 48 * cur], cur, 1)
+                    sizes[str(cur)] = cur / (time.perf_counter() - t0)
+                    if not ok:
+                        raise SystemExit("bench.py: the oracle rejects the engine's proofs (batch of %d)" % cur)
+                    cur *= 2
+                cpu_baseline["batch_verify_by_size_one_core_blobs_per_s"] = sizes
+    e2e_bytes = ({"h2d_bytes_per_step": n * BLOB + n * 32 + n * (48 + 48 + 32 + 32), "d2h_bytes_per_step": n * (48 + 32) + 8 * n + 200} if paz else
+                 {"h2d_bytes_per_step": 3 * n * BLOB + 3 * n * 48, "d2h_bytes_per_step": 2 * n * 48 + 200 + 8 * n})
+    line = {"metric": METRIC_PAZ if paz else METRIC, "value": value, "unit": "blobs/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
             "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "u32 limbs (Fp 12x32, Fr 8x32 Montgomery, IMAD.WIDE)",
             "data": "synthetic canonical field elements, uniform in [0, r)",
-            "config": {"workload": "commit + compute_blob_kzg_proof + verify_blob_kzg_proof_batch over %d blobs per GPU (BASELINE configs[2] size; configs[3] sharding)" % n,
+            "config": {"workload": ("compute_kzg_proof at random points + verify_kzg_proof (RLC batch over all GPUs) over %d blobs per GPU (BASELINE configs[4])" % n) if paz else
+                                   ("commit + compute_blob_kzg_proof + verify_blob_kzg_proof_batch over %d blobs per GPU (BASELINE configs[2] size; configs[3] sharding)" % n),
                        "blobs_per_gpu": n, "global_blobs": total, "window_bits": info["window_bits"], "windows": info["windows"], "glv": bool(info.get("glv", 0)), "points_per_scalar": W, "msm_shape": "batch-affine (k_msm_ba)" if ba else "xyzz (k_msm)",
                        "table_gb": round(info["table_bytes"] / 2 ** 30, 2), "parallelism": "blob shards x%d, replicated tables, 1 ncclAllGather of %d B per rank inside the C ABI (kb200_group_*, NCCL %s)" % (world, K_RECORD, r["ginfo"]["nccl_version"] or "not needed"),
                        "l2": "inputs (%d MiB of blobs + multi-GB table) exceed the 126 MB L2; no flush needed" % (n * BLOB >> 20)},
-            "stages_ms": {"commit": stage[0], "prove": stage[1], "verify": stage[2]},
-            "stage_blobs_per_s_per_gpu": {"commit": n / stage[0] * 1e3, "prove": n / stage[1] * 1e3, "verify": n / stage[2] * 1e3},
-            "e2e": {"value": total / (ms_e2e * 1e-3), "unit": "blobs/s", "h2d_bytes_per_step": 3 * n * BLOB + 3 * n * 48, "d2h_bytes_per_step": 2 * n * 48 + 200 + 8 * n,
-                    "ms_per_step": ms_e2e, "steps": r["e2e_steps"], "api": "kb200_blob_to_commitment + kb200_compute_blob_proof + kb200_group_verify_blob_proof_batch (pinned host buffers)"},
+            "stages_ms": {k: v for k, v in zip(stage_names, stage)},
+            "stage_blobs_per_s_per_gpu": {k: n / v * 1e3 for k, v in zip(stage_names, stage)},
+            "e2e": {"value": total / (ms_e2e * 1e-3), "unit": "blobs/s", **e2e_bytes,
+                    "ms_per_step": ms_e2e, "steps": r["e2e_steps"],
+                    "api": "kb200_compute_proof + kb200_group_verify_proof_batch (pinned host buffers)" if paz else
+                           "kb200_blob_to_commitment + kb200_compute_blob_proof + kb200_group_verify_blob_proof_batch (pinned host buffers)"},
+            "per_item_verdicts": r["per_item"],
             "gpu_launches": int(r["launches"]), "roofline": roofline, "cpu_baseline": cpu_baseline, "clocks": r["clocks"],
             "setup_seconds": info["setup_seconds"],
-            "checks": {"valid_batch_verdict": True, "one_corrupted_proof_verdict": False, "host_buffer_outputs_equal_resident": True,
+            "checks": {"valid_batch_verdict": True, "one_corrupted_item_verdict": False, "host_buffer_outputs_equal_resident": True,
                        "oracle_outputs_equal_engine_on_cpu_sample": True if cpu_baseline is not None else None}}      # None: CPU leg not run (N > 1 or --no-cpu-baseline)
     emit(line)
     s.close()

@@ -181,6 +181,9 @@ int kb200_group_verify_proof_batch(kb200_group* g, const uint8_t* proofs48, cons
                                    size_t n_local, size_t index_offset, size_t n_total, int* ok, int32_t* status);
 int kb200_group_verify_proof_many(kb200_group* g, const uint8_t* proofs48, const uint8_t* commitments48, const uint8_t* z32, const uint8_t* y32, size_t n,
                                   int32_t* ok, int32_t* status);
+int kb200_group_verify_proof_batch_device(kb200_group* g, const void* const* d_proofs48, const void* const* d_commitments48, const void* const* d_z32,
+                                          const void* const* d_y32, const size_t* n_per_replica, size_t index_offset, size_t n_total, int* ok,
+                                          int32_t* const* d_status);
 /* The same with the shards already in HBM: entry i of each array belongs to local replica i (device pointers on that replica's GPU),
  * n_per_replica[i] items each, laid out one after the other from index_offset on. */
 int kb200_group_verify_blob_proof_batch_device(kb200_group* g, const void* const* d_blobs, const void* const* d_commitments48,

@@ -313,3 +313,23 @@ extern "C" int kb200_group_verify_blob_proof_batch_device(kb200_group* g, const 
     if (rc < 0) return rc;
     return exchange_and_finish(g, ok);
 }
+// Setup::verify_proof_batch over the group with the tuples already in HBM (the outputs of compute_proof_device): entry i of each array
+// belongs to local replica i.
+extern "C" int kb200_group_verify_proof_batch_device(kb200_group* g, const void* const* d_proofs48, const void* const* d_commitments48, const void* const* d_z32,
+                                                     const void* const* d_y32, const size_t* n_per_replica, size_t index_offset, size_t n_total, int* ok,
+                                                     int32_t* const* d_status) {
+    if (!g || !ok || !d_proofs48 || !d_commitments48 || !d_z32 || !d_y32 || !n_per_replica || !d_status) return KB200_E_ARG;
+    std::lock_guard<std::mutex> lk(g->mu);
+    if (n_total == 0) { *ok = 1; return 0; }
+    const size_t nl = g->reps.size();
+    std::vector<size_t> off(nl + 1, index_offset);
+    for (size_t i = 0; i < nl; i++) off[i + 1] = off[i] + n_per_replica[i];
+    if (off[nl] > n_total) return KB200_E_ARG;
+    int rc = for_replicas(g, [&](size_t i) {
+        int r = kb200_verify_proof_batch_partial_device(g->reps[i], d_proofs48[i], d_commitments48[i], d_z32[i], d_y32[i], n_per_replica[i], off[i], n_total, g->d_rec[i],
+                                                        d_status[i]);
+        return r < 0 ? r : 0;
+    });
+    if (rc < 0) return rc;
+    return exchange_and_finish(g, ok);
+}

@@ -45,7 +45,7 @@ SYMBOLS = [
     "kb200_test_g1_decompress", "kb200_test_mac_peak", "kb200_test_host_pairing",
     "kb200_group_create_json", "kb200_group_unique_id", "kb200_group_create_rank", "kb200_group_free", "kb200_group_info", "kb200_group_replica",
     "kb200_group_blob_to_commitment", "kb200_group_compute_blob_proof", "kb200_group_compute_proof", "kb200_group_verify_blob_proof_batch",
-    "kb200_group_verify_blob_proof_batch_device", "kb200_group_verify_proof_batch", "kb200_group_verify_proof_many",
+    "kb200_group_verify_blob_proof_batch_device", "kb200_group_verify_proof_batch", "kb200_group_verify_proof_many", "kb200_group_verify_proof_batch_device",
 ]
 
 
@@ -295,6 +295,9 @@ class Setup:
         _check(lib().kb200_verify_blob_proof_batch(self._h, _vp(blobs_ptr), _vp(comm48_ptr), _vp(proofs48_ptr), C.c_size_t(n), C.byref(ok), None))
         return bool(ok.value)
 
+    def proof_host(self, blobs_ptr, z32_ptr, n, out48_ptr, y32_ptr, status_ptr=0):
+        return lib().kb200_compute_proof(self._h, _vp(blobs_ptr), _vp(z32_ptr), C.c_size_t(n), _vp(out48_ptr), _vp(y32_ptr), _vp(status_ptr) if status_ptr else None)
+
     def verify_finish_device(self, d_records, n_records):
         ok = C.c_int(0)
         _check(lib().kb200_verify_batch_finish_device(self._h, _vp(d_records), C.c_size_t(n_records), C.byref(ok)))
@@ -409,6 +412,20 @@ class Group:
         ok = C.c_int(0)
         rc = lib().kb200_group_verify_blob_proof_batch(self._g, _vp(blobs_ptr), _vp(comm48_ptr), _vp(proofs48_ptr), C.c_size_t(n_local), C.c_size_t(index_offset),
                                                        C.c_size_t(n_total), C.byref(ok), None)
+        return rc, bool(ok.value)
+
+    def verify_points_host(self, proofs_ptr, comm48_ptr, z32_ptr, y32_ptr, n_local, index_offset, n_total):
+        ok = C.c_int(0)
+        rc = lib().kb200_group_verify_proof_batch(self._g, _vp(proofs_ptr), _vp(comm48_ptr), _vp(z32_ptr), _vp(y32_ptr), C.c_size_t(n_local), C.c_size_t(index_offset),
+                                                  C.c_size_t(n_total), C.byref(ok), None)
+        return rc, bool(ok.value)
+
+    def verify_points_device(self, d_proofs48, d_comm48, d_z32, d_y32, n_per_replica, index_offset, n_total, d_status):
+        k = len(n_per_replica)
+        vp = lambda xs: (C.c_void_p * k)(*[int(x) for x in xs])
+        ok = C.c_int(0)
+        rc = lib().kb200_group_verify_proof_batch_device(self._g, vp(d_proofs48), vp(d_comm48), vp(d_z32), vp(d_y32), (C.c_size_t * k)(*n_per_replica),
+                                                         C.c_size_t(index_offset), C.c_size_t(n_total), C.byref(ok), vp(d_status))
         return rc, bool(ok.value)
 
     def verify_device(self, d_blobs, d_comm48, d_proofs48, n_per_replica, index_offset, n_total, d_status):
