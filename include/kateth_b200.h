@@ -55,6 +55,7 @@ extern "C" {
 #define KB200_E_PARSE (-3)                 /* LoadSetupError::Serde */
 #define KB200_E_SETUP_G1_LEN (-10)         /* LoadSetupError::InvalidLenG1Lagrange */
 #define KB200_E_SETUP_G2_LEN (-11)         /* LoadSetupError::InvalidLenG2Monomial */
+#define KB200_E_SETUP_G1_MONOMIAL (-12)     /* the file's g1_monomial points do not match its g1_lagrange points (kb200_setup_check_g1_monomial) */
 #define KB200_E_ARG (-20)                  /* null pointer / bad argument */
 #define KB200_E_NCCL (-30)                 /* NCCL missing (dlopen libnccl.so.2) or a collective failed (kb200_last_error has the text) */
 
@@ -63,18 +64,30 @@ typedef struct kb200_setup kb200_setup;
 /* ---- Setup::load_json (/root/reference/src/kzg/setup.rs:46-82) ----
  * Parses {"g1_lagrange": [4096 x "0x" + 96 hex], "g2_monomial": [65 x "0x" + 192 hex]}, validates every point
  * (curve + subgroup; G1 on the GPU, G2 on the host), bit-reverses the Lagrange points, builds the roots-of-unity
- * table and the fixed-base window table on `device`.  window_bits: 0 = default (13 -> 28.6 GiB table), else 4..15
- * (15 -> 17 windows, 107 GiB).  The top window is unsigned; the others hold signed-digit magnitudes.
+ * table and the fixed-base window table on `device`.  window_bits: 0 = default = the widest table the device's FREE memory takes with
+ * room for the workspace of 4096-blob batches: 16 (the throughput configuration: GLV, 100 GiB) on an idle B200, else 13 (28.6 GiB), 9
+ * or 6; kb200_get_info reports the choice.  4..15 = that many bits (15 -> 17 windows, 107 GiB).  The top window is unsigned; the
+ * others hold signed-digit magnitudes.
+ * If the file also has a "g1_monomial" array (consensus-spec presets) it is cross-checked: see kb200_setup_check_g1_monomial.
  * 16, or 100 + c for c in 4..16, selects the GLV form: every scalar is split along the G1 endomorphism into two 128-bit
  * halves that share one table of ceil(128 / c) windows (16 -> 8 windows, 100 GiB, 16 gathered points per scalar instead of 17). */
 int kb200_setup_load_json(const char* path, int device, int window_bits, kb200_setup** out);
-/* Same from c-kzg-4844's trusted_setup.txt ("4096", "65", 4096 G1 Lagrange lines, 65 G2 monomial lines, optional G1 monomial
- * lines which are ignored); kateth itself only reads the JSON form. */
+/* Same from c-kzg-4844's trusted_setup.txt ("4096", "65", 4096 G1 Lagrange lines, 65 G2 monomial lines, optionally 4096 G1 monomial
+ * lines, which are cross-checked when all are there); kateth itself only reads the JSON form. */
 int kb200_setup_load_txt(const char* path, int device, int window_bits, kb200_setup** out);
 /* Same from decoded bytes: n_g1 x 48 bytes, n_g2 x 96 bytes. */
 int kb200_setup_load_raw(const uint8_t* g1_lagrange48, size_t n_g1, const uint8_t* g2_monomial96, size_t n_g2, int device, int window_bits,
                          kb200_setup** out);
 void kb200_setup_free(kb200_setup* s);
+/* g1_lagrange against the monomial basis of the same ceremony: for every k < n the evaluations of X^k over the domain (in blob order) must
+ * commit to g1_monomial[k] = [tau^k]G1.  One batch commit on the GPU; returns 0, or KB200_E_SETUP_G1_MONOMIAL with the first k in
+ * kb200_last_error.  Called by the loaders when the file carries the array. */
+int kb200_setup_check_g1_monomial(kb200_setup* s, const uint8_t* g1_monomial48, size_t n);
+/* On-disk cache of the window table, process-wide, off by default (NULL / "" switches it off; the KB200_TABLE_CACHE environment variable
+ * names a directory too).  File name = sha256(g1_lagrange | window form | layout version); a 64-bit checksum of the table, computed on the GPU
+ * after the upload, is checked against the header, and a missing / torn / edited file is rebuilt and rewritten.  Whether it pays depends on
+ * the storage: the GPU rebuilds the 100 GiB table in 4.8 s, which a file has to beat. */
+int kb200_set_table_cache(const char* dir);
 /* Stream for all later work on this handle (a cudaStream_t passed as void*; NULL = default stream). */
 int kb200_set_stream(kb200_setup* s, void* cuda_stream);
 const char* kb200_last_error(void);
@@ -208,6 +221,7 @@ typedef struct {
     int last_msm_batch_affine; /* 1 when the most recent MSM ran as k_msm_ba (batch-affine), 0 for k_msm (XYZZ) */
     int ba_grid;               /* persistent grid of k_msm_ba (resident CTAs) */
     int glv;                   /* 1: GLV table (windows = windows per 128-bit half, 2 * windows points per scalar) */
+    int table_from_cache;      /* 1: the table was read from the on-disk cache instead of being built */
 } kb200_info;
 int kb200_get_info(kb200_setup* s, kb200_info* info);
 /* CUDA-event timing of the dominant kernel (the fixed-base MSM) for roofline reporting: switch on, run, read the summed

@@ -66,6 +66,7 @@ struct kb200_setup {
     host::G2Prepared tau_prep, g2_prep;   // g2_monomial[1] and the G2 generator, Miller lines precomputed
     uint64_t launches = 0;
     double setup_seconds = 0;
+    bool table_from_cache = false;
     // workspace (per chunk)
     DBuf blobs, c48, p48, zy32, out48, out32, st_blob, st_a, st_b, status, z, y, prod, indom, q, partials, aff_c, aff_p, rlc_part, rlc_s, rmont,
         records, combine, dig, scr_pts, scr_pre;
@@ -217,14 +218,107 @@ static int json_hex_array(const std::string& doc, const char* key, std::vector<s
     }
 }
 
+static inline int blocks(size_t n, int t) { return (int)((n + t - 1) / t); }
 static int first_nonzero(const std::vector<int32_t>& v) { for (int32_t x : v) if (x) return x; return 0; }
 
+static void host_sha256(const uint8_t* data, size_t len, uint8_t out[32]);
+
+// ---- optional on-disk cache of the fixed-base window table ----
+// Off unless a directory is named (kb200_set_table_cache or KB200_TABLE_CACHE).  File: 64-byte header + the table bytes as they sit in HBM,
+// named after sha256(g1_lagrange bytes | c | glv | layout version); a 64-bit checksum of the table is computed ON THE GPU after the upload
+// and compared with the header, so a torn or edited file is rebuilt instead of trusted.
+static std::mutex g_cache_mu;
+static std::string g_cache_dir;
+static bool g_cache_env_read = false;
+static std::string cache_dir() {
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    if (!g_cache_env_read) { g_cache_env_read = true; if (g_cache_dir.empty()) if (const char* e = getenv("KB200_TABLE_CACHE")) g_cache_dir = e; }
+    return g_cache_dir;
+}
+extern "C" int kb200_set_table_cache(const char* dir) {
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    g_cache_env_read = true;
+    g_cache_dir = dir ? dir : "";
+    return 0;
+}
+struct CacheHeader { char magic[8]; uint32_t version, c, nwin, dlast, glv, pad; uint64_t rows, bytes, checksum; uint8_t reserved[8]; };
+static_assert(sizeof(CacheHeader) == 64, "cache header");
+__global__ void k_table_checksum(const uint64_t* __restrict__ data, size_t nwords, unsigned long long* __restrict__ out) {
+    unsigned long long acc = 0;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nwords; i += (size_t)gridDim.x * blockDim.x) acc += data[i] * (2 * (unsigned long long)i + 1);
+    for (int o = 16; o >= 1; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) atomicAdd(out, acc);
+}
 // scoped device allocation: freed on every exit path
 struct DevTmp {
     void* p = nullptr;
     ~DevTmp() { if (p) cudaFree(p); }
     template <class T> T* as() { return reinterpret_cast<T*>(p); }
 };
+
+static int table_checksum(kb200_setup* s, const void* d_table, size_t bytes, uint64_t* out) {
+    DevTmp acc; CU(cudaMalloc(&acc.p, 8));
+    CU(cudaMemsetAsync(acc.p, 0, 8, s->stream));
+    LAUNCH(s, k_table_checksum, s->sm_count * 8, 256, (const uint64_t*)d_table, bytes / 8, acc.as<unsigned long long>());
+    CU(cudaMemcpyAsync(out, acc.p, 8, cudaMemcpyDeviceToHost, s->stream));
+    CU(cudaStreamSynchronize(s->stream));
+    return 0;
+}
+struct PinnedPair {       // two staging buffers for chunked disk <-> HBM streaming
+    void* b[2] = {nullptr, nullptr}; cudaEvent_t ev[2] = {nullptr, nullptr};
+    static const size_t CH = (size_t)64 << 20;
+    int init() { for (int i = 0; i < 2; i++) { CU(cudaHostAlloc(&b[i], CH, cudaHostAllocDefault)); CU(cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming)); } return 0; }
+    ~PinnedPair() { for (int i = 0; i < 2; i++) { if (b[i]) cudaFreeHost(b[i]); if (ev[i]) cudaEventDestroy(ev[i]); } }
+};
+static std::string cache_path(const std::string& dir, const uint8_t* g1, int c, int glv) {
+    std::vector<uint8_t> key(KB_N * 48 + 12);
+    memcpy(key.data(), g1, KB_N * 48);
+    const uint32_t tail[3] = {(uint32_t)c, (uint32_t)glv, 1u /* layout version */};
+    memcpy(key.data() + KB_N * 48, tail, 12);
+    uint8_t dg[32]; host_sha256(key.data(), key.size(), dg);
+    char hex[65]; for (int i = 0; i < 32; i++) snprintf(hex + 2 * i, 3, "%02x", dg[i]);
+    return dir + "/kb200_table_" + hex + ".bin";
+}
+// 0: table loaded from the cache; 1: no usable file (caller builds); < 0: CUDA error
+static int cache_load(kb200_setup* s, const std::string& path, const CacheHeader& want, void* d_table) {
+    FILE* f = fopen(path.c_str(), "rb");
+    if (!f) return 1;
+    CacheHeader h;
+    bool ok = fread(&h, sizeof h, 1, f) == 1 && memcmp(h.magic, "KB200TBL", 8) == 0 && h.version == want.version && h.c == want.c && h.nwin == want.nwin &&
+              h.dlast == want.dlast && h.glv == want.glv && h.rows == want.rows && h.bytes == want.bytes;
+    PinnedPair pp;
+    if (ok && pp.init() != 0) { fclose(f); return KB200_E_CUDA; }
+    for (size_t off = 0, k = 0; ok && off < h.bytes; k++) {
+        const size_t m = (h.bytes - off < PinnedPair::CH) ? h.bytes - off : PinnedPair::CH;
+        const int i = (int)(k & 1);
+        if (k >= 2) cudaEventSynchronize(pp.ev[i]);
+        if (fread(pp.b[i], 1, m, f) != m) { ok = false; break; }
+        if (cudaMemcpyAsync((char*)d_table + off, pp.b[i], m, cudaMemcpyHostToDevice, s->stream) != cudaSuccess) { fclose(f); return KB200_E_CUDA; }
+        cudaEventRecord(pp.ev[i], s->stream);
+        off += m;
+    }
+    fclose(f);
+    cudaStreamSynchronize(s->stream);
+    if (!ok) return 1;
+    uint64_t sum = 0;
+    if (int rc = table_checksum(s, d_table, h.bytes, &sum)) return rc;
+    return sum == h.checksum ? 0 : 1;
+}
+static void cache_store(kb200_setup* s, const std::string& path, CacheHeader h, const void* d_table) {
+    if (table_checksum(s, d_table, h.bytes, &h.checksum) != 0) return;
+    const std::string tmp = path + ".tmp";
+    FILE* f = fopen(tmp.c_str(), "wb");
+    if (!f) return;
+    PinnedPair pp;
+    bool ok = pp.init() == 0 && fwrite(&h, sizeof h, 1, f) == 1;
+    for (size_t off = 0; ok && off < h.bytes;) {
+        const size_t m = (h.bytes - off < PinnedPair::CH) ? h.bytes - off : PinnedPair::CH;
+        ok = cudaMemcpy(pp.b[0], (const char*)d_table + off, m, cudaMemcpyDeviceToHost) == cudaSuccess && fwrite(pp.b[0], 1, m, f) == m;
+        off += m;
+    }
+    ok = (fclose(f) == 0) && ok;
+    if (ok) rename(tmp.c_str(), path.c_str()); else remove(tmp.c_str());
+}
 
 static int build_setup(kb200_setup* s, const uint8_t* g1, const uint8_t* g2, int window_bits) {
     auto t0 = std::chrono::steady_clock::now();
@@ -277,7 +371,15 @@ static int build_setup(kb200_setup* s, const uint8_t* g1, const uint8_t* g2, int
     // window is unsigned and holds (r >> c*(nwin-1)) + 1 magnitudes (scalars are canonical, so its digit never exceeds that)
     // GLV form (window_bits 16, or 100 + c for any c): the windows cover one 128-bit half of the scalar split k = k1 + k2*N
     // (glv.cuh), nwin = ceil(128 / c), and the top window holds (N >> c*(nwin-1)) + 1 magnitudes; both halves read the same table.
-    int c = window_bits ? window_bits : 13;
+    if (window_bits == 0) {
+        // default: the widest table the free HBM takes with room for the workspace of 4096-blob batches -- on an idle B200 the
+        // throughput configuration (16 = GLV, 8 shared windows, 100 GiB); a second handle on the same GPU, or a smaller part, steps down
+        size_t free_b = 0, total_b = 0;
+        CU(cudaMemGetInfo(&free_b, &total_b));
+        const double gib = (double)free_b / (double)((size_t)1 << 30);
+        window_bits = gib >= 124.0 ? 16 : (gib >= 45.0 ? 13 : (gib >= 10.0 ? 9 : 6));
+    }
+    int c = window_bits;
     int glv = 0;
     if (c == 16) glv = 1;
     else if (c >= 100) { glv = 1; c -= 100; }
@@ -304,12 +406,25 @@ static int build_setup(kb200_setup* s, const uint8_t* g1, const uint8_t* g2, int
     size_t scratch_rows = (size_t)group * win_rows;
     if ((size_t)dlast > scratch_rows) scratch_rows = dlast;
     CU(cudaMalloc(&s->d_table, bytes));
-    CU(cudaMalloc(&t_scratch.p, scratch_rows * row_bytes));
-    uint4* scratch = t_scratch.as<uint4>();
-    for (int j0 = 0; j0 < nwin;) {
-        int cnt = (j0 == nwin - 1) ? 1 : ((nwin - 1 - j0 < group) ? nwin - 1 - j0 : group);
-        LAUNCH(s, k_table_build, (KB_N * cnt + 31) / 32, 32, s->d_table, scratch, s->d_bases, c, nwin, dlast, j0, cnt);
-        j0 += cnt;
+    const std::string cdir = cache_dir();
+    CacheHeader hdr; memset(&hdr, 0, sizeof hdr);
+    memcpy(hdr.magic, "KB200TBL", 8); hdr.version = 1; hdr.c = (uint32_t)c; hdr.nwin = (uint32_t)nwin; hdr.dlast = (uint32_t)dlast; hdr.glv = (uint32_t)glv;
+    hdr.rows = rows; hdr.bytes = bytes;
+    const std::string cpath = cdir.empty() ? std::string() : cache_path(cdir, g1, c, glv);
+    int cached = 1;
+    if (!cpath.empty()) { cached = cache_load(s, cpath, hdr, s->d_table); if (cached < 0) return cached; }
+    s->table_from_cache = cached == 0;
+    if (cached != 0) {
+        CU(cudaMalloc(&t_scratch.p, scratch_rows * row_bytes));
+        uint4* scratch = t_scratch.as<uint4>();
+        for (int j0 = 0; j0 < nwin;) {
+            int cnt = (j0 == nwin - 1) ? 1 : ((nwin - 1 - j0 < group) ? nwin - 1 - j0 : group);
+            LAUNCH(s, k_table_build, (KB_N * cnt + 31) / 32, 32, s->d_table, scratch, s->d_bases, c, nwin, dlast, j0, cnt);
+            j0 += cnt;
+        }
+        CU(cudaStreamSynchronize(s->stream));
+        CU(cudaGetLastError());
+        if (!cpath.empty()) cache_store(s, cpath, hdr, s->d_table);
     }
     CU(cudaStreamSynchronize(s->stream));
     CU(cudaGetLastError());
@@ -347,6 +462,39 @@ extern "C" int kb200_setup_load_raw(const uint8_t* g1, size_t n_g1, const uint8_
     if (rc) { kb200_setup_free(s); return rc; }
     *out = s; return 0;
 }
+// Cross-check of a loaded setup against the monomial-basis points the same ceremony publishes (consensus-spec presets, c-kzg's
+// trusted_setup.txt): X^k evaluated over the domain, in blob order, must commit to [tau^k]G1 = g1_monomial[k].  All n <= 4096 powers are
+// checked with the engine's own batch MSM (one 4096-blob commit, ~80 ms): a Lagrange array that was permuted, truncated or mixed with
+// another ceremony's fails here instead of producing commitments nobody else can verify.
+extern "C" int kb200_setup_check_g1_monomial(kb200_setup* s, const uint8_t* g1_monomial48, size_t n) {
+    if (!s || !g1_monomial48 || n == 0 || n > KB_N) return KB200_E_ARG;
+    LOCK(s);
+    CU(cudaSetDevice(s->device));
+    if (int rc = s->blobs.ensure(n * (size_t)KB_BLOB_BYTES)) return rc;
+    if (int rc = s->out48.ensure(n * 48)) return rc;
+    if (int rc = s->status.ensure(n * 4)) return rc;
+    LAUNCH(s, k_vandermonde, blocks(n * KB_N, 256), 256, s->d_roots, 0, (int)n, s->blobs.as<uint32_t>());
+    int rc = kb200_blob_to_commitment_device(s, s->blobs.p, n, s->out48.p, s->status.as<int32_t>());
+    if (rc) return rc < 0 ? rc : KB200_E_SETUP_G1_MONOMIAL;
+    std::vector<uint8_t> got(n * 48);
+    CU(cudaMemcpy(got.data(), s->out48.p, n * 48, cudaMemcpyDeviceToHost));
+    for (size_t k = 0; k < n; k++)
+        if (memcmp(&got[48 * k], g1_monomial48 + 48 * k, 48) != 0) {
+            snprintf(g_err, sizeof g_err, "g1_monomial[%zu] is not the commitment of X^%zu under g1_lagrange: the two bases belong to different setups", k, k);
+            return KB200_E_SETUP_G1_MONOMIAL;
+        }
+    return 0;
+}
+static int check_monomial_if_present(kb200_setup** out, const std::vector<std::vector<uint8_t>>& g1m) {
+    if (g1m.empty()) return 0;
+    int rc = 0;
+    if (g1m.size() != KB_N) { snprintf(g_err, sizeof g_err, "g1_monomial has %zu points, expected %d", g1m.size(), KB_N); rc = KB200_E_SETUP_G1_MONOMIAL; }
+    std::vector<uint8_t> b(KB_N * 48);
+    for (size_t i = 0; !rc && i < g1m.size(); i++) { if (g1m[i].size() != 48) rc = KB200_E_G1_INVALID_ENCODING; else memcpy(&b[48 * i], g1m[i].data(), 48); }
+    if (!rc) rc = kb200_setup_check_g1_monomial(*out, b.data(), KB_N);
+    if (rc) { kb200_setup_free(*out); *out = nullptr; }
+    return rc;
+}
 extern "C" int kb200_setup_load_json(const char* path, int device, int window_bits, kb200_setup** out) {
     if (!path || !out) return KB200_E_ARG;
     FILE* f = fopen(path, "rb");
@@ -363,7 +511,11 @@ extern "C" int kb200_setup_load_json(const char* path, int device, int window_bi
     // kateth reads 48/96 bytes behind the pointer without a length check (src/bls.rs:514); the ABI checks.
     for (size_t i = 0; i < g1.size(); i++) { if (g1[i].size() != 48) return KB200_E_G1_INVALID_ENCODING; memcpy(&b1[48 * i], g1[i].data(), 48); }
     for (size_t i = 0; i < g2.size(); i++) { if (g2[i].size() != 96) return KB200_E_G1_INVALID_ENCODING; memcpy(&b2[96 * i], g2[i].data(), 96); }
-    return kb200_setup_load_raw(b1.data(), KB_N, b2.data(), 65, device, window_bits, out);
+    // files that also carry the monomial basis (consensus-spec presets) are cross-checked against it; kateth's own file has no such key
+    std::vector<std::vector<uint8_t>> g1m;
+    if (doc.find("\"g1_monomial\"") != std::string::npos) if (int rc = json_hex_array(doc, "g1_monomial", g1m)) return rc;
+    if (int rc = kb200_setup_load_raw(b1.data(), KB_N, b2.data(), 65, device, window_bits, out)) return rc;
+    return check_monomial_if_present(out, g1m);
 }
 // c-kzg-4844's trusted_setup.txt: "4096\n65\n", then 4096 lines of 96 hex digits (g1_lagrange), 65 lines of 192 hex digits
 // (g2_monomial) and, in newer files, 4096 more G1 lines (g1_monomial, ignored here).  Whitespace-separated tokens, no "0x".
@@ -403,7 +555,12 @@ extern "C" int kb200_setup_load_txt(const char* path, int device, int window_bit
     };
     for (size_t i = 0; i < n1; i++) if (int rc = unhex(tok[2 + i], &b1[48 * i], 48)) return rc;
     for (size_t i = 0; i < n2; i++) if (int rc = unhex(tok[2 + n1 + i], &b2[96 * i], 96)) return rc;
-    return kb200_setup_load_raw(b1.data(), KB_N, b2.data(), 65, device, window_bits, out);
+    // newer files append the 4096 monomial-basis G1 points: cross-check them (a partial tail is ignored, as before)
+    std::vector<std::vector<uint8_t>> g1m;
+    if (tok.size() >= 2 + n1 + n2 + KB_N)
+        for (size_t i = 0; i < (size_t)KB_N; i++) { std::vector<uint8_t> v(48); if (int rc = unhex(tok[2 + n1 + n2 + i], v.data(), 48)) return rc; g1m.push_back(std::move(v)); }
+    if (int rc = kb200_setup_load_raw(b1.data(), KB_N, b2.data(), 65, device, window_bits, out)) return rc;
+    return check_monomial_if_present(out, g1m);
 }
 extern "C" void kb200_setup_free(kb200_setup* s) {
     if (!s) return;
@@ -475,7 +632,7 @@ extern "C" int kb200_get_info(kb200_setup* s, kb200_info* info) {
     LOCK(s);
     info->window_bits = s->tab.c; info->windows = s->tab.nwin; info->table_bytes = s->table_bytes; info->kernel_launches = s->launches;
     info->device = s->device; info->sm_count = s->sm_count; info->setup_seconds = s->setup_seconds;
-    info->last_msm_batch_affine = s->last_ba; info->ba_grid = s->ba_grid; info->glv = s->tab.glv;
+    info->last_msm_batch_affine = s->last_ba; info->ba_grid = s->ba_grid; info->glv = s->tab.glv; info->table_from_cache = s->table_from_cache ? 1 : 0;
     return 0;
 }
 
@@ -487,7 +644,6 @@ static inline int pick_slices(kb200_setup* s, size_t n) {
     while (S < 32 && n * S < target) S <<= 1;
     return S;
 }
-static inline int blocks(size_t n, int t) { return (int)((n + t - 1) / t); }
 
 // MSM of n scalar vectors (FMT 0: blobs, FMT 1: LE limbs) -> n compressed points
 template <int FMT>

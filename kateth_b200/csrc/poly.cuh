@@ -31,6 +31,18 @@ __global__ void k_roots(Fr* roots_brp) {
     roots_brp[i] = r;
 }
 
+// ---- monomial cross-check of a setup: blob k0 + b holds the evaluations of X^(k0+b) over the domain in kateth's blob order, i.e. element
+// i = roots_brp[i]^(k0+b) = w^(brp(i) * (k0+b) mod 4096), as canonical big-endian bytes; its commitment must be [tau^(k0+b)]G1 ----
+__global__ void k_vandermonde(const Fr* __restrict__ roots_brp, int k0, int count, uint32_t* __restrict__ blobs) {
+    size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= (size_t)count * KB_N) return;
+    const uint32_t b = (uint32_t)(gid >> 12), i = (uint32_t)(gid & (KB_N - 1));
+    const uint32_t e = (brp12(i) * (uint32_t)(k0 + b)) & (KB_N - 1);
+    Fr w = roots_brp[brp12(e)], plain;
+    fr_from_mont(plain, w);
+    fr_store_be(blobs + gid * 8, plain);
+}
+
 // ---- Blob::from_slice: status[b] = 2 (InvalidFieldElement) if any element >= r ----
 __global__ void k_blob_check(const uint32_t* __restrict__ blobs, int n, int32_t* __restrict__ status) {
     size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;

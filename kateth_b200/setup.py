@@ -9,7 +9,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _STATUS_NAMES = {
     1: "Blob(InvalidLen)", 2: "Blob(InvalidFieldElement)", 3: "Bls(ECGroup(InvalidEncoding))", 4: "Bls(ECGroup(NotOnCurve))",
     5: "Bls(ECGroup(NotInGroup))", 6: "Bls(FiniteField(InvalidEncoding))", 7: "Bls(FiniteField(NotInFiniteField))",
-    -1: "CUDA", -2: "Io", -3: "Serde", -10: "InvalidLenG1Lagrange", -11: "InvalidLenG2Monomial", -20: "BadArgument",
+    -1: "CUDA", -2: "Io", -3: "Serde", -10: "InvalidLenG1Lagrange", -11: "InvalidLenG2Monomial", -12: "G1MonomialMismatch", -20: "BadArgument", -30: "Nccl",
 }
 
 
@@ -32,12 +32,12 @@ _lib = None
 class _Info(C.Structure):
     _fields_ = [("window_bits", C.c_int), ("windows", C.c_int), ("table_bytes", C.c_uint64), ("kernel_launches", C.c_uint64),
                 ("device", C.c_int), ("sm_count", C.c_int), ("setup_seconds", C.c_double),
-                ("last_msm_batch_affine", C.c_int), ("ba_grid", C.c_int), ("glv", C.c_int)]
+                ("last_msm_batch_affine", C.c_int), ("ba_grid", C.c_int), ("glv", C.c_int), ("table_from_cache", C.c_int)]
 
 
 # every symbol include/kateth_b200.h declares (tests/test_abi.py checks the header against this list and the .so)
 SYMBOLS = [
-    "kb200_setup_load_json", "kb200_setup_load_txt", "kb200_setup_load_raw", "kb200_setup_free", "kb200_set_stream", "kb200_last_error", "kb200_alloc_pinned", "kb200_free_pinned",
+    "kb200_setup_load_json", "kb200_setup_load_txt", "kb200_setup_load_raw", "kb200_setup_free", "kb200_setup_check_g1_monomial", "kb200_set_table_cache", "kb200_set_stream", "kb200_last_error", "kb200_alloc_pinned", "kb200_free_pinned",
     "kb200_blob_to_commitment", "kb200_blob_to_commitment_device", "kb200_check_blobs", "kb200_compute_blob_proof", "kb200_compute_blob_proof_device",
     "kb200_compute_proof", "kb200_compute_proof_device", "kb200_verify_proof", "kb200_verify_proof_batch", "kb200_verify_proof_many", "kb200_verify_blob_proof",
     "kb200_verify_blob_proof_batch", "kb200_verify_blob_proof_batch_device", "kb200_verify_blob_proof_batch_partial_device",
@@ -68,6 +68,11 @@ def lib():
         _lib.kb200_group_replica.restype = C.c_void_p
         _lib.kb200_group_replica.argtypes = [C.c_void_p, C.c_int]
     return _lib
+
+
+def set_table_cache(directory):
+    """Process-wide on-disk cache of the window table (None switches it off)."""
+    _check(lib().kb200_set_table_cache(os.fsencode(directory) if directory else None))
 
 
 def _vp(x):
@@ -109,6 +114,10 @@ class Setup:
             self.close()
         except Exception:
             pass
+
+    def check_g1_monomial(self, points48):
+        """Raises KzgError(-12) unless points48[k] == commit(X^k) for every k (kb200_setup_check_g1_monomial)."""
+        _check(lib().kb200_setup_check_g1_monomial(self._h, b"".join(points48), C.c_size_t(len(points48))))
 
     def set_stream(self, cuda_stream_ptr):
         _check(lib().kb200_set_stream(self._h, _vp(cuda_stream_ptr)))

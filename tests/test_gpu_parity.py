@@ -781,3 +781,83 @@ def test_sharded_point_batches_equal_single_call(engine_setup):
     bp = bytearray(pr); bp[48 * 8:48 * 9] = RV.INVALID_G1[3]
     assert run(bytes(bp), comm, zs, bytes(ny)) == ([7, 0, 4], 4, 0)
     assert run(pr, comm, zs, bytes(ny)) == ([7, 0, 0], 7, 0)
+
+
+# ---------------------------------------------------------------- loader extras
+def test_g1_monomial_cross_check(engine_setup, tmp_path):
+    """Files that also carry the monomial basis are cross-checked: X^k over the domain, in blob order, must commit to [tau^k]G1 for all
+    4096 k (one batch commit).  The mainnet ceremony's own points pass; two swapped points, or a monomial array from another setup, do not."""
+    import json
+    import kateth_b200 as K
+    mono = [bytes.fromhex(x[2:]) for x in json.load(open(os.path.join(ROOT, "tests/golden/g1_monomial_4096.json")))["g1_monomial"]]
+    assert mono[0] == RV.G1
+    engine_setup.check_g1_monomial(mono)
+    engine_setup.check_g1_monomial(mono[:5])
+    bad = list(mono); bad[7], bad[4000] = bad[4000], bad[7]
+    with pytest.raises(K.KzgError) as e:
+        engine_setup.check_g1_monomial(bad)
+    assert e.value.status == -12 and "g1_monomial[7]" in str(e.value)
+
+
+def test_loaders_cross_check_g1_monomial_and_default_window(tmp_path, gpu_free):
+    import json
+    import kateth_b200 as K
+    d = json.load(open(os.path.join(ROOT, "tests/golden/trusted_setup_4096.json")))
+    mono = json.load(open(os.path.join(ROOT, "tests/golden/g1_monomial_4096.json")))["g1_monomial"]
+    full = tmp_path / "presets.json"
+    full.write_text(json.dumps({"g1_monomial": mono, "g1_lagrange": d["g1_lagrange"], "g2_monomial": d["g2_monomial"]}))
+    s = K.Setup.load_json(str(full), window_bits=9)          # parses, builds, cross-checks
+    assert s.blob_to_commitment(RV.valid_blobs()[2]).hex() == GOLD_COMM[2]
+    s.close()
+    wrong = tmp_path / "wrong.json"
+    wrong.write_text(json.dumps({"g1_monomial": mono[1:] + mono[:1], "g1_lagrange": d["g1_lagrange"], "g2_monomial": d["g2_monomial"]}))
+    with pytest.raises(K.KzgError) as e:
+        K.Setup.load_json(str(wrong), window_bits=9)
+    assert e.value.status == -12
+    txt = tmp_path / "trusted_setup.txt"
+    txt.write_text("\n".join(["4096", "65"] + [x[2:] for x in d["g1_lagrange"]] + [x[2:] for x in d["g2_monomial"]] + [x[2:] for x in mono]) + "\n")
+    s = K.Setup.load_txt(str(txt), window_bits=9); s.close()
+    # window_bits 0: on an idle B200 the default is the throughput table (GLV, 16-bit windows, 100 GiB) -- what bench.py measures
+    s = K.Setup.load_json(os.path.join(ROOT, "tests/golden/trusted_setup_4096.json"))
+    try:
+        info = s.info()
+        assert (info["window_bits"], info["glv"]) == (16, 1) and info["table_bytes"] > 100 * 2 ** 30
+        # a second handle beside it no longer has 100 GiB free and steps down instead of failing
+        s2 = K.Setup.load_json(os.path.join(ROOT, "tests/golden/trusted_setup_4096.json"))
+        assert s2.info()["window_bits"] in (13, 9) and s2.blob_to_commitment(RV.valid_blobs()[2]).hex() == GOLD_COMM[2]
+        s2.close()
+    finally:
+        s.close()
+
+
+def test_table_cache_round_trip(tmp_path, gpu_free):
+    """On-disk cache of the window table: first load builds and writes, second load reads (checksum verified on the GPU), a flipped byte
+    in the file is noticed and the table is rebuilt and rewritten.  Same bytes out in every case."""
+    import kateth_b200 as K
+    path = os.path.join(ROOT, "tests/golden/trusted_setup_4096.json")
+    K.set_table_cache(str(tmp_path))
+    try:
+        outs = []
+        for expect_cached in (0, 1):
+            s = K.Setup.load_json(path, window_bits=106)          # GLV, 6-bit windows: a 0.26 GiB table
+            assert s.info()["table_from_cache"] == expect_cached
+            outs.append(s.blob_to_commitment(RV.valid_blobs()[2]))
+            s.close()
+        files = [f for f in os.listdir(tmp_path) if f.startswith("kb200_table_") and f.endswith(".bin")]
+        assert len(files) == 1 and outs[0] == outs[1] and outs[0].hex() == GOLD_COMM[2]
+        fn = os.path.join(tmp_path, files[0])
+        with open(fn, "r+b") as f:
+            f.seek(os.path.getsize(fn) // 2); b = f.read(1); f.seek(-1, 1); f.write(bytes([b[0] ^ 0x40]))
+        s = K.Setup.load_json(path, window_bits=106)
+        assert s.info()["table_from_cache"] == 0 and s.blob_to_commitment(RV.valid_blobs()[2]) == outs[0]
+        s.close()
+        s = K.Setup.load_json(path, window_bits=106)
+        assert s.info()["table_from_cache"] == 1
+        s.close()
+        # another window form is another file
+        s = K.Setup.load_json(path, window_bits=6)
+        assert s.info()["table_from_cache"] == 0
+        s.close()
+        assert len([f for f in os.listdir(tmp_path) if f.endswith(".bin")]) == 2
+    finally:
+        K.set_table_cache(None)
