@@ -96,6 +96,11 @@ const char* kb200_last_error(void);
 int kb200_alloc_pinned(size_t bytes, void** out);
 int kb200_free_pinned(void* p);
 
+/* ---- P1::decompress (src/bls.rs:505-531: curve check, then subgroup check) for n 48-byte encodings, no setup needed: status[i] = 0 or
+ *      KB200_E_G1_INVALID_ENCODING / _NOT_ON_CURVE / _NOT_IN_GROUP.  kateth's `Decompress` is an associated function of the point type
+ *      (Commitment::decompress(bytes)); the Rust wrapper's P1 calls this. ---- */
+int kb200_g1_validate(const uint8_t* in48, size_t n, int device, int32_t* status);
+
 /* ---- Setup::blob_to_commitment (src/kzg/setup.rs:167-171) + Compress::compress; n = 1 is the reference call ---- */
 int kb200_blob_to_commitment(kb200_setup* s, const uint8_t* blobs, size_t n, uint8_t* out48, int32_t* status);
 int kb200_blob_to_commitment_device(kb200_setup* s, const void* d_blobs, size_t n, void* d_out48, int32_t* d_status);

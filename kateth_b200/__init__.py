@@ -5,4 +5,4 @@ kateth's own (/root/reference/src/kzg/setup.rs:319-463): same method names, argu
 All computation happens in libkateth_b200.so (hand-written sm_100a CUDA + a host pairing); there is NO CPU
 fallback -- without the built library or without a GPU, loading a Setup raises.
 """
-from .setup import Setup, Group, KzgError, BatchVerifier, batch_error_of_records, shard_bounds, set_table_cache, lib, lib_path, BYTES_PER_BLOB, RECORD_BYTES, test_hooks  # noqa: F401
+from .setup import Setup, Group, KzgError, BatchVerifier, batch_error_of_records, shard_bounds, set_table_cache, g1_validate, lib, lib_path, BYTES_PER_BLOB, RECORD_BYTES, test_hooks  # noqa: F401

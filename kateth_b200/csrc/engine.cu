@@ -1340,6 +1340,22 @@ extern "C" int kb200_test_g1_decompress(kb200_setup* s, const uint8_t* in48, siz
     if (int rc = d2h(s, status, s->status.p, n * 4)) return rc;
     return d2h(s, re48, s->out48.p, n * 48);
 }
+// P1::decompress without a setup (src/bls.rs:505-531: blst_p1_uncompress + blst_p1_affine_in_g1): status[i] = 0 / 3 / 4 / 5 for n encodings.
+// kateth's Decompress is an associated function of the point type; a wrapper that offers it has no handle to pass.
+extern "C" int kb200_g1_validate(const uint8_t* in48, size_t n, int device, int32_t* status) {
+    if ((n && !in48) || !status) return KB200_E_ARG;
+    if (n == 0) return 0;
+    CU(cudaSetDevice(device));
+    if (int rc = init_consts()) return rc;
+    DevTmp tin, tpt, tst;
+    CU(cudaMalloc(&tin.p, n * 48)); CU(cudaMalloc(&tpt.p, n * sizeof(G1Affine))); CU(cudaMalloc(&tst.p, n * 4));
+    CU(cudaMemcpy(tin.p, in48, n * 48, cudaMemcpyHostToDevice));
+    CU(cudaMemset(tst.p, 0, n * 4));
+    k_g1_decompress<<<blocks(n, 64), 64>>>(tin.as<uint32_t>(), (const uint32_t*)nullptr, (int)n, tpt.as<G1Affine>(), (G1Affine*)nullptr, tst.as<int32_t>(), (int32_t*)nullptr, 0);
+    CU(cudaMemcpy(status, tst.p, n * 4, cudaMemcpyDeviceToHost));
+    CU(cudaGetLastError());
+    return 0;
+}
 extern "C" int kb200_test_mac_peak(int iters, double* tmacs_wide, double* tmacs_fpmul) {
     if (int rc = init_consts()) return rc;
     cudaDeviceProp prop; CU(cudaGetDeviceProperties(&prop, 0));

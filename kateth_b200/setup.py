@@ -37,7 +37,7 @@ class _Info(C.Structure):
 
 # every symbol include/kateth_b200.h declares (tests/test_abi.py checks the header against this list and the .so)
 SYMBOLS = [
-    "kb200_setup_load_json", "kb200_setup_load_txt", "kb200_setup_load_raw", "kb200_setup_free", "kb200_setup_check_g1_monomial", "kb200_set_table_cache", "kb200_set_stream", "kb200_last_error", "kb200_alloc_pinned", "kb200_free_pinned",
+    "kb200_setup_load_json", "kb200_setup_load_txt", "kb200_setup_load_raw", "kb200_setup_free", "kb200_setup_check_g1_monomial", "kb200_set_table_cache", "kb200_g1_validate", "kb200_set_stream", "kb200_last_error", "kb200_alloc_pinned", "kb200_free_pinned",
     "kb200_blob_to_commitment", "kb200_blob_to_commitment_device", "kb200_check_blobs", "kb200_compute_blob_proof", "kb200_compute_blob_proof_device",
     "kb200_compute_proof", "kb200_compute_proof_device", "kb200_verify_proof", "kb200_verify_proof_batch", "kb200_verify_proof_many", "kb200_verify_blob_proof",
     "kb200_verify_blob_proof_batch", "kb200_verify_blob_proof_batch_device", "kb200_verify_blob_proof_batch_partial_device",
@@ -68,6 +68,14 @@ def lib():
         _lib.kb200_group_replica.restype = C.c_void_p
         _lib.kb200_group_replica.argtypes = [C.c_void_p, C.c_int]
     return _lib
+
+
+def g1_validate(points48, device=0):
+    """P1::decompress for a list of 48-byte encodings, no Setup needed: list of statuses (0, 3, 4 or 5)."""
+    n = len(points48)
+    st = (C.c_int32 * n)()
+    _check(lib().kb200_g1_validate(b"".join(points48), C.c_size_t(n), int(device), st))
+    return list(st)
 
 
 def set_table_cache(directory):

@@ -201,6 +201,7 @@ def test_g1_decompress_classes(engine_setup):
     st, re = K.test_hooks.g1_decompress(engine_setup, pts)
     assert st == [0, 0, 5, 4, 3, 3, 3]
     assert re[0] == RV.G1 and re[1] == RV.INF
+    assert K.g1_validate(pts) == st          # the handle-free form behind the Rust wrapper's P1::decompress
 
 
 GLV_N = 0xac45a4010001a4020000000100000000      # x^2; r = N^2 - N + 1 (kateth_b200/csrc/glv.cuh)
