@@ -232,9 +232,12 @@ def run_engine(args):
     def step_e2e():
         if paz:
             return step_e2e_paz()
-        check(s.blob_to_commitment_host(h_blobs.data_ptr(), n, h_comm.data_ptr()), "blob_to_commitment(host)")
-        check(s.blob_proof_host(h_blobs.data_ptr(), h_comm.data_ptr(), n, h_proof.data_ptr()), "compute_blob_proof(host)")
-        verdict(*g.verify_host(h_blobs.data_ptr(), h_comm.data_ptr(), h_proof.data_ptr(), n, rank * n, world * n), "group_verify_blob_proof_batch(host)")
+        if args.e2e_api == "three_calls":
+            check(s.blob_to_commitment_host(h_blobs.data_ptr(), n, h_comm.data_ptr()), "blob_to_commitment(host)")
+            check(s.blob_proof_host(h_blobs.data_ptr(), h_comm.data_ptr(), n, h_proof.data_ptr()), "compute_blob_proof(host)")
+            verdict(*g.verify_host(h_blobs.data_ptr(), h_comm.data_ptr(), h_proof.data_ptr(), n, rank * n, world * n), "group_verify_blob_proof_batch(host)")
+        else:       # the same three pipelines over ONE upload of the blobs per step
+            verdict(*g.commit_prove_verify_host(h_blobs.data_ptr(), n, rank * n, world * n, h_comm.data_ptr(), h_proof.data_ptr()), "group_commit_prove_verify(host)")
 
     def barrier():
         if world > 1:
@@ -351,6 +354,8 @@ def main():
     ap.add_argument("--window-bits", type=int, default=int(os.environ.get("KB200_WINDOW_BITS", "16")),
                     help="fixed-base table window width: 15 = 17 windows, 107 GiB table; 16 = GLV form, 2 x 8 windows on a 100 GiB table; library default 13 = 28.6 GiB")
     ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--e2e-api", default="fused", choices=["fused", "three_calls"],
+                    help="end-to-end arm: kb200_group_commit_prove_verify (one upload of the blobs per step) or the three separate host-buffer calls (three uploads)")
     ap.add_argument("--per-item", type=int, default=8192, help="proof_at_z: items per GPU checked with the device pairing (per-item verdicts)")
     ap.add_argument("--ref-blobs", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -488,7 +493,8 @@ def main():
                     cur *= 2
                 cpu_baseline["batch_verify_by_size_one_core_blobs_per_s"] = sizes
     e2e_bytes = ({"h2d_bytes_per_step": n * BLOB + n * 32 + n * (48 + 48 + 32 + 32), "d2h_bytes_per_step": n * (48 + 32) + 8 * n + 200} if paz else
-                 {"h2d_bytes_per_step": 3 * n * BLOB + 3 * n * 48, "d2h_bytes_per_step": 2 * n * 48 + 200 + 8 * n})
+                 {"h2d_bytes_per_step": 3 * n * BLOB + 3 * n * 48, "d2h_bytes_per_step": 2 * n * 48 + 200 + 8 * n} if args.e2e_api == "three_calls" else
+                 {"h2d_bytes_per_step": n * BLOB, "d2h_bytes_per_step": 2 * n * 48 + 216 + 24 * n})
     line = {"metric": METRIC_PAZ if paz else METRIC, "value": value, "unit": "blobs/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
             "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "u32 limbs (Fp 12x32, Fr 8x32 Montgomery, IMAD.WIDE)",
             "data": "synthetic canonical field elements, uniform in [0, r)",
@@ -502,7 +508,8 @@ def main():
             "e2e": {"value": total / (ms_e2e * 1e-3), "unit": "blobs/s", **e2e_bytes,
                     "ms_per_step": ms_e2e, "steps": r["e2e_steps"],
                     "api": "kb200_compute_proof + kb200_group_verify_proof_batch (pinned host buffers)" if paz else
-                           "kb200_blob_to_commitment + kb200_compute_blob_proof + kb200_group_verify_blob_proof_batch (pinned host buffers)"},
+                           ("kb200_blob_to_commitment + kb200_compute_blob_proof + kb200_group_verify_blob_proof_batch (pinned host buffers, three uploads)" if args.e2e_api == "three_calls"
+                            else "kb200_group_commit_prove_verify: commit + blob proof + batch verification, each complete, over one upload of the blobs (pinned host buffers)")},
             "per_item_verdicts": r["per_item"],
             "gpu_launches": int(r["launches"]), "roofline": roofline, "cpu_baseline": cpu_baseline, "clocks": r["clocks"],
             "setup_seconds": info["setup_seconds"],

@@ -157,6 +157,12 @@ int kb200_verify_proof_batch_partial_device(kb200_setup* s, const void* d_proofs
                                             size_t n_local, size_t index_offset, size_t n_total, void* d_record, int32_t* d_status);
 int kb200_verify_proof_batch_partial(kb200_setup* s, const uint8_t* proofs48, const uint8_t* commitments48, const uint8_t* z32, const uint8_t* y32,
                                      size_t n_local, size_t index_offset, size_t n_total, void* d_record, int32_t* status);
+/* Commit + blob proof + the batch-verification shard of a FRESH batch over one upload of the blobs: the three pipelines of
+ * kb200_blob_to_commitment, kb200_compute_blob_proof and kb200_verify_blob_proof_batch_partial, each complete (the verification decodes the
+ * 48-byte outputs again and recomputes every challenge and evaluation), run on the bytes of a single host-to-device copy per chunk.
+ * Outputs: n commitments, n proofs (host), the shard's record (device). */
+int kb200_commit_prove_verify_partial(kb200_setup* s, const uint8_t* blobs, size_t n_local, size_t index_offset, size_t n_total, uint8_t* out_commitments48,
+                                      uint8_t* out_proofs48, void* d_record, int32_t* status);
 /* d_records: n_records x KB200_RECORD_BYTES in device memory. */
 int kb200_verify_batch_finish_device(kb200_setup* s, const void* d_records, size_t n_records, int* ok);
 /* The two compressed G1 operands of the final pairing check of the last finish call (for diffing intermediate sums). */
@@ -193,6 +199,9 @@ int kb200_group_compute_proof(kb200_group* g, const uint8_t* blobs, const uint8_
  * order (the errors travel inside the records). */
 int kb200_group_verify_blob_proof_batch(kb200_group* g, const uint8_t* blobs, const uint8_t* commitments48, const uint8_t* proofs48, size_t n_local,
                                         size_t index_offset, size_t n_total, int* ok, int32_t* status);
+/* kb200_commit_prove_verify_partial on every replica + the exchange + one pairing: commitments, proofs and the verdict of a fresh batch. */
+int kb200_group_commit_prove_verify(kb200_group* g, const uint8_t* blobs, size_t n_local, size_t index_offset, size_t n_total, uint8_t* out_commitments48,
+                                    uint8_t* out_proofs48, int* ok, int32_t* status);
 /* Setup::verify_proof_batch over the whole group (tuples instead of blobs), and n independent verify_proof calls with per-item verdicts from the
  * device pairing, cut over this process's replicas. */
 int kb200_group_verify_proof_batch(kb200_group* g, const uint8_t* proofs48, const uint8_t* commitments48, const uint8_t* z32, const uint8_t* y32,

@@ -69,7 +69,7 @@ struct kb200_setup {
     bool table_from_cache = false;
     // workspace (per chunk)
     DBuf blobs, c48, p48, zy32, out48, out32, st_blob, st_a, st_b, status, z, y, prod, indom, q, partials, aff_c, aff_p, rlc_part, rlc_s, rmont,
-        records, combine, dig, scr_pts, scr_pre;
+        records, combine, dig, scr_pts, scr_pre, st_tmp;
     // batch-affine MSM (msm_ba.cuh): 0 = automatic (batches that fill the GPU), 1 = always k_msm, 2 = always k_msm_ba
     int msm_mode = 0, ba_grid = 0, last_ba = 0;
     int challenge_mode = 0;          // batch-verification challenge: 0 = kateth's (parity with the reference), 1 = consensus-spec transcript
@@ -582,7 +582,7 @@ extern "C" void kb200_setup_free(kb200_setup* s) {
     for (int j = 0; j < 8; j++) if (s->ev_col[j]) cudaEventDestroy(s->ev_col[j]);
     s->sha_state.release();
     DBuf* bufs[] = {&s->blobs, &s->c48, &s->p48, &s->zy32, &s->out48, &s->out32, &s->st_blob, &s->st_a, &s->st_b, &s->status, &s->z, &s->y, &s->prod,
-                    &s->indom, &s->q, &s->partials, &s->aff_c, &s->aff_p, &s->rlc_part, &s->rlc_s, &s->rmont, &s->records, &s->combine, &s->dig, &s->scr_pts, &s->scr_pre, &s->transcript};
+                    &s->indom, &s->q, &s->partials, &s->aff_c, &s->aff_p, &s->rlc_part, &s->rlc_s, &s->rmont, &s->records, &s->combine, &s->dig, &s->scr_pts, &s->scr_pre, &s->transcript, &s->st_tmp};
     for (DBuf* b : bufs) b->release();
     for (cudaEvent_t e : s->prof_ev) cudaEventDestroy(e);
     delete s;
@@ -1186,6 +1186,63 @@ extern "C" int kb200_verify_blob_proof_batch_partial(kb200_setup* s, const uint8
     CU(cudaGetLastError());
     return e.first();
 }
+// ---- commit + blob proof + batch-verification shard over ONE upload of the blobs ----
+// The three calls a producer makes for a fresh batch (Setup::blob_to_commitment, ::blob_proof, then ::verify_blob_proof_batch on what
+// it is about to publish) each read the same 128 KiB per blob; done as three host-buffer calls the batch crosses PCIe three times.
+// Here a chunk is uploaded once (head wave first, so the first MSM starts under the rest of the copy) and the three device-side
+// pipelines run on the resident bytes -- each of them complete: the verification shard decodes the 48-byte commitments and proofs
+// again, recomputes every challenge and evaluation, exactly as kb200_verify_blob_proof_batch_partial would.
+extern "C" int kb200_commit_prove_verify_partial(kb200_setup* s, const uint8_t* blobs, size_t n, size_t index_offset, size_t n_total, uint8_t* out_comm48,
+                                                 uint8_t* out_proof48, void* d_record, int32_t* status) {
+    if (!s || !d_record || (n && (!blobs || !out_comm48 || !out_proof48))) return KB200_E_ARG;
+    LOCK(s);
+    CU(cudaSetDevice(s->device));
+    CopyGuard guard{s};
+    if (int rc = verify_reserve(s, n)) return rc;
+    if (int rc = s->status.ensure(n ? n * 4 : 16)) return rc;
+    if (int rc = s->c48.ensure(n ? n * 48 : 16)) return rc;
+    if (int rc = s->p48.ensure(n ? n * 48 : 16)) return rc;
+    if (int rc = s->combine.ensure(64 * 4)) return rc;
+    DBuf& st_tmp = s->st_tmp;                      // per-chunk statuses of commit / proof (the verification shard keeps the merged ones)
+    VErr e;
+    int first = 0;
+    if (int rc = st_tmp.ensure((n < CHUNK ? n : CHUNK) * 4 + 16)) return rc;
+    // Chunks are taken from the LAST to the first: the proof pipeline of a chunk works in items [0, m) of the shared workspace, the
+    // verification data of a chunk is kept at its own offset, so a later (lower) chunk never overwrites what an earlier one left;
+    // errors of lower chunks replace those of higher ones, which keeps kateth's first-in-item-order rule.
+    const size_t nch = (n + CHUNK - 1) / CHUNK;
+    for (size_t c = nch; c-- > 0;) {
+        const size_t off = c * CHUNK, m = (n - off < CHUNK) ? n - off : CHUNK, h = head_items(s, m);
+        if (int rc = h2d_split(s, s->blobs, blobs + off * KB_BLOB_BYTES, m * KB_BLOB_BYTES, h * KB_BLOB_BYTES)) return rc;
+        uint32_t* d_c = s->c48.as<uint32_t>() + off * 12;
+        uint32_t* d_p = s->p48.as<uint32_t>() + off * 12;
+        int chunk_first = 0;
+        for (size_t o = 0, k = h; o < m; o += k, k = m - o) {       // commit: head, then the rest
+            if (o) CU(cudaStreamWaitEvent(s->stream, s->ev_tail, 0));
+            int rc = kb200_blob_to_commitment_device(s, (char*)s->blobs.p + o * KB_BLOB_BYTES, k, d_c + o * 12, st_tmp.as<int32_t>() + o);
+            if (rc < 0) return rc;
+            if (rc && !chunk_first) chunk_first = rc;
+        }
+        if (int rc = d2h(s, out_comm48 + off * 48, d_c, m * 48)) return rc;
+        int rc = kb200_compute_blob_proof_device(s, s->blobs.p, d_c, m, d_p, st_tmp.as<int32_t>());
+        if (rc < 0) return rc;
+        if (rc && !chunk_first) chunk_first = rc;
+        if (int rc2 = d2h(s, out_proof48 + off * 48, d_p, m * 48)) return rc2;
+        VErr ec;
+        if (int rc2 = verify_prepare(s, s->blobs.as<uint32_t>(), d_c, d_p, m, off, s->status.as<int32_t>() + off, ec)) return rc2;
+        if (chunk_first) first = chunk_first;
+        if (ec.blob) e.blob = ec.blob;
+        if (ec.comm) e.comm = ec.comm;
+        if (ec.proof) e.proof = ec.proof;
+    }
+    if (status && n) if (int rc = d2h(s, status, s->status.p, n * 4)) return rc;
+    if (int rc = run_rlc(s, n, index_offset, n_total, 0, (RlcRecord*)d_record, n ? s->status.as<int32_t>() : nullptr, s->c48.as<uint32_t>(), s->p48.as<uint32_t>())) return rc;
+    if (int rc = set_record_err(s, (RlcRecord*)d_record, e)) return rc;
+    CU(cudaStreamSynchronize(s->stream));
+    CU(cudaGetLastError());
+    return first ? first : e.first();
+}
+
 // ---- (proof, commitment, z, y) tuples given directly: the private Setup::verify_proof_batch (src/kzg/setup.rs:115-161) ----
 // decode the n tuples at the device pointers into s->aff_p / aff_c / z / y (workspace sized by verify_reserve); merged per-item
 // status in kateth's order (proof, commitment, point, eval: src/kzg/setup.rs:103-110) -> d_status; first error of each class -> e

@@ -333,3 +333,20 @@ extern "C" int kb200_group_verify_proof_batch_device(kb200_group* g, const void*
     if (rc < 0) return rc;
     return exchange_and_finish(g, ok);
 }
+// commit + blob proof + batch verification of a fresh batch over ONE upload per shard (kb200_commit_prove_verify_partial), the verdict
+// over the whole group: what a producer of blobs runs before publishing them.
+extern "C" int kb200_group_commit_prove_verify(kb200_group* g, const uint8_t* blobs, size_t n_local, size_t index_offset, size_t n_total, uint8_t* out_comm48,
+                                               uint8_t* out_proof48, int* ok, int32_t* status) {
+    if (!g || !ok || (n_local && (!blobs || !out_comm48 || !out_proof48)) || index_offset + n_local > n_total) return KB200_E_ARG;
+    std::lock_guard<std::mutex> lk(g->mu);
+    if (n_total == 0) { *ok = 1; return 0; }
+    std::vector<size_t> lo; split(n_local, g->reps.size(), lo);
+    int rc = for_replicas(g, [&](size_t i) {
+        const size_t a = lo[i], m = lo[i + 1] - a;
+        int r = kb200_commit_prove_verify_partial(g->reps[i], blobs + a * KB200_BYTES_PER_BLOB, m, index_offset + a, n_total, out_comm48 + a * 48, out_proof48 + a * 48,
+                                                  g->d_rec[i], status ? status + a : nullptr);
+        return r < 0 ? r : 0;
+    });
+    if (rc < 0) return rc;
+    return exchange_and_finish(g, ok);
+}

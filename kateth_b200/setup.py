@@ -41,11 +41,11 @@ SYMBOLS = [
     "kb200_blob_to_commitment", "kb200_blob_to_commitment_device", "kb200_check_blobs", "kb200_compute_blob_proof", "kb200_compute_blob_proof_device",
     "kb200_compute_proof", "kb200_compute_proof_device", "kb200_verify_proof", "kb200_verify_proof_batch", "kb200_verify_proof_many", "kb200_verify_blob_proof",
     "kb200_verify_blob_proof_batch", "kb200_verify_blob_proof_batch_device", "kb200_verify_blob_proof_batch_partial_device",
-    "kb200_verify_blob_proof_batch_partial", "kb200_verify_proof_batch_partial_device", "kb200_verify_proof_batch_partial", "kb200_verify_batch_finish_device", "kb200_set_profiling", "kb200_set_msm_mode", "kb200_set_batch_challenge", "kb200_get_msm_profile", "kb200_last_pairing_operands", "kb200_get_info", "kb200_test_fp_mul", "kb200_test_fr_mul",
+    "kb200_verify_blob_proof_batch_partial", "kb200_commit_prove_verify_partial", "kb200_verify_proof_batch_partial_device", "kb200_verify_proof_batch_partial", "kb200_verify_batch_finish_device", "kb200_set_profiling", "kb200_set_msm_mode", "kb200_set_batch_challenge", "kb200_get_msm_profile", "kb200_last_pairing_operands", "kb200_get_info", "kb200_test_fp_mul", "kb200_test_fr_mul",
     "kb200_test_g1_decompress", "kb200_test_mac_peak", "kb200_test_host_pairing",
     "kb200_group_create_json", "kb200_group_unique_id", "kb200_group_create_rank", "kb200_group_free", "kb200_group_info", "kb200_group_replica",
     "kb200_group_blob_to_commitment", "kb200_group_compute_blob_proof", "kb200_group_compute_proof", "kb200_group_verify_blob_proof_batch",
-    "kb200_group_verify_blob_proof_batch_device", "kb200_group_verify_proof_batch", "kb200_group_verify_proof_many", "kb200_group_verify_proof_batch_device",
+    "kb200_group_verify_blob_proof_batch_device", "kb200_group_verify_proof_batch", "kb200_group_verify_proof_many", "kb200_group_verify_proof_batch_device", "kb200_group_commit_prove_verify",
 ]
 
 
@@ -429,6 +429,19 @@ class Group:
         ok = C.c_int(0)
         rc = lib().kb200_group_verify_blob_proof_batch(self._g, _vp(blobs_ptr), _vp(comm48_ptr), _vp(proofs48_ptr), C.c_size_t(n_local), C.c_size_t(index_offset),
                                                        C.c_size_t(n_total), C.byref(ok), None)
+        return rc, bool(ok.value)
+
+    def commit_prove_verify(self, blobs, n_local, index_offset=0, n_total=None):
+        """Fresh batch: (commitments, proofs, verdict) over one upload of the blobs per GPU."""
+        oc, op, ok = C.create_string_buffer(48 * n_local), C.create_string_buffer(48 * n_local), C.c_int(0)
+        _check(lib().kb200_group_commit_prove_verify(self._g, self._p(blobs), C.c_size_t(n_local), C.c_size_t(index_offset),
+                                                     C.c_size_t(n_local if n_total is None else n_total), oc, op, C.byref(ok), None))
+        return oc.raw, op.raw, bool(ok.value)
+
+    def commit_prove_verify_host(self, blobs_ptr, n_local, index_offset, n_total, out_comm48_ptr, out_proof48_ptr):
+        ok = C.c_int(0)
+        rc = lib().kb200_group_commit_prove_verify(self._g, _vp(blobs_ptr), C.c_size_t(n_local), C.c_size_t(index_offset), C.c_size_t(n_total), _vp(out_comm48_ptr),
+                                                   _vp(out_proof48_ptr), C.byref(ok), None)
         return rc, bool(ok.value)
 
     def verify_points_host(self, proofs_ptr, comm48_ptr, z32_ptr, y32_ptr, n_local, index_offset, n_total):

@@ -57,6 +57,12 @@ def _check_group(g, oracle_setup, n):
     c2, st2 = g.blob_to_commitment_many(bytes(badb), n)
     assert st2 == [0] * (n - 1) + [2] and c2[:48 * (n - 1)] == comm[:48 * (n - 1)]
     assert g.verify_blob_proof_batch(b"", b"", b"", 0) is True
+    # the three pipelines over one upload per GPU
+    oc, op, ok = g.commit_prove_verify(cat, n)
+    assert ok is True and oc == comm and op == proofs
+    with pytest.raises(K.KzgError) as e:
+        g.commit_prove_verify(bytes(badb), n)
+    assert e.value.status == 2
 
 
 def test_group_of_one(oracle_setup, gpu_free):

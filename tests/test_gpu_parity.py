@@ -608,6 +608,17 @@ def test_batches_larger_than_a_chunk(engine_setup, oracle_setup):
             assert e.value.status == 4
         finally:
             engine_setup.set_batch_challenge(0)
+    # commit + prove + verify over ONE upload (kb200_group_commit_prove_verify, a group of one around this handle): 4100 blobs are two
+    # chunks, taken last-first inside the library -- same bytes, same verdict, same operands; a bad blob in the second chunk is the error
+    g = K.Group.join(engine_setup, 0, 1, None)
+    try:
+        oc, op, ok = g.commit_prove_verify(gcat, n)
+        assert ok is True and oc == gcomm and op == proofs and engine_setup.last_pairing_operands() == single
+        with pytest.raises(K.KzgError) as e:
+            g.commit_prove_verify(bytes(bb), n)
+        assert e.value.status == 2
+    finally:
+        g.close()
     # the host-buffer shard call has no size limit either: one "rank" holding all 4100 blobs, finished from its record
     rec = torch.zeros(K.RECORD_BYTES, dtype=torch.uint8, device="cuda")
     assert engine_setup.verify_partial_host(gcat, gcomm, proofs, n, 0, n, rec.data_ptr()) == 0
