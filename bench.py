@@ -417,7 +417,7 @@ def main():
     gather_bytes = gather_per_msm * msms_per_launch
     traffic = None
     try:        # dram__bytes_read.sum + dram__bytes_write.sum of the committed ncu --set full capture, scaled to this launch
-        tr = json.load(open(os.path.join(ROOT, "profiles", "r01_k_msm_ba_traffic.json")))
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r02_k_msm_ba_traffic.json")))
         if ba:
             traffic = tr["dram_bytes_per_msm"] * msms_per_launch
     except Exception:
@@ -427,7 +427,7 @@ def main():
     # The SURVEY 8d yardstick (bucket Pippenger, 2.80e8 MAC32 per MSM) is reported beside it as an ALGORITHMIC ratio: the fixed-base
     # table does the yardstick's job with fewer multiplications (bought with HBM), which is not pipe utilisation.
     roofline = {"bound": "imad", "achieved": executed, "peak": peak_wide, "unit": "TMAC32/s", "frac": executed / peak_wide if peak_wide else None,
-                "traffic": traffic, "traffic_note": "DRAM bytes per launch: ncu capture of a 1184-MSM launch (profiles/r01_k_msm_ba_traffic.json) scaled by MSMs per launch; table gathers + per-CTA scratch of the affine rounds",
+                "traffic": traffic, "traffic_note": "DRAM bytes per launch: ncu capture of a 1184-MSM launch (profiles/r02_k_msm_ba_traffic.json) scaled by MSMs per launch; table gathers + per-CTA scratch of the affine rounds",
                 "kernel": kernel, "launch_ms": msm_ms, "msms_per_launch": msms_per_launch, "share_of_step": prof["ms"] / r["ms_res"],
                 "executed_mac32_per_msm": mac_per_msm,
                 "peak_source": "K0 measured in this run: max(IMAD.WIDE.U32.X carry chains %.2f, Fp-product chain %.2f) TMAC32/s; IMAD.WIDE issues at half the 32-bit IMAD rate on sm_100a; no integer peak in MEASURED_PEAKS.json" % (peak_chain, peak_fp),
