@@ -82,6 +82,8 @@ struct kb200_setup {
     cudaEvent_t ev_copy = nullptr, ev_head = nullptr, ev_tail = nullptr;
     cudaEvent_t ev_col[8] = {};             // column pieces of a hashed upload (h2d_blobs_hashed)
     DBuf sha_state;                         // chaining values between the pieces, [8][n] words
+    cudaEvent_t ev_eval = nullptr;          // end of the evaluation that batch verification runs on the auxiliary stream beside k_rlc
+    bool eval_pending = false;              // ... and whether the main stream still has to wait for it (run_rlc does)
     bool z_ready = false;                   // the challenges of the next proof / verify pass are already in s->z
     bool fork_recorded = false;             // ev_fork already marks the point of the main stream the point decompression may start from
     uint8_t last_lhs[48], last_rhs[48];
@@ -437,6 +439,7 @@ static int build_setup(kb200_setup* s, const uint8_t* g1, const uint8_t* g2, int
         CU(cudaStreamCreateWithFlags(&s->aux_stream, cudaStreamNonBlocking));
         CU(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&s->ev_join, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&s->ev_eval, cudaEventDisableTiming));
         CU(cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking));
         CU(cudaEventCreateWithFlags(&s->ev_copy, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&s->ev_head, cudaEventDisableTiming));
@@ -575,6 +578,7 @@ extern "C" void kb200_setup_free(kb200_setup* s) {
     if (s->aux_stream) cudaStreamDestroy(s->aux_stream);
     if (s->ev_fork) cudaEventDestroy(s->ev_fork);
     if (s->ev_join) cudaEventDestroy(s->ev_join);
+    if (s->ev_eval) cudaEventDestroy(s->ev_eval);
     if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
     if (s->ev_copy) cudaEventDestroy(s->ev_copy);
     if (s->ev_head) cudaEventDestroy(s->ev_head);
@@ -846,6 +850,7 @@ static int run_rlc(kb200_setup* s, size_t n, size_t index_offset, size_t n_total
     if (int rc = s->rmont.ensure(sizeof(Fr))) return rc;
     const int spec = (!raw && s->challenge_mode == 1) ? 1 : 0;
     if (spec) {
+        if (s->eval_pending) { CU(cudaStreamWaitEvent(s->stream, s->ev_eval, 0)); s->eval_pending = false; }      // the transcript hashes every y
         // r = hash_to_bls_field(domain | u64(4096) | u64(n) | sum(commitment | z | y | proof)): needs the whole batch in one place
         if (n != n_total || index_offset != 0 || !d_c48 || !d_p48) {
             snprintf(g_err, sizeof g_err, "consensus-spec batch challenge: the batch must be verified in one call (no shards)");
@@ -868,7 +873,9 @@ static int run_rlc(kb200_setup* s, size_t n, size_t index_offset, size_t n_total
         LAUNCH(s, k_batch_r, 1, 1, (uint32_t)n_total, s->rmont.as<Fr>());
     }
     if (nb) LAUNCH(s, k_rlc, dim3(nb, 3), RLC_THREADS, s->aff_p.as<G1Affine>(), s->aff_c.as<G1Affine>(), s->z.as<Fr>(), s->y.as<Fr>(), (int)n, (uint32_t)index_offset,
-                   s->rmont.as<Fr>(), raw, spec, d_status, s->rlc_part.as<G1>(), s->rlc_s.as<Fr>());
+                   s->rmont.as<Fr>(), raw, spec, d_status, s->rlc_part.as<G1>(), (Fr*)nullptr);
+    if (s->eval_pending) { CU(cudaStreamWaitEvent(s->stream, s->ev_eval, 0)); s->eval_pending = false; }      // y: see verify_prepare
+    if (nb) LAUNCH(s, k_rlc_s, nb, RLC_THREADS / 2, s->y.as<Fr>(), (int)n, (uint32_t)index_offset, s->rmont.as<Fr>(), raw, spec, d_status, s->rlc_s.as<Fr>());
     LAUNCH(s, k_rlc_finish, 3, RLC_FIN_THREADS, s->rlc_part.as<G1>(), s->rlc_s.as<Fr>(), nb, d_record);     // nb == 0: the identity record
     return 0;
 }
@@ -920,7 +927,7 @@ extern "C" int kb200_last_pairing_operands(kb200_setup* s, uint8_t lhs48[48], ui
 // decode + decompress + challenge + evaluate for items [off, off + m) of a call whose workspace verify_reserve sized: d_blobs,
 // d_c48, d_p48, d_status point at item `off`; fills aff_c, aff_p, z, y at `off`.  Accumulates the first error of each class in e.
 static int verify_prepare(kb200_setup* s, const uint32_t* d_blobs, const uint32_t* d_c48, const uint32_t* d_p48, size_t m, size_t off, int32_t* d_status,
-                          VErr& e) {
+                          VErr& e, bool last = true) {
     int32_t *st_blob = s->st_blob.as<int32_t>() + off, *st_a = s->st_a.as<int32_t>() + off, *st_b = s->st_b.as<int32_t>() + off;
     G1Affine *aff_c = s->aff_c.as<G1Affine>() + off, *aff_p = s->aff_p.as<G1Affine>() + off;
     Fr *z = s->z.as<Fr>() + off, *y = s->y.as<Fr>() + off;
@@ -943,7 +950,20 @@ static int verify_prepare(kb200_setup* s, const uint32_t* d_blobs, const uint32_
     s->z_ready = false;
     CU(cudaStreamWaitEvent(s->stream, s->ev_join, 0));
     LAUNCH(s, k_merge_status, blocks(m, 256), 256, st_blob, st_a, st_b, n, d_status);
-    if (int rc = run_eval<false>(s, d_blobs, m, d_status, z, y)) return rc;
+    // The evaluations y are only needed for the scalar s of the record; the scalar multiplications of k_rlc need z.  So the evaluation
+    // goes to the auxiliary stream and, for the last (or only) chunk of a call, run_rlc joins it after k_rlc; an earlier chunk joins at
+    // once, because the next chunk's upload reuses the blob buffer the evaluation reads.
+    {
+        CU(cudaEventRecord(s->ev_fork, s->stream));
+        CU(cudaStreamWaitEvent(s->aux_stream, s->ev_fork, 0));
+        cudaStream_t keep = s->stream; s->stream = s->aux_stream;
+        int rc = run_eval<false>(s, d_blobs, m, d_status, z, y);
+        s->stream = keep;
+        if (rc) return rc;
+        CU(cudaEventRecord(s->ev_eval, s->aux_stream));
+        s->eval_pending = true;
+        if (!last) { CU(cudaStreamWaitEvent(s->stream, s->ev_eval, 0)); s->eval_pending = false; }
+    }
     std::vector<int32_t> h0, h1, h2;
     if (int rc = fetch_status(s, st_blob, m, h0)) return rc;
     if (int rc = fetch_status(s, st_a, m, h1)) return rc;
@@ -1153,7 +1173,7 @@ static int verify_host_shard(kb200_setup* s, const uint8_t* blobs, const uint8_t
         const size_t m = (n - off < CHUNK) ? n - off : CHUNK;
         if (int rc = h2d_blobs_hashed(s, blobs + off * KB_BLOB_BYTES, m, s->c48.as<uint32_t>() + off * 12, s->z.as<Fr>() + off)) return rc;
         if (int rc = verify_prepare(s, s->blobs.as<uint32_t>(), s->c48.as<uint32_t>() + off * 12, s->p48.as<uint32_t>() + off * 12, m, off,
-                                    s->status.as<int32_t>() + off, e)) return rc;
+                                    s->status.as<int32_t>() + off, e, off + m >= n)) return rc;
     }
     if (status && n) if (int rc = d2h(s, status, s->status.p, n * 4)) return rc;
     if (int rc = run_rlc(s, n, index_offset, n_total, 0, d_record, n ? s->status.as<int32_t>() : nullptr, s->c48.as<uint32_t>(), s->p48.as<uint32_t>())) return rc;
@@ -1229,7 +1249,7 @@ extern "C" int kb200_commit_prove_verify_partial(kb200_setup* s, const uint8_t* 
         if (rc && !chunk_first) chunk_first = rc;
         if (int rc2 = d2h(s, out_proof48 + off * 48, d_p, m * 48)) return rc2;
         VErr ec;
-        if (int rc2 = verify_prepare(s, s->blobs.as<uint32_t>(), d_c, d_p, m, off, s->status.as<int32_t>() + off, ec)) return rc2;
+        if (int rc2 = verify_prepare(s, s->blobs.as<uint32_t>(), d_c, d_p, m, off, s->status.as<int32_t>() + off, ec, c == 0)) return rc2;
         if (chunk_first) first = chunk_first;
         if (ec.blob) e.blob = ec.blob;
         if (ec.comm) e.comm = ec.comm;
@@ -1358,7 +1378,10 @@ extern "C" int kb200_verify_blob_proof(kb200_setup* s, const uint8_t* blob, cons
     if (int rc = verify_reserve(s, 1)) return rc;
     VErr e;
     if (int rc = verify_prepare(s, s->blobs.as<uint32_t>(), s->c48.as<uint32_t>(), s->p48.as<uint32_t>(), 1, 0, s->status.as<int32_t>(), e)) return rc;
-    if (e.first()) return e.first();
+    if (e.first()) {
+        if (s->eval_pending) { CU(cudaStreamWaitEvent(s->stream, s->ev_eval, 0)); s->eval_pending = false; }      // nothing of this call may outlive it
+        return e.first();
+    }
     if (int rc = s->records.ensure(sizeof(RlcRecord))) return rc;
     if (int rc = run_rlc(s, 1, 0, 1, 1, s->records.as<RlcRecord>(), nullptr)) return rc;
     return finish_records(s, s->records.as<RlcRecord>(), 1, ok);

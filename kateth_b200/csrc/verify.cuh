@@ -117,7 +117,7 @@ __global__ void __launch_bounds__(RLC_THREADS) k_rlc(const G1Affine* __restrict_
         if (half) {
             if (!g1a_is_inf(p)) { Fp b; fp_set(b, c_k.fp_beta); fp_mul(p.x, p.x, b); fp_neg(p.y, p.y); }      // Q = (beta x, -y)
             k1 = k2;
-        } else if (which == 0) { Fr y = y_canon[i]; fr_mul(s, y, wgt); }
+        } else if (which == 0 && s_partials != nullptr) { Fr y = y_canon[i]; fr_mul(s, y, wgt); }
         g1_mul(acc, p, k1, 128);          // ONE call site: the two halves of a warp must not serialise their scalar multiplications
     }
 #pragma unroll 1
@@ -128,7 +128,7 @@ __global__ void __launch_bounds__(RLC_THREADS) k_rlc(const G1Affine* __restrict_
         __syncthreads();
     }
     if (tid == 0) partials[(size_t)which * gridDim.x + blockIdx.x] = acc;
-    if (which == 0) {
+    if (which == 0 && s_partials != nullptr) {
         sms[tid] = s;
         __syncthreads();
 #pragma unroll 1
@@ -138,6 +138,29 @@ __global__ void __launch_bounds__(RLC_THREADS) k_rlc(const G1Affine* __restrict_
         }
         if (tid == 0) s_partials[blockIdx.x] = sms[0];
     }
+}
+// The scalar part of the record on its own: s_partials[b] = sum of w_i * y_i over the items of k_rlc's block b (RLC_THREADS / 2 items).
+// Only this needs the evaluations y, so batch verification runs the barycentric evaluation BESIDE the scalar multiplications of
+// k_rlc (which need the challenges z only) and joins here.
+__global__ void __launch_bounds__(RLC_THREADS / 2) k_rlc_s(const Fr* __restrict__ y_canon, int n, uint32_t index_offset, const Fr* __restrict__ r_mont, int raw, int spec,
+                                                          const int32_t* __restrict__ status, Fr* __restrict__ s_partials) {
+    __shared__ Fr sms[RLC_THREADS / 2];
+    const int tid = threadIdx.x, i = blockIdx.x * (RLC_THREADS / 2) + tid;
+    Fr s; fr_zero(s);
+    if (i < n && (status == nullptr || status[i] == 0)) {
+        Fr wgt;
+        if (raw) fr_set(wgt, c_k.fr_one);
+        else { const uint32_t gi = index_offset + (uint32_t)i; Fr r = *r_mont; fr_pow_u32(wgt, r, (gi == 0 && !spec) ? 1u : gi); }
+        Fr y = y_canon[i]; fr_mul(s, y, wgt);
+    }
+    sms[tid] = s;
+    __syncthreads();
+#pragma unroll 1
+    for (int stride = RLC_THREADS / 4; stride >= 1; stride >>= 1) {
+        if (tid < stride) { Fr a = sms[tid], c = sms[tid + stride]; fr_add(a, a, c); sms[tid] = a; }
+        __syncthreads();
+    }
+    if (tid == 0) s_partials[blockIdx.x] = sms[0];
 }
 // grid 3 CTAs of RLC_FIN_THREADS: CTA `which` reduces its row of partials, normalises, writes the record field.
 #define RLC_FIN_THREADS 128
