@@ -96,6 +96,20 @@ struct kb200_setup {
 };
 
 #define LOCK(s) std::lock_guard<std::recursive_mutex> lock_((s)->mu)
+// KB200_TRACE=1: CUDA-event marks on the main stream at the phase boundaries of a call, printed to stderr when the call ends (debugging aid)
+struct Trace {
+    bool on = getenv("KB200_TRACE") != nullptr;
+    std::vector<std::pair<const char*, cudaEvent_t>> ev;
+    void mark(cudaStream_t st, const char* what) { if (!on) return; cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, st); ev.emplace_back(what, e); }
+    ~Trace() {
+        if (!on || ev.empty()) return;
+        cudaEventSynchronize(ev.back().second);
+        for (size_t i = 1; i < ev.size(); i++) { float ms = 0; cudaEventElapsedTime(&ms, ev[i - 1].second, ev[i].second); fprintf(stderr, "[kb200 trace] %-28s %8.3f ms\n", ev[i].first, ms); }
+        for (auto& p : ev) cudaEventDestroy(p.second);
+    }
+};
+static thread_local Trace* g_trace = nullptr;
+#define TRACE(s, what) do { if (g_trace) g_trace->mark((s)->stream, what); } while (0)
 #define LAUNCH(s, kern, grid, block, ...)                   \
     do {                                                    \
         kern<<<grid, block, 0, (s)->stream>>>(__VA_ARGS__); \
@@ -748,7 +762,7 @@ extern "C" int kb200_compute_blob_proof_device(kb200_setup* s, const void* d_blo
     s->launches++;
     CU(cudaEventRecord(s->ev_join, s->aux_stream));
     LAUNCH(s, k_blob_check, blocks(n * KB_N, 256), 256, (const uint32_t*)d_blobs, (int)n, s->st_blob.as<int32_t>());
-    if (!s->z_ready) LAUNCH(s, k_challenge, blocks(n, 32), 32, (const uint32_t*)d_blobs, (const uint32_t*)d_comm48, (int)n, s->st_blob.as<int32_t>(), s->z.as<Fr>());
+    if (!s->z_ready) LAUNCH(s, k_challenge_w2, blocks(n, 32), 64, (const uint32_t*)d_blobs, (const uint32_t*)d_comm48, (int)n, s->st_blob.as<int32_t>(), (uint32_t*)nullptr, s->z.as<Fr>(), 0, 2050);
     s->z_ready = false;
     CU(cudaStreamWaitEvent(s->stream, s->ev_join, 0));
     LAUNCH(s, k_merge_status, blocks(n, 256), 256, s->st_blob.as<int32_t>(), s->st_a.as<int32_t>(), (const int32_t*)nullptr, (int)n, d_status);
@@ -874,9 +888,12 @@ static int run_rlc(kb200_setup* s, size_t n, size_t index_offset, size_t n_total
     }
     if (nb) LAUNCH(s, k_rlc, dim3(nb, 3), RLC_THREADS, s->aff_p.as<G1Affine>(), s->aff_c.as<G1Affine>(), s->z.as<Fr>(), s->y.as<Fr>(), (int)n, (uint32_t)index_offset,
                    s->rmont.as<Fr>(), raw, spec, d_status, s->rlc_part.as<G1>(), (Fr*)nullptr);
+    TRACE(s, "k_rlc");
     if (s->eval_pending) { CU(cudaStreamWaitEvent(s->stream, s->ev_eval, 0)); s->eval_pending = false; }      // y: see verify_prepare
     if (nb) LAUNCH(s, k_rlc_s, nb, RLC_THREADS / 2, s->y.as<Fr>(), (int)n, (uint32_t)index_offset, s->rmont.as<Fr>(), raw, spec, d_status, s->rlc_s.as<Fr>());
+    TRACE(s, "join evaluation + k_rlc_s");
     LAUNCH(s, k_rlc_finish, 3, RLC_FIN_THREADS, s->rlc_part.as<G1>(), s->rlc_s.as<Fr>(), nb, d_record);     // nb == 0: the identity record
+    TRACE(s, "k_rlc_finish");
     return 0;
 }
 // the shard's errors travel with its sums (k_rlc_finish wrote zeros)
@@ -933,44 +950,57 @@ static int verify_prepare(kb200_setup* s, const uint32_t* d_blobs, const uint32_
     Fr *z = s->z.as<Fr>() + off, *y = s->y.as<Fr>() + off;
     const int n = (int)m;
     CU(cudaMemsetAsync(st_blob, 0, m * 4, s->stream));
-    // Two latency-bound kernels that do not depend on each other run side by side: the point decompression (a 380-step
-    // square-and-multiply chain per point) on the auxiliary stream, the blob check and the serial SHA-256 of each blob on the
-    // main one.  The challenge only needs the blob's own status; items with a bad point are dropped after the join.
-    // (A host-buffer caller has already marked the fork point, before the blob upload it queued: fork_recorded.)
-    if (!s->fork_recorded) CU(cudaEventRecord(s->ev_fork, s->stream));
+    TRACE(s, "start");
+    const bool forked = s->fork_recorded;       // a host-buffer caller marked the fork point before the blob upload it queued
     s->fork_recorded = false;
-    CU(cudaStreamWaitEvent(s->aux_stream, s->ev_fork, 0));
-    CU(cudaMemsetAsync(st_a, 0, m * 4, s->aux_stream));
-    CU(cudaMemsetAsync(st_b, 0, m * 4, s->aux_stream));
-    k_g1_decompress<<<blocks(2 * m, 64), 64, 0, s->aux_stream>>>(d_c48, d_p48, n, aff_c, aff_p, st_a, st_b, 0);
-    s->launches++;
-    CU(cudaEventRecord(s->ev_join, s->aux_stream));
+    if (forked) {
+        // host-buffer call: the point decompression (a 380-step square-and-multiply chain per point) runs on the auxiliary stream UNDER
+        // the upload of the blobs; the challenges came with the upload (z_ready) or follow it
+        CU(cudaStreamWaitEvent(s->aux_stream, s->ev_fork, 0));
+        CU(cudaMemsetAsync(st_a, 0, m * 4, s->aux_stream));
+        CU(cudaMemsetAsync(st_b, 0, m * 4, s->aux_stream));
+        k_g1_decompress<<<blocks(2 * m, 64), 64, 0, s->aux_stream>>>(d_c48, d_p48, n, aff_c, aff_p, st_a, st_b, 0);
+        s->launches++;
+        CU(cudaEventRecord(s->ev_join, s->aux_stream));
+    }
     LAUNCH(s, k_blob_check, blocks(m * KB_N, 256), 256, d_blobs, n, st_blob);
-    if (!s->z_ready) LAUNCH(s, k_challenge, blocks(m, 32), 32, d_blobs, d_c48, n, st_blob, z);
+    if (!s->z_ready) LAUNCH(s, k_challenge_w2, blocks(m, 32), 64, d_blobs, d_c48, n, st_blob, (uint32_t*)nullptr, z, 0, 2050);
     s->z_ready = false;
-    CU(cudaStreamWaitEvent(s->stream, s->ev_join, 0));
-    LAUNCH(s, k_merge_status, blocks(m, 256), 256, st_blob, st_a, st_b, n, d_status);
-    // The evaluations y are only needed for the scalar s of the record; the scalar multiplications of k_rlc need z.  So the evaluation
-    // goes to the auxiliary stream and, for the last (or only) chunk of a call, run_rlc joins it after k_rlc; an earlier chunk joins at
-    // once, because the next chunk's upload reuses the blob buffer the evaluation reads.
+    TRACE(s, "blob check + challenge");
+    if (forked) CU(cudaStreamWaitEvent(s->stream, s->ev_join, 0));
+    else {
+        // resident data: the decompression runs AFTER the challenge, not beside it -- the serial SHA-256 chains are the critical path
+        // and stretch from 2.4 to 5.6 ms when 8192 decompression threads compete for issue slots on the same SMs
+        CU(cudaMemsetAsync(st_a, 0, m * 4, s->stream));
+        CU(cudaMemsetAsync(st_b, 0, m * 4, s->stream));
+        LAUNCH(s, k_g1_decompress, blocks(2 * m, 64), 64, d_c48, d_p48, n, aff_c, aff_p, st_a, st_b, 0);
+    }
+    // The evaluations y are only needed for the scalar s of the record; the scalar multiplications of k_rlc need z and the points.  So
+    // the evaluation (multiplier-bound) goes to the auxiliary stream HERE, beside k_rlc (latency-bound: 128-step ladders on few warps),
+    // and for the last (or only) chunk of a call run_rlc joins it after k_rlc; an earlier chunk joins at once, because the next chunk's
+    // upload reuses the blob buffer the evaluation reads.  It skips blobs that failed their own check; a bad point does not matter to it.
     {
         CU(cudaEventRecord(s->ev_fork, s->stream));
         CU(cudaStreamWaitEvent(s->aux_stream, s->ev_fork, 0));
         cudaStream_t keep = s->stream; s->stream = s->aux_stream;
-        int rc = run_eval<false>(s, d_blobs, m, d_status, z, y);
+        int rc = run_eval<false>(s, d_blobs, m, st_blob, z, y);
         s->stream = keep;
         if (rc) return rc;
         CU(cudaEventRecord(s->ev_eval, s->aux_stream));
         s->eval_pending = true;
         if (!last) { CU(cudaStreamWaitEvent(s->stream, s->ev_eval, 0)); s->eval_pending = false; }
     }
+    TRACE(s, "decompress");
+    LAUNCH(s, k_merge_status, blocks(m, 256), 256, st_blob, st_a, st_b, n, d_status);
     std::vector<int32_t> h0, h1, h2;
+    TRACE(s, "merge status");
     if (int rc = fetch_status(s, st_blob, m, h0)) return rc;
     if (int rc = fetch_status(s, st_a, m, h1)) return rc;
     if (int rc = fetch_status(s, st_b, m, h2)) return rc;
     if (!e.blob) e.blob = first_nonzero(h0);
     if (!e.comm) e.comm = first_nonzero(h1);
     if (!e.proof) e.proof = first_nonzero(h2);
+    TRACE(s, "fetch statuses (host sync)");
     return 0;
 }
 extern "C" int kb200_verify_blob_proof_batch_partial_device(kb200_setup* s, const void* d_blobs, const void* d_c48, const void* d_p48, size_t n,
@@ -978,6 +1008,8 @@ extern "C" int kb200_verify_blob_proof_batch_partial_device(kb200_setup* s, cons
     if (!s || !d_record || (n && (!d_blobs || !d_c48 || !d_p48 || !d_status))) return KB200_E_ARG;
     LOCK(s);
     CU(cudaSetDevice(s->device));
+    Trace trace; g_trace = trace.on ? &trace : nullptr;
+    struct Untrace { ~Untrace() { g_trace = nullptr; } } untrace;
     VErr e;
     if (int rc = verify_reserve(s, n)) return rc;
     if (n) if (int rc = verify_prepare(s, (const uint32_t*)d_blobs, (const uint32_t*)d_c48, (const uint32_t*)d_p48, n, 0, d_status, e)) return rc;
@@ -1068,7 +1100,7 @@ static int h2d_blobs_hashed(kb200_setup* s, const uint8_t* blobs, size_t n, cons
     for (int j = 0; j < NCOL; j++) {
         CU(cudaStreamWaitEvent(s->stream, s->ev_col[j], 0));
         const int blk0 = (int)(j * W / 64), blk1 = (j == NCOL - 1) ? 2050 : (int)((j + 1) * W / 64);
-        LAUNCH(s, k_challenge_range, blocks(n, 32), 32, s->blobs.as<uint32_t>(), d_c48, (int)n, s->sha_state.as<uint32_t>(), d_z, blk0, blk1);
+        LAUNCH(s, k_challenge_w2, blocks(n, 32), 64, s->blobs.as<uint32_t>(), d_c48, (int)n, (const int32_t*)nullptr, s->sha_state.as<uint32_t>(), d_z, blk0, blk1);
     }
     s->z_ready = true;
     return 0;

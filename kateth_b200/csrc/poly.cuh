@@ -180,6 +180,113 @@ __global__ void k_challenge_range(const uint32_t* __restrict__ blobs, const uint
     z_out[b] = z;
 }
 
+// ---- the same hash with the work of one blob spread over TWO warps (one CTA = 32 blobs, 64 threads) ----
+// A SHA-256 stream is serial, and with one thread per blob the kernel's duration IS the latency of one thread's chain: ~3.9 k cycles per
+// 64-byte block, of which only the 64 rounds (four dependent operations each) are inherently serial -- the message schedule (48 words of
+// sigma0 / sigma1 expansion), the loads and the byte swaps are not.  So lane l of warp 1 prepares K[i] + w[i] for blob l's next block in
+// shared memory (double-buffered, named barriers) while lane l of warp 0 runs the rounds of the current one.
+// Covers both forms: all 2,050 blocks (state == nullptr) or a range [blk0, blk1) with the chaining value parked in `state`.
+#define CH2_FULL 1      // named barriers: FULL + j = buffer j holds a block, EMPTY + j = buffer j has been read
+#define CH2_EMPTY 3
+__device__ __forceinline__ void ch2_bar_sync(int id) { asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory"); }
+__device__ __forceinline__ void ch2_bar_arrive(int id) { asm volatile("bar.arrive %0, 64;" ::"r"(id) : "memory"); }
+// the sixteen big-endian message words of block k of  "FSBLOBVERIFY_V1_" | u128_be(4096) | blob | compress(C)
+__device__ __forceinline__ void ch2_block_words(uint32_t (&w)[16], int k, const uint4* __restrict__ bp, const uint32_t* __restrict__ cp) {
+    if (k == 0) {
+        w[0] = 0x4653424c; w[1] = 0x4f425645; w[2] = 0x52494659; w[3] = 0x5f56315f; w[4] = 0; w[5] = 0; w[6] = 0; w[7] = KB_N;
+        uint4 c0 = __ldg(bp), c1 = __ldg(bp + 1);
+        w[8] = bswap32(c0.x); w[9] = bswap32(c0.y); w[10] = bswap32(c0.z); w[11] = bswap32(c0.w);
+        w[12] = bswap32(c1.x); w[13] = bswap32(c1.y); w[14] = bswap32(c1.z); w[15] = bswap32(c1.w);
+    } else if (k < 2048) {
+        const uint4* p = bp + (4 * k - 2);
+        uint4 v0 = __ldg(p), v1 = __ldg(p + 1), v2 = __ldg(p + 2), v3 = __ldg(p + 3);
+        w[0] = bswap32(v0.x); w[1] = bswap32(v0.y); w[2] = bswap32(v0.z); w[3] = bswap32(v0.w);
+        w[4] = bswap32(v1.x); w[5] = bswap32(v1.y); w[6] = bswap32(v1.z); w[7] = bswap32(v1.w);
+        w[8] = bswap32(v2.x); w[9] = bswap32(v2.y); w[10] = bswap32(v2.z); w[11] = bswap32(v2.w);
+        w[12] = bswap32(v3.x); w[13] = bswap32(v3.y); w[14] = bswap32(v3.z); w[15] = bswap32(v3.w);
+    } else if (k == 2048) {
+        const uint4* p = bp + (4 * 2048 - 2);
+        uint4 v0 = __ldg(p), v1 = __ldg(p + 1);
+        w[0] = bswap32(v0.x); w[1] = bswap32(v0.y); w[2] = bswap32(v0.z); w[3] = bswap32(v0.w);
+        w[4] = bswap32(v1.x); w[5] = bswap32(v1.y); w[6] = bswap32(v1.z); w[7] = bswap32(v1.w);
+#pragma unroll
+        for (int q = 0; q < 8; q++) w[8 + q] = bswap32(cp[q]);
+    } else {
+#pragma unroll
+        for (int q = 0; q < 4; q++) w[q] = bswap32(cp[8 + q]);
+        w[4] = 0x80000000u;
+#pragma unroll
+        for (int q = 5; q < 15; q++) w[q] = 0;
+        w[15] = 131152u * 8u;
+    }
+}
+__global__ void __launch_bounds__(64) k_challenge_w2(const uint32_t* __restrict__ blobs, const uint32_t* __restrict__ comm48, int n, const int32_t* __restrict__ status,
+                                                     uint32_t* __restrict__ state, Fr* __restrict__ z_out, int blk0, int blk1) {
+    __shared__ uint32_t kw[2][64][32];
+    const int lane = threadIdx.x & 31, role = threadIdx.x >> 5;
+    const int b = blockIdx.x * 32 + lane, bc = b < n ? b : n - 1;          // lanes past the end hash the last blob again and write nothing
+    const uint4* bp = reinterpret_cast<const uint4*>(blobs + (size_t)bc * (KB_N * 8));
+    const uint32_t* cp = comm48 + (size_t)bc * 12;
+    if (role == 1) {
+        // ---- producer: K[i] + w[i], i = 0..63, for every block of the range ----
+#pragma unroll 1
+        for (int k = blk0; k < blk1; k++) {
+            const int j = (k - blk0) & 1;
+            uint32_t w[16];
+            ch2_block_words(w, k, bp, cp);
+            if (k - blk0 >= 2) ch2_bar_sync(CH2_EMPTY + j);
+#pragma unroll
+            for (int i = 0; i < 64; i++) {
+                if (i >= 16) {
+                    const uint32_t w15 = w[(i + 1) & 15], w2 = w[(i + 14) & 15];
+                    const uint32_t s0 = rotr(w15, 7) ^ rotr(w15, 18) ^ (w15 >> 3);
+                    const uint32_t s1 = rotr(w2, 17) ^ rotr(w2, 19) ^ (w2 >> 10);
+                    w[i & 15] = w[i & 15] + s0 + w[(i + 9) & 15] + s1;
+                }
+                kw[j][i][lane] = w[i & 15] + c_sha_k[i];
+            }
+            ch2_bar_arrive(CH2_FULL + j);
+        }
+        return;
+    }
+    // ---- consumer: the 64 rounds of every block ----
+    uint32_t h[8];
+    if (blk0 == 0) sha256_init(h);
+    else {
+#pragma unroll
+        for (int q = 0; q < 8; q++) h[q] = state[(size_t)q * n + bc];
+    }
+#pragma unroll 1
+    for (int k = blk0; k < blk1; k++) {
+        const int j = (k - blk0) & 1;
+        ch2_bar_sync(CH2_FULL + j);
+        uint32_t x[64];
+#pragma unroll
+        for (int i = 0; i < 64; i++) x[i] = kw[j][i][lane];
+        if (k + 2 < blk1) ch2_bar_arrive(CH2_EMPTY + j);
+        uint32_t a = h[0], bb = h[1], c = h[2], d = h[3], e = h[4], f = h[5], g = h[6], hh = h[7];
+#pragma unroll
+        for (int i = 0; i < 64; i++) {
+            const uint32_t t1 = hh + x[i] + (rotr(e, 6) ^ rotr(e, 11) ^ rotr(e, 25)) + ((e & f) ^ (~e & g));
+            const uint32_t t2 = (rotr(a, 2) ^ rotr(a, 13) ^ rotr(a, 22)) + ((a & bb) ^ (a & c) ^ (bb & c));
+            hh = g; g = f; f = e; e = d + t1; d = c; c = bb; bb = a; a = t1 + t2;
+        }
+        h[0] += a; h[1] += bb; h[2] += c; h[3] += d; h[4] += e; h[5] += f; h[6] += g; h[7] += hh;
+    }
+    if (b >= n) return;
+    if (blk1 < 2050) {
+#pragma unroll
+        for (int q = 0; q < 8; q++) state[(size_t)q * n + b] = h[q];
+        return;
+    }
+    Fr z;
+#pragma unroll
+    for (int q = 0; q < 8; q++) z.l[7 - q] = h[q];
+    fr_reduce_256(z);
+    if (status != nullptr && status[b] != 0) fr_zero(z);
+    z_out[b] = z;
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // Evaluation, phase 1.  CTA per blob, EV_THREADS threads, EV_PER = 4096/EV_THREADS denominators per thread
 // (element index i = k*EV_THREADS + tid).  d_i = z - w_i; if some d_m == 0 (z in the domain, poly.rs:14-18) the
