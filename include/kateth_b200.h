@@ -105,6 +105,16 @@ int kb200_g1_validate(const uint8_t* in48, size_t n, int device, int32_t* status
 int kb200_blob_to_commitment(kb200_setup* s, const uint8_t* blobs, size_t n, uint8_t* out48, int32_t* status);
 int kb200_blob_to_commitment_device(kb200_setup* s, const void* d_blobs, size_t n, void* d_out48, int32_t* d_status);
 
+/* NO counterpart in the reference: added for callers that cannot call cudaMalloc (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid it).  Same bytes as kb200_blob_to_commitment_device for n <=
+ * KB200_NOALLOC_MAX_BLOBS blobs (more: KB200_E_ARG and a message in kb200_last_error), but the call allocates nothing on host or device:
+ * the MSM's partial sums live in a static 384 KiB device array that every GPU loading the library holds until exit.  Enqueue-only on the
+ * handle's stream (kb200_set_stream): it returns 0 once the work is queued; d_status[i] (0, or the error class of blob i, whose
+ * output is then 48 zero bytes) and d_out48 are valid when that stream has passed them.  All calls on one GPU share the array and it keeps
+ * the last call's contents: calls that overlap on the device (two handles or two streams on the same GPU) race. */
+#define KB200_NOALLOC_MAX_BLOBS 64
+int kb200_blob_to_commitment_device_noalloc(kb200_setup* s, const void* d_blobs, size_t n, void* d_out48, int32_t* d_status);
+
 /* Blob::from_slice alone (src/blob.rs:26-37) over n full-length blobs: status[i] = 0 or KB200_E_INVALID_FIELD_ELEMENT; returns the first
  * non-zero status.  For wrappers whose callers pass blobs of unequal byte lengths (kateth: `impl AsRef<[u8]>` per blob) and that must
  * report the first error in blob order -- an element error of blob 3 before the length error of blob 7. */

@@ -75,6 +75,7 @@ struct kb200_setup {
     int challenge_mode = 0;          // batch-verification challenge: 0 = kateth's (parity with the reference), 1 = consensus-spec transcript
     DBuf transcript;
     unsigned int* d_counter = nullptr;
+    G1* d_noalloc = nullptr;         // device address of g_noalloc_scratch on this handle's GPU (kb200_blob_to_commitment_device_noalloc)
     cudaStream_t aux_stream = nullptr;      // independent light kernels of one call run beside each other (verify_prepare)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     cudaStream_t copy_stream = nullptr;     // host-buffer entry points: blobs cross PCIe in two pieces (h2d_split)
@@ -336,6 +337,29 @@ static void cache_store(kb200_setup* s, const std::string& path, CacheHeader h, 
     if (ok) rename(tmp.c_str(), path.c_str()); else remove(tmp.c_str());
 }
 
+// ------------------------------------------------------------------ scratch of the allocation-free commit entry point
+// kb200_blob_to_commitment_device_noalloc (below) keeps the per-(blob, slice) partial sums of k_msm in this file-scope array instead of
+// the handle's growable workspace: KB200_NOALLOC_MAX_BLOBS blobs x 32 slices x one XYZZ point (192 B) = 384 KiB, held by every GPU that
+// loads the library until the process exits.  In HOST code the name below is only a stand-in for the symbol: the address a kernel can
+// use comes from cudaGetSymbolAddress, asked once per device with that device current.
+#define NOALLOC_SLICES 32
+static __device__ __align__(256) uint4 g_noalloc_scratch[(size_t)KB200_NOALLOC_MAX_BLOBS * NOALLOC_SLICES * (sizeof(G1) / sizeof(uint4))];
+static_assert(sizeof(G1) % sizeof(uint4) == 0, "XYZZ point is a whole number of 16-byte words");
+static std::mutex g_noalloc_mu;
+static void* g_noalloc_ptr[64] = {};          // per device ordinal
+static int noalloc_setup(kb200_setup* s) {    // called from build_setup with s->device current
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (s->device < 0 || s->device >= 64) return KB200_E_ARG;
+    if (!g_noalloc_ptr[s->device]) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) { snprintf(g_err, sizeof g_err, "cudaGetSymbolAddress(g_noalloc_scratch) on device %d: %s", s->device, cudaGetErrorString(e)); return KB200_E_CUDA; }
+        g_noalloc_ptr[s->device] = p;
+    }
+    s->d_noalloc = (G1*)g_noalloc_ptr[s->device];
+    return 0;
+}
+
 static int build_setup(kb200_setup* s, const uint8_t* g1, const uint8_t* g2, int window_bits) {
     auto t0 = std::chrono::steady_clock::now();
     CU(cudaSetDevice(s->device));
@@ -450,6 +474,7 @@ static int build_setup(kb200_setup* s, const uint8_t* g1, const uint8_t* g2, int
         if (ba_init(&plan) != 0) { snprintf(g_err, sizeof g_err, "ba_init: %s", cudaGetErrorString(cudaGetLastError())); return KB200_E_CUDA; }
         s->ba_grid = plan.ctas_per_sm * s->sm_count;
         CU(cudaMalloc(&s->d_counter, sizeof(unsigned int)));
+        if (int rc = noalloc_setup(s)) return rc;
         CU(cudaStreamCreateWithFlags(&s->aux_stream, cudaStreamNonBlocking));
         CU(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&s->ev_join, cudaEventDisableTiming));
@@ -728,6 +753,34 @@ extern "C" int kb200_blob_to_commitment_device(kb200_setup* s, const void* d_blo
     if (int rc = run_msm<0>(s, (const uint32_t*)d_blobs, n, d_status, (uint32_t*)d_out48)) return rc;
     std::vector<int32_t> h; if (int rc = fetch_status(s, d_status, n, h)) return rc;
     return first_nonzero(h);
+}
+
+// The same commitments with NO allocation of any kind (no counterpart in kateth; added for callers
+// that cannot call cudaMalloc: graph capture, tight serving loops).  At most KB200_NOALLOC_MAX_BLOBS blobs per call; always the sliced XYZZ
+// shape k_msm (the batch-affine shape needs gigabytes of workspace), its partial sums in g_noalloc_scratch.  Enqueue-only: blob check, MSM
+// and compression go onto the handle's stream and the call returns; d_status[i] (0 or the blob's error class) and d_out48 are valid once
+// that stream has passed them.  Every call on a GPU shares the one array: calls that overlap on the device (two handles or two streams
+// on one GPU) race.  k_msm writes every partial slot it later reads, so nothing in the array has to start at zero; the slots of the call
+// are cleared anyway so that a skipped launch could not pass on the previous call's sums.
+extern "C" int kb200_blob_to_commitment_device_noalloc(kb200_setup* s, const void* d_blobs, size_t n, void* d_out48, int32_t* d_status) {
+    if (!s || (n && (!d_blobs || !d_out48 || !d_status))) return KB200_E_ARG;
+    if (n > (size_t)KB200_NOALLOC_MAX_BLOBS) {
+        snprintf(g_err, sizeof g_err, "kb200_blob_to_commitment_device_noalloc: %zu blobs exceed the static scratch (KB200_NOALLOC_MAX_BLOBS = %d)", n, KB200_NOALLOC_MAX_BLOBS);
+        return KB200_E_ARG;
+    }
+    LOCK(s);
+    CU(cudaSetDevice(s->device));
+    if (n == 0) return 0;
+    if (!s->d_noalloc) { snprintf(g_err, sizeof g_err, "static scratch address missing (setup did not complete)"); return KB200_E_CUDA; }
+    int S = pick_slices(s, n);
+    if (S > NOALLOC_SLICES) S = NOALLOC_SLICES;
+    CU(cudaMemsetAsync(d_status, 0, n * 4, s->stream));
+    CU(cudaMemsetAsync(s->d_noalloc, 0, n * S * sizeof(G1), s->stream));
+    LAUNCH(s, k_blob_check, blocks(n * KB_N, 256), 256, (const uint32_t*)d_blobs, (int)n, d_status);
+    LAUNCH(s, (k_msm<0>), (unsigned)(n * S), MSM_THREADS, s->tab, (const uint32_t*)d_blobs, (const int32_t*)d_status, s->d_noalloc, S);
+    LAUNCH(s, k_msm_finish, blocks(n, FIN_WARPS), 32 * FIN_WARPS, (const G1*)s->d_noalloc, S, (int)n, (const int32_t*)d_status, (uint32_t*)d_out48, (G1Affine*)nullptr);
+    CU(cudaGetLastError());
+    return 0;
 }
 
 // shared tail of blob_proof / proof: z in s->z (n items), status final -> quotient -> MSM -> compressed proofs; y is left in s->out32

@@ -4,6 +4,7 @@ import os
 
 BYTES_PER_BLOB = 131072
 RECORD_BYTES = 336
+NOALLOC_MAX_BLOBS = 64  # KB200_NOALLOC_MAX_BLOBS (include/kateth_b200.h)
 _HERE = os.path.dirname(os.path.abspath(__file__))
 
 _STATUS_NAMES = {
@@ -38,7 +39,7 @@ class _Info(C.Structure):
 # every symbol include/kateth_b200.h declares (tests/test_abi.py checks the header against this list and the .so)
 SYMBOLS = [
     "kb200_setup_load_json", "kb200_setup_load_txt", "kb200_setup_load_raw", "kb200_setup_free", "kb200_setup_check_g1_monomial", "kb200_set_table_cache", "kb200_g1_validate", "kb200_set_stream", "kb200_last_error", "kb200_alloc_pinned", "kb200_free_pinned",
-    "kb200_blob_to_commitment", "kb200_blob_to_commitment_device", "kb200_check_blobs", "kb200_compute_blob_proof", "kb200_compute_blob_proof_device",
+    "kb200_blob_to_commitment", "kb200_blob_to_commitment_device", "kb200_blob_to_commitment_device_noalloc", "kb200_check_blobs", "kb200_compute_blob_proof", "kb200_compute_blob_proof_device",
     "kb200_compute_proof", "kb200_compute_proof_device", "kb200_verify_proof", "kb200_verify_proof_batch", "kb200_verify_proof_many", "kb200_verify_blob_proof",
     "kb200_verify_blob_proof_batch", "kb200_verify_blob_proof_batch_device", "kb200_verify_blob_proof_batch_partial_device",
     "kb200_verify_blob_proof_batch_partial", "kb200_commit_prove_verify_partial", "kb200_verify_proof_batch_partial_device", "kb200_verify_proof_batch_partial", "kb200_verify_batch_finish_device", "kb200_set_profiling", "kb200_set_msm_mode", "kb200_set_batch_challenge", "kb200_get_msm_profile", "kb200_last_pairing_operands", "kb200_get_info", "kb200_test_fp_mul", "kb200_test_fr_mul",
@@ -255,6 +256,11 @@ class Setup:
         return bool(ok.value)
 
     # device-pointer calls (integers = device addresses, e.g. torch.Tensor.data_ptr())
+    def blob_to_commitment_device_noalloc(self, d_blobs, n, d_out48, d_status):
+        """kb200_blob_to_commitment_device_noalloc: at most NOALLOC_MAX_BLOBS blobs, nothing allocated, enqueue-only (the caller
+        synchronises the stream and reads d_status / d_out48)."""
+        return lib().kb200_blob_to_commitment_device_noalloc(self._h, _vp(d_blobs), C.c_size_t(n), _vp(d_out48), _vp(d_status))
+
     def blob_to_commitment_device(self, d_blobs, n, d_out48, d_status):
         return lib().kb200_blob_to_commitment_device(self._h, _vp(d_blobs), C.c_size_t(n), _vp(d_out48), _vp(d_status))
 

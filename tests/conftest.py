@@ -67,3 +67,12 @@ def gpu_free():
 
 def pytest_sessionfinish(session, exitstatus):
     release_engines()
+
+
+@pytest.fixture
+def any_engine():
+    """Whichever engine is alive (after the other tests: the last configuration they used), else the small table -- for tests that do not
+    depend on the table form and must not be reordered by a parametrised session fixture (tests/test_zz_no_alloc.py runs last)."""
+    if _ENGINES:
+        return next(iter(_ENGINES.values()))
+    return engine(int(os.environ.get("KB200_WINDOW_BITS", "13")))
