@@ -72,6 +72,8 @@ struct kb200_setup {
         records, combine, dig, scr_pts, scr_pre, st_tmp;
     // batch-affine MSM (msm_ba.cuh): 0 = automatic (batches that fill the GPU), 1 = always k_msm, 2 = always k_msm_ba
     int msm_mode = 0, ba_grid = 0, last_ba = 0;
+    int rlc_mode = 0;                // sums of batch verification: 0 = automatic (buckets from RLC_BUCKET_MIN items), 1 = ladders (k_rlc), 2 = buckets (k_rlc_bucket)
+    DBuf rlc_dig, rlc_wsum;
     int challenge_mode = 0;          // batch-verification challenge: 0 = kateth's (parity with the reference), 1 = consensus-spec transcript
     DBuf transcript;
     unsigned int* d_counter = nullptr;
@@ -117,6 +119,7 @@ static thread_local Trace* g_trace = nullptr;
         (s)->launches++;                                    \
     } while (0)
 
+static const size_t RLC_BUCKET_MIN = 512;   // batch verification: shards from this size sum their terms with the bucket method (verify.cuh)
 static const size_t CHUNK = 4096;   // blobs per internal pass (bounds the quotient scratch to 512 MiB)
 
 static int init_consts() {
@@ -485,6 +488,7 @@ static int build_setup(kb200_setup* s, const uint8_t* g1, const uint8_t* g2, int
         CU(cudaEventCreateWithFlags(&s->ev_tail, cudaEventDisableTiming));
         for (int j = 0; j < 8; j++) CU(cudaEventCreateWithFlags(&s->ev_col[j], cudaEventDisableTiming));
         if (const char* e = getenv("KB200_MSM_MODE")) { int m = atoi(e); if (m >= 0 && m <= 2) s->msm_mode = m; }
+        if (const char* e = getenv("KB200_RLC_MODE")) { int m = atoi(e); if (m >= 0 && m <= 2) s->rlc_mode = m; }
         if (const char* e = getenv("KB200_H2D_SPLIT")) s->split_copy = atoi(e) != 0;
     }
     s->table_bytes = bytes;
@@ -625,7 +629,7 @@ extern "C" void kb200_setup_free(kb200_setup* s) {
     for (int j = 0; j < 8; j++) if (s->ev_col[j]) cudaEventDestroy(s->ev_col[j]);
     s->sha_state.release();
     DBuf* bufs[] = {&s->blobs, &s->c48, &s->p48, &s->zy32, &s->out48, &s->out32, &s->st_blob, &s->st_a, &s->st_b, &s->status, &s->z, &s->y, &s->prod,
-                    &s->indom, &s->q, &s->partials, &s->aff_c, &s->aff_p, &s->rlc_part, &s->rlc_s, &s->rmont, &s->records, &s->combine, &s->dig, &s->scr_pts, &s->scr_pre, &s->transcript, &s->st_tmp};
+                    &s->indom, &s->q, &s->partials, &s->aff_c, &s->aff_p, &s->rlc_part, &s->rlc_s, &s->rmont, &s->records, &s->combine, &s->dig, &s->scr_pts, &s->scr_pre, &s->transcript, &s->st_tmp, &s->rlc_dig, &s->rlc_wsum};
     for (DBuf* b : bufs) b->release();
     for (cudaEvent_t e : s->prof_ev) cudaEventDestroy(e);
     delete s;
@@ -650,6 +654,12 @@ extern "C" int kb200_set_msm_mode(kb200_setup* s, int mode) {
     if (!s || mode < 0 || mode > 2) return KB200_E_ARG;
     LOCK(s);
     s->msm_mode = mode;
+    return 0;
+}
+extern "C" int kb200_set_rlc_mode(kb200_setup* s, int mode) {
+    if (!s || mode < 0 || mode > 2) return KB200_E_ARG;
+    LOCK(s);
+    s->rlc_mode = mode;
     return 0;
 }
 extern "C" int kb200_set_profiling(kb200_setup* s, int on) {
@@ -912,7 +922,13 @@ static int verify_reserve(kb200_setup* s, size_t n) {
 static int run_rlc(kb200_setup* s, size_t n, size_t index_offset, size_t n_total, int raw, RlcRecord* d_record, const int32_t* d_status,
                    const uint32_t* d_c48 = nullptr, const uint32_t* d_p48 = nullptr) {
     int nb = blocks(2 * n, RLC_THREADS);          // two threads per term (GLV halves); 0 for an empty shard
-    if (int rc = s->rlc_part.ensure((size_t)3 * (nb ? nb : 1) * sizeof(G1))) return rc;
+    const bool buckets = s->rlc_mode == 2 ? n > 0 : (s->rlc_mode == 0 && n >= RLC_BUCKET_MIN);
+    const int nslices = (int)((n + RLCB_ITEMS - 1) / RLCB_ITEMS);
+    if (int rc = s->rlc_part.ensure((size_t)3 * (nb > RLCB_WINDOWS ? nb : RLCB_WINDOWS) * sizeof(G1))) return rc;
+    if (buckets) {
+        if (int rc = s->rlc_dig.ensure((size_t)2 * RLCB_WINDOWS * n * sizeof(uint16_t))) return rc;
+        if (int rc = s->rlc_wsum.ensure((size_t)3 * RLCB_WINDOWS * nslices * sizeof(G1))) return rc;
+    }
     if (int rc = s->rlc_s.ensure((size_t)(nb ? nb : 1) * sizeof(Fr))) return rc;
     if (int rc = s->rmont.ensure(sizeof(Fr))) return rc;
     const int spec = (!raw && s->challenge_mode == 1) ? 1 : 0;
@@ -939,13 +955,19 @@ static int run_rlc(kb200_setup* s, size_t n, size_t index_offset, size_t n_total
     } else if (!raw) {
         LAUNCH(s, k_batch_r, 1, 1, (uint32_t)n_total, s->rmont.as<Fr>());
     }
-    if (nb) LAUNCH(s, k_rlc, dim3(nb, 3), RLC_THREADS, s->aff_p.as<G1Affine>(), s->aff_c.as<G1Affine>(), s->z.as<Fr>(), s->y.as<Fr>(), (int)n, (uint32_t)index_offset,
-                   s->rmont.as<Fr>(), raw, spec, d_status, s->rlc_part.as<G1>(), (Fr*)nullptr);
+    if (buckets) {
+        LAUNCH(s, k_rlc_scalars, blocks(n, 128), 128, s->z.as<Fr>(), (int)n, (uint32_t)index_offset, s->rmont.as<Fr>(), raw, spec, d_status, s->rlc_dig.as<uint16_t>());
+        LAUNCH(s, k_rlc_bucket, dim3(RLCB_WINDOWS * nslices, 3), RLCB_THREADS, s->aff_p.as<G1Affine>(), s->aff_c.as<G1Affine>(), s->rlc_dig.as<uint16_t>(), (int)n, nslices,
+               s->rlc_wsum.as<G1>());
+        LAUNCH(s, k_rlc_shift, dim3(RLCB_WINDOWS, 3), 32, s->rlc_wsum.as<G1>(), nslices, s->rlc_part.as<G1>());
+    } else if (nb)
+        LAUNCH(s, k_rlc, dim3(nb, 3), RLC_THREADS, s->aff_p.as<G1Affine>(), s->aff_c.as<G1Affine>(), s->z.as<Fr>(), s->y.as<Fr>(), (int)n, (uint32_t)index_offset,
+               s->rmont.as<Fr>(), raw, spec, d_status, s->rlc_part.as<G1>(), (Fr*)nullptr);
     TRACE(s, "k_rlc");
     if (s->eval_pending) { CU(cudaStreamWaitEvent(s->stream, s->ev_eval, 0)); s->eval_pending = false; }      // y: see verify_prepare
     if (nb) LAUNCH(s, k_rlc_s, nb, RLC_THREADS / 2, s->y.as<Fr>(), (int)n, (uint32_t)index_offset, s->rmont.as<Fr>(), raw, spec, d_status, s->rlc_s.as<Fr>());
     TRACE(s, "join evaluation + k_rlc_s");
-    LAUNCH(s, k_rlc_finish, 3, RLC_FIN_THREADS, s->rlc_part.as<G1>(), s->rlc_s.as<Fr>(), nb, d_record);     // nb == 0: the identity record
+    LAUNCH(s, k_rlc_finish, 3, RLC_FIN_THREADS, s->rlc_part.as<G1>(), buckets ? RLCB_WINDOWS : nb, s->rlc_s.as<Fr>(), nb, d_record);     // nb == 0: the identity record
     TRACE(s, "k_rlc_finish");
     return 0;
 }
@@ -1021,19 +1043,8 @@ static int verify_prepare(kb200_setup* s, const uint32_t* d_blobs, const uint32_
     s->z_ready = false;
     TRACE(s, "blob check + challenge");
     if (forked) CU(cudaStreamWaitEvent(s->stream, s->ev_join, 0));
-    else {
-        // resident data: the decompression runs AFTER the challenge, not beside it -- the serial SHA-256 chains are the critical path
-        // and stretch from 2.4 to 5.6 ms when 8192 decompression threads compete for issue slots on the same SMs
-        CU(cudaMemsetAsync(st_a, 0, m * 4, s->stream));
-        CU(cudaMemsetAsync(st_b, 0, m * 4, s->stream));
-        LAUNCH(s, k_g1_decompress, blocks(2 * m, 64), 64, d_c48, d_p48, n, aff_c, aff_p, st_a, st_b, 0);
-    }
-    // The evaluations y are only needed for the scalar s of the record; the scalar multiplications of k_rlc need z and the points.  So
-    // the evaluation (multiplier-bound) goes to the auxiliary stream HERE, beside k_rlc (latency-bound: 128-step ladders on few warps),
-    // and for the last (or only) chunk of a call run_rlc joins it after k_rlc; an earlier chunk joins at once, because the next chunk's
-    // upload reuses the blob buffer the evaluation reads.  It skips blobs that failed their own check; a bad point does not matter to it.
-    {
-        CU(cudaEventRecord(s->ev_fork, s->stream));
+    CU(cudaEventRecord(s->ev_fork, s->stream));            // z is known: from here the evaluation may run on the auxiliary stream
+    auto launch_eval = [&]() -> int {
         CU(cudaStreamWaitEvent(s->aux_stream, s->ev_fork, 0));
         cudaStream_t keep = s->stream; s->stream = s->aux_stream;
         int rc = run_eval<false>(s, d_blobs, m, st_blob, z, y);
@@ -1042,7 +1053,22 @@ static int verify_prepare(kb200_setup* s, const uint32_t* d_blobs, const uint32_
         CU(cudaEventRecord(s->ev_eval, s->aux_stream));
         s->eval_pending = true;
         if (!last) { CU(cudaStreamWaitEvent(s->stream, s->ev_eval, 0)); s->eval_pending = false; }
+        return 0;
+    };
+    if (!forked) {
+        // resident data: the decompression runs AFTER the challenge, not beside it -- the serial SHA-256 chains are the critical path
+        // and stretch from 2.4 to 5.6 ms when 8192 decompression threads compete for issue slots on the same SMs.  It is queued BEFORE
+        // the evaluation so that its 128 two-warp CTAs (one 1.9 ms dependent chain per point) start at once and the evaluation's
+        // CTAs fill the SMs around them.
+        CU(cudaMemsetAsync(st_a, 0, m * 4, s->stream));
+        CU(cudaMemsetAsync(st_b, 0, m * 4, s->stream));
+        LAUNCH(s, k_g1_decompress, blocks(2 * m, 64), 64, d_c48, d_p48, n, aff_c, aff_p, st_a, st_b, 0);
     }
+    // The evaluations y are only needed for the scalar s of the record; the scalar multiplications of k_rlc need z and the points.  So
+    // the evaluation (multiplier-bound) goes to the auxiliary stream HERE, beside the decompression and k_rlc (128-step ladders on few warps),
+    // and for the last (or only) chunk of a call run_rlc joins it after k_rlc; an earlier chunk joins at once, because the next chunk's
+    // upload reuses the blob buffer the evaluation reads.  It skips blobs that failed their own check; a bad point does not matter to it.
+    if (int rc = launch_eval()) return rc;      // measured (4096 blobs): 8.45 ms per shard this way, 9.1-9.4 forked after the decompression, 9.7 with no overlap
     TRACE(s, "decompress");
     LAUNCH(s, k_merge_status, blocks(m, 256), 256, st_blob, st_a, st_b, n, d_status);
     std::vector<int32_t> h0, h1, h2;

@@ -44,6 +44,27 @@ static __device__ __noinline__ void g1_dbl(G1& p) {
     fp_sub(s, s, p.x); fp_mul(s, m, s); fp_sub(p.y, s, t);
     fp_mul(p.zz, v, p.zz); fp_mul(p.zzz, w, p.zzz);
 }
+// p = 2^k * p.  Runs of three or more doublings leave XYZZ for Jacobian coordinates, where a doubling on this curve (a = 0) is
+// 2M + 5S (dbl-2009-l) against 9 products in XYZZ: (X, Y, ZZ, ZZZ) -> (X*ZZ, Y*ZZZ, Z = ZZ), back with ZZ = Z^2, ZZZ = Z^3.  E(Fp) has
+// odd order, so Y = 0 never occurs on a finite point; infinity (ZZ = 0) stays Z = 0.
+static __device__ __noinline__ void g1_dbl_k(G1& p, int k) {
+    if (k < 3) { for (int i = 0; i < k; i++) g1_dbl(p); return; }
+    if (g1_is_inf(p)) return;
+    Fp X, Y, Z, A, B, C, D, E, t;
+    fp_mul(X, p.x, p.zz); fp_mul(Y, p.y, p.zzz); Z = p.zz;
+#pragma unroll 1
+    for (int i = 0; i < k; i++) {
+        fp_sqr(A, X); fp_sqr(B, Y); fp_sqr(C, B);
+        fp_add(t, X, B); fp_sqr(t, t); fp_sub(t, t, A); fp_sub(t, t, C); fp_dbl(D, t);
+        fp_dbl(E, A); fp_add(E, E, A);
+        fp_mul(Z, Y, Z); fp_dbl(Z, Z);                     // Z3 = 2 Y1 Z1, before Y is overwritten
+        fp_sqr(t, E); fp_sub(t, t, D); fp_sub(X, t, D);    // X3 = E^2 - 2D
+        fp_sub(t, D, X); fp_mul(t, E, t);
+        fp_dbl(C, C); fp_dbl(C, C); fp_dbl(C, C);
+        fp_sub(Y, t, C);                                   // Y3 = E (D - X3) - 8C
+    }
+    p.x = X; p.y = Y; fp_sqr(p.zz, Z); fp_mul(p.zzz, p.zz, Z);
+}
 // rare paths of the mixed addition, kept out of line so the hot loop stays small
 static __device__ __noinline__ void g1_madd_rare(G1* acc, const Fp* x2, const Fp* y2, bool same_y) {
     if (same_y) { G1 t; g1_dbl_affine(t, *x2, *y2); *acc = t; } else g1_set_inf(*acc);
@@ -171,10 +192,14 @@ template <bool AFFINE>
 static __device__ __noinline__ void g1_mul_bls_x(G1& acc, const Fp& bx, const Fp& by, const G1* bz) {
     const uint64_t X = 0xd201000000010000ull;
     if (AFFINE) { acc.x = bx; acc.y = by; fp_set(acc.zz, c_k.fp_one); fp_set(acc.zzz, c_k.fp_one); } else acc = *bz;
+    // doublings between the set bits below bit 63: 1, 2, 3, 9, 32, and 16 after the last addition
 #pragma unroll 1
-    for (int i = 62; i >= 0; i--) {
-        g1_dbl(acc);
-        if ((X >> i) & 1) { if (AFFINE) g1_madd(acc, bx, by); else g1_add(acc, *bz); }
+    for (int i = 62, run = 0; i >= 0; i--) {
+        run++;
+        if (((X >> i) & 1) || i == 0) {
+            g1_dbl_k(acc, run); run = 0;
+            if ((X >> i) & 1) { if (AFFINE) g1_madd(acc, bx, by); else g1_add(acc, *bz); }
+        }
     }
 }
 // Subgroup membership (blst_p1_affine_in_g1).  With beta the cube root of unity below and phi(x, y) = (beta x, y), G1 is the

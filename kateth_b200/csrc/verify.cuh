@@ -162,9 +162,133 @@ __global__ void __launch_bounds__(RLC_THREADS / 2) k_rlc_s(const Fr* __restrict_
     }
     if (tid == 0) s_partials[blockIdx.x] = sms[0];
 }
+// ---------------------------------------------------------------------------------------------------------
+// The same three sums for LARGE shards as a bucket (Pippenger) multi-scalar multiplication over the batch itself.
+// k_rlc spends one 128-step double-and-add ladder per term: 3 x 2 x n ladders, ~760 M warp instructions at n = 4096 -- as much
+// multiplier work as the barycentric evaluation it runs beside.  Here the 2n terms (P_i, k1_i), (Q_i, k2_i) of a sum are cut into 16
+// byte-wide windows; per (sum, window, slice of 1024 items) one CTA counting-sorts its <= 2048 terms by digit in shared memory, thread d sums
+// the points of bucket d (mixed additions), the CTA forms sum_d d * B_d with a suffix scan + tree (16 levels of full additions), and
+// k_rlc_shift adds the slices of a window and doubles the window sum 8j times.  ~14x fewer group operations than the ladders; what is
+// left on the critical path is the chain of <= 120 doublings no method avoids.  Same group elements, hence the same record bytes.
+// ---------------------------------------------------------------------------------------------------------
+#define RLCB_THREADS 256
+#define RLCB_WINDOWS 16
+#define RLCB_ITEMS 1024                           // items per slice: 2048 terms, 8 per thread
+#define RLCB_PER_THREAD (2 * RLCB_ITEMS / RLCB_THREADS)
+static __device__ __noinline__ void g1_madd_ool(G1& acc, const Fp& x2, const Fp& y2) { g1_madd(acc, x2, y2); }
+
+// dig[(sel * 16 + j) * n + i] = byte j of k1 | byte j of k2 << 8, (k1, k2) = GLV halves of the canonical scalar of item i:
+// sel 0: w_i (sums A and C), sel 1: w_i z_i (sum B).  Items with a non-zero status get zero digits: they contribute nothing.
+__global__ void __launch_bounds__(128) k_rlc_scalars(const Fr* __restrict__ z_canon, int n, uint32_t index_offset, const Fr* __restrict__ r_mont, int raw, int spec,
+                                                     const int32_t* __restrict__ status, uint16_t* __restrict__ dig) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Fr ka, kb; fr_zero(ka); fr_zero(kb);
+    if (status == nullptr || status[i] == 0) {
+        Fr wgt;
+        if (raw) fr_set(wgt, c_k.fr_one);
+        else { const uint32_t gi = index_offset + (uint32_t)i; Fr r = *r_mont; fr_pow_u32(wgt, r, (gi == 0 && !spec) ? 1u : gi); }
+        fr_from_mont(ka, wgt);
+        Fr z = z_canon[i]; fr_mul(kb, z, wgt);
+    }
+    Fr a1, a2, b1, b2;
+    fr_glv_split(a1, a2, ka); fr_glv_split(b1, b2, kb);
+#pragma unroll
+    for (int j = 0; j < RLCB_WINDOWS; j++) {
+        const int sh = 8 * (j & 3), l = j >> 2;
+        dig[(size_t)j * n + i] = (uint16_t)(((a1.l[l] >> sh) & 0xffu) | (((a2.l[l] >> sh) & 0xffu) << 8));
+        dig[(size_t)(RLCB_WINDOWS + j) * n + i] = (uint16_t)(((b1.l[l] >> sh) & 0xffu) | (((b2.l[l] >> sh) & 0xffu) << 8));
+    }
+}
+
+// grid (16 * nslices, 3): CTA (window j, slice, which) -> wsum[(which * 16 + j) * nslices + slice] = sum over the slice's terms of digit * point
+__global__ void __launch_bounds__(RLCB_THREADS, 2) k_rlc_bucket(const G1Affine* __restrict__ proofs, const G1Affine* __restrict__ comms,
+                                                             const uint16_t* __restrict__ dig, int n, int nslices, G1* __restrict__ wsum) {
+    __shared__ __align__(16) unsigned char raw_sm[RLCB_THREADS * sizeof(G1)];       // 48 KiB: sort arrays first, bucket sums afterwards
+    G1* bkt = reinterpret_cast<G1*>(raw_sm);
+    uint32_t* cnt = reinterpret_cast<uint32_t*>(raw_sm);
+    uint32_t* cur = cnt + RLCB_THREADS;
+    uint16_t* sorted = reinterpret_cast<uint16_t*>(cur + RLCB_THREADS);
+    const int tid = threadIdx.x, which = blockIdx.y, j = blockIdx.x % RLCB_WINDOWS, slice = blockIdx.x / RLCB_WINDOWS;
+    const int i0 = slice * RLCB_ITEMS, i1 = (n < i0 + RLCB_ITEMS) ? n : i0 + RLCB_ITEMS, T = 2 * (i1 - i0);
+    const uint16_t* dg = dig + (size_t)((which == 1 ? RLCB_WINDOWS : 0) + j) * n;
+    const G1Affine* pts = (which == 2) ? comms : proofs;
+    cnt[tid] = 0;
+    __syncthreads();
+    uint32_t myd[RLCB_PER_THREAD];
+#pragma unroll
+    for (int k = 0; k < RLCB_PER_THREAD; k++) {
+        const int t = tid + RLCB_THREADS * k;
+        uint32_t d = 0;
+        if (t < T) d = ((uint32_t)dg[i0 + (t >> 1)] >> (8 * (t & 1))) & 0xffu;
+        myd[k] = d;
+        if (d) atomicAdd(&cnt[d], 1u);
+    }
+    __syncthreads();
+    uint32_t off = 0;
+    for (int e = 1; e < tid; e++) off += cnt[e];
+    const uint32_t mycnt = cnt[tid];              // bucket 0 stays empty
+    cur[tid] = off;
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < RLCB_PER_THREAD; k++)
+        if (myd[k]) { const uint32_t pos = atomicAdd(&cur[myd[k]], 1u); sorted[pos] = (uint16_t)(tid + RLCB_THREADS * k); }
+    __syncthreads();
+    G1 acc; g1_set_inf(acc);
+#pragma unroll 1
+    for (uint32_t q = off; q < off + mycnt; q++) {
+        const uint32_t t = sorted[q];
+        G1Affine pt = pts[i0 + (int)(t >> 1)];
+        if (g1a_is_inf(pt)) continue;
+        if (t & 1) { Fp b; fp_set(b, c_k.fp_beta); fp_mul(pt.x, pt.x, b); fp_neg(pt.y, pt.y); }        // Q = (beta x, -y)
+        g1_madd_ool(acc, pt.x, pt.y);
+    }
+    __syncthreads();                               // the sort arrays are dead: their bytes become the bucket sums
+    bkt[tid] = acc;
+    __syncthreads();
+    // suffix sums S_d = sum_{e >= d} B_e (Hillis-Steele), then sum_{d >= 1} S_d = sum_d d * B_d
+#pragma unroll 1
+    for (int st = 1; st < RLCB_THREADS; st <<= 1) {
+        const bool has = tid + st < RLCB_THREADS;
+        G1 other;
+        if (has) other = bkt[tid + st];
+        __syncthreads();
+        if (has) { g1_add(acc, other); bkt[tid] = acc; }
+        __syncthreads();
+    }
+    if (tid == 0) { g1_set_inf(acc); bkt[0] = acc; }
+    __syncthreads();
+#pragma unroll 1
+    for (int stride = RLCB_THREADS / 2; stride >= 1; stride >>= 1) {
+        if (tid < stride) { G1 other = bkt[tid + stride]; g1_add(acc, other); bkt[tid] = acc; }
+        __syncthreads();
+    }
+    if (tid == 0) wsum[(size_t)(which * RLCB_WINDOWS + j) * nslices + slice] = acc;
+}
+// grid (16, 3), one warp: window sum = sum of its slices, shifted: partials[which * 16 + j] = 2^(8j) * W_j  (k_rlc_finish adds the 16)
+__global__ void __launch_bounds__(32) k_rlc_shift(const G1* __restrict__ wsum, int nslices, G1* __restrict__ partials) {
+    __shared__ G1 sm[16];
+    const int lane = threadIdx.x, j = blockIdx.x, which = blockIdx.y;
+    G1 acc; g1_set_inf(acc);
+    for (int k = lane; k < nslices; k += 32) { G1 t = wsum[(size_t)(which * RLCB_WINDOWS + j) * nslices + k]; g1_add(acc, t); }
+#pragma unroll 1
+    for (int stride = 16; stride >= 1; stride >>= 1) {
+        if (stride < nslices) {                    // uniform: lanes >= nslices hold infinity
+            if (lane >= stride && lane < 2 * stride) sm[lane - stride] = acc;
+            __syncwarp();
+            if (lane < stride) g1_add(acc, sm[lane]);
+            __syncwarp();
+        }
+    }
+    if (lane == 0) {
+        g1_dbl_k(acc, 8 * j);
+        partials[which * RLCB_WINDOWS + j] = acc;
+    }
+}
+
 // grid 3 CTAs of RLC_FIN_THREADS: CTA `which` reduces its row of partials, normalises, writes the record field.
 #define RLC_FIN_THREADS 128
-__global__ void __launch_bounds__(RLC_FIN_THREADS) k_rlc_finish(const G1* __restrict__ partials, const Fr* __restrict__ s_partials, int nparts,
+__global__ void __launch_bounds__(RLC_FIN_THREADS) k_rlc_finish(const G1* __restrict__ partials, int nparts, const Fr* __restrict__ s_partials, int nparts_s,
                                                                  RlcRecord* __restrict__ rec) {
     __shared__ G1 sm[RLC_FIN_THREADS / 2];
     __shared__ Fr sms[RLC_FIN_THREADS];
@@ -184,7 +308,7 @@ __global__ void __launch_bounds__(RLC_FIN_THREADS) k_rlc_finish(const G1* __rest
     }
     if (which == 0) {
         Fr s; fr_zero(s);
-        for (int k = tid; k < nparts; k += RLC_FIN_THREADS) { Fr t = s_partials[k]; fr_add(s, s, t); }
+        for (int k = tid; k < nparts_s; k += RLC_FIN_THREADS) { Fr t = s_partials[k]; fr_add(s, s, t); }
         sms[tid] = s;
         __syncthreads();
 #pragma unroll 1

@@ -42,7 +42,7 @@ SYMBOLS = [
     "kb200_blob_to_commitment", "kb200_blob_to_commitment_device", "kb200_blob_to_commitment_device_noalloc", "kb200_check_blobs", "kb200_compute_blob_proof", "kb200_compute_blob_proof_device",
     "kb200_compute_proof", "kb200_compute_proof_device", "kb200_verify_proof", "kb200_verify_proof_batch", "kb200_verify_proof_many", "kb200_verify_blob_proof",
     "kb200_verify_blob_proof_batch", "kb200_verify_blob_proof_batch_device", "kb200_verify_blob_proof_batch_partial_device",
-    "kb200_verify_blob_proof_batch_partial", "kb200_commit_prove_verify_partial", "kb200_verify_proof_batch_partial_device", "kb200_verify_proof_batch_partial", "kb200_verify_batch_finish_device", "kb200_set_profiling", "kb200_set_msm_mode", "kb200_set_batch_challenge", "kb200_get_msm_profile", "kb200_last_pairing_operands", "kb200_get_info", "kb200_test_fp_mul", "kb200_test_fr_mul",
+    "kb200_verify_blob_proof_batch_partial", "kb200_commit_prove_verify_partial", "kb200_verify_proof_batch_partial_device", "kb200_verify_proof_batch_partial", "kb200_verify_batch_finish_device", "kb200_set_profiling", "kb200_set_msm_mode", "kb200_set_rlc_mode", "kb200_set_batch_challenge", "kb200_get_msm_profile", "kb200_last_pairing_operands", "kb200_get_info", "kb200_test_fp_mul", "kb200_test_fr_mul",
     "kb200_test_g1_decompress", "kb200_test_mac_peak", "kb200_test_host_pairing",
     "kb200_group_create_json", "kb200_group_unique_id", "kb200_group_create_rank", "kb200_group_free", "kb200_group_info", "kb200_group_replica",
     "kb200_group_blob_to_commitment", "kb200_group_compute_blob_proof", "kb200_group_compute_proof", "kb200_group_verify_blob_proof_batch",
@@ -289,6 +289,10 @@ class Setup:
         """One shard of a sharded batch of (proof, commitment, z, y) tuples (host bytes); the record goes to device memory."""
         return lib().kb200_verify_proof_batch_partial(self._h, proofs, comm48, z32, y32, C.c_size_t(n_local), C.c_size_t(index_offset), C.c_size_t(n_total),
                                                       _vp(d_record), None)
+
+    def set_rlc_mode(self, mode):
+        """0 = automatic, 1 = ladders (k_rlc), 2 = bucket method (k_rlc_bucket): same records."""
+        _check(lib().kb200_set_rlc_mode(self._h, int(mode)))
 
     def set_msm_mode(self, mode):
         """0 = automatic, 1 = XYZZ accumulation (k_msm), 2 = batch-affine summation (k_msm_ba); same bytes either way."""

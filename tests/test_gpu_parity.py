@@ -795,6 +795,65 @@ def test_sharded_point_batches_equal_single_call(engine_setup):
     assert run(pr, comm, zs, bytes(ny)) == ([7, 0, 0], 7, 0)
 
 
+def test_bucket_sums_equal_ladder_sums(engine_setup):
+    """The two forms of a shard's sums (one 128-step ladder per term, k_rlc; bucket method over the batch, k_rlc_bucket) give the same
+    336 record bytes: blob batches over 1 and 2 slices with a partial slice, items repeated hundreds of times (a bucket adds a point to
+    itself: the doubling path of the mixed addition), points at infinity (the zero blob), an invalid item (left out of the sums, error in
+    the record), a wrong proof (verdict false), a point batch (weights from z), and the single-proof form (weights 1)."""
+    import torch
+    import kateth_b200 as K
+    s = engine_setup
+    RB = K.RECORD_BYTES
+    base = [rand_blob(17000 + i) for i in range(5)] + [bytes(131072)]
+    try:
+        for n in (700, 1500):
+            cat = b"".join(base[(i * i) % 6] for i in range(n))
+            comm, _ = s.blob_to_commitment_many(cat, n)
+            pr, st = s.blob_proof_many(cat, comm, n)
+            assert st == [0] * n
+            d_b = torch.frombuffer(bytearray(cat), dtype=torch.uint8).cuda()
+            rec = torch.zeros(2 * RB, dtype=torch.uint8, device="cuda"); d_st = torch.zeros(n, dtype=torch.int32, device="cuda")
+
+            def records(comm_, pr_, off=3, total=n + 5):
+                d_c = torch.frombuffer(bytearray(comm_), dtype=torch.uint8).cuda(); d_p = torch.frombuffer(bytearray(pr_), dtype=torch.uint8).cuda()
+                out = []
+                for g, mode in enumerate((1, 2)):
+                    s.set_rlc_mode(mode)
+                    out.append(s.verify_partial_device(d_b.data_ptr(), d_c.data_ptr(), d_p.data_ptr(), n, off, total, rec.data_ptr() + g * RB, d_st.data_ptr()))
+                r = bytes(rec.cpu().numpy())
+                return out, r[:RB], r[RB:]
+
+            rcs, ladder, bucket = records(comm, pr)
+            assert rcs == [0, 0] and ladder == bucket and any(ladder[:288])
+            rcs, ladder, bucket = records(comm, pr, 0, n)                      # the whole batch: index 0 takes the pow(r, 0) == r weight
+            assert rcs == [0, 0] and ladder == bucket
+            assert s.verify_finish_device(rec.data_ptr() + RB, 1) is True
+            swapped = bytearray(pr); swapped[0:48], swapped[48:96] = pr[48:96], pr[0:48]
+            rcs, ladder, bucket = records(comm, bytes(swapped), 0, n)
+            assert rcs == [0, 0] and ladder == bucket
+            assert s.verify_finish_device(rec.data_ptr() + RB, 1) is False
+            badc = bytearray(comm); badc[48 * 611:48 * 612] = RV.INVALID_G1[3]
+            rcs, ladder, bucket = records(bytes(badc), pr)
+            assert rcs[0] == rcs[1] != 0 and ladder == bucket
+        # point batches (Setup::verify_proof_batch) and the single check
+        n = 600
+        cat = b"".join(base[i % 6] for i in range(n))
+        comm, _ = s.blob_to_commitment_many(cat, n)
+        zs = b"".join(RV.fe(int.from_bytes(hashlib.sha256(b"bk%d" % i).digest(), "big")) for i in range(n))
+        pr, ys, st = s.proof_many(cat, zs, n)
+        assert st == [0] * n
+        ops = []
+        for mode in (1, 2):
+            s.set_rlc_mode(mode)
+            assert s.verify_proof_batch(pr, comm, zs, ys, n) is True
+            ops.append(s.last_pairing_operands())
+            assert s.verify_proof(pr[:48], comm[:48], zs[:32], ys[:32]) is True
+            ops.append(s.last_pairing_operands())
+        assert ops[0] == ops[2] and ops[1] == ops[3]
+    finally:
+        s.set_rlc_mode(0)
+
+
 # ---------------------------------------------------------------- loader extras (SURVEY 8f rank 4)
 def test_g1_monomial_cross_check(engine_setup, tmp_path):
     """Files that also carry the monomial basis are cross-checked: X^k over the domain, in blob order, must commit to [tau^k]G1 for all
