@@ -825,7 +825,7 @@ extern "C" int kb200_compute_blob_proof_device(kb200_setup* s, const void* d_blo
     s->launches++;
     CU(cudaEventRecord(s->ev_join, s->aux_stream));
     LAUNCH(s, k_blob_check, blocks(n * KB_N, 256), 256, (const uint32_t*)d_blobs, (int)n, s->st_blob.as<int32_t>());
-    if (!s->z_ready) LAUNCH(s, k_challenge_w2, blocks(n, 32), 64, (const uint32_t*)d_blobs, (const uint32_t*)d_comm48, (int)n, s->st_blob.as<int32_t>(), (uint32_t*)nullptr, s->z.as<Fr>(), 0, 2050);
+    if (!s->z_ready) LAUNCH(s, k_challenge_w2, blocks(n, CH2_THREADS / 2), CH2_THREADS, (const uint32_t*)d_blobs, (const uint32_t*)d_comm48, (int)n, s->st_blob.as<int32_t>(), (uint32_t*)nullptr, s->z.as<Fr>(), 0, 2050);
     s->z_ready = false;
     CU(cudaStreamWaitEvent(s->stream, s->ev_join, 0));
     LAUNCH(s, k_merge_status, blocks(n, 256), 256, s->st_blob.as<int32_t>(), s->st_a.as<int32_t>(), (const int32_t*)nullptr, (int)n, d_status);
@@ -1026,23 +1026,25 @@ static int verify_prepare(kb200_setup* s, const uint32_t* d_blobs, const uint32_
     const int n = (int)m;
     CU(cudaMemsetAsync(st_blob, 0, m * 4, s->stream));
     TRACE(s, "start");
-    const bool forked = s->fork_recorded;       // a host-buffer caller marked the fork point before the blob upload it queued
+    if (!s->fork_recorded) CU(cudaEventRecord(s->ev_fork, s->stream));      // a host-buffer caller marked the fork point before the blob upload it queued; resident data: fork here
     s->fork_recorded = false;
-    if (forked) {
-        // host-buffer call: the point decompression (a 380-step square-and-multiply chain per point) runs on the auxiliary stream UNDER
-        // the upload of the blobs; the challenges came with the upload (z_ready) or follow it
+    {
+        // The point decompression (one ~1500-product dependent chain per point, 64 CTAs per 4096 blobs) runs on the auxiliary stream
+        // beside the challenges (64 CTAs of SHA-256 chains) -- for a host-buffer call also under the upload of the blobs.  The two
+        // kernels are shaped so that they land on DIFFERENT SMs: sharing an SM stretches the SHA chains from 2.4 to 5 ms (measured with
+        // 128 + 128 smaller CTAs), on SMs of their own neither slows the other.
         CU(cudaStreamWaitEvent(s->aux_stream, s->ev_fork, 0));
         CU(cudaMemsetAsync(st_a, 0, m * 4, s->aux_stream));
         CU(cudaMemsetAsync(st_b, 0, m * 4, s->aux_stream));
-        k_g1_decompress<<<blocks(2 * m, 64), 64, 0, s->aux_stream>>>(d_c48, d_p48, n, aff_c, aff_p, st_a, st_b, 0);
+        k_g1_decompress<<<blocks(2 * m, 128), 128, 0, s->aux_stream>>>(d_c48, d_p48, n, aff_c, aff_p, st_a, st_b, 0);
         s->launches++;
         CU(cudaEventRecord(s->ev_join, s->aux_stream));
     }
     LAUNCH(s, k_blob_check, blocks(m * KB_N, 256), 256, d_blobs, n, st_blob);
-    if (!s->z_ready) LAUNCH(s, k_challenge_w2, blocks(m, 32), 64, d_blobs, d_c48, n, st_blob, (uint32_t*)nullptr, z, 0, 2050);
+    if (!s->z_ready) LAUNCH(s, k_challenge_w2, blocks(m, CH2_THREADS / 2), CH2_THREADS, d_blobs, d_c48, n, st_blob, (uint32_t*)nullptr, z, 0, 2050);
     s->z_ready = false;
     TRACE(s, "blob check + challenge");
-    if (forked) CU(cudaStreamWaitEvent(s->stream, s->ev_join, 0));
+    CU(cudaStreamWaitEvent(s->stream, s->ev_join, 0));
     CU(cudaEventRecord(s->ev_fork, s->stream));            // z is known: from here the evaluation may run on the auxiliary stream
     auto launch_eval = [&]() -> int {
         CU(cudaStreamWaitEvent(s->aux_stream, s->ev_fork, 0));
@@ -1055,15 +1057,6 @@ static int verify_prepare(kb200_setup* s, const uint32_t* d_blobs, const uint32_
         if (!last) { CU(cudaStreamWaitEvent(s->stream, s->ev_eval, 0)); s->eval_pending = false; }
         return 0;
     };
-    if (!forked) {
-        // resident data: the decompression runs AFTER the challenge, not beside it -- the serial SHA-256 chains are the critical path
-        // and stretch from 2.4 to 5.6 ms when 8192 decompression threads compete for issue slots on the same SMs.  It is queued BEFORE
-        // the evaluation so that its 128 two-warp CTAs (one 1.9 ms dependent chain per point) start at once and the evaluation's
-        // CTAs fill the SMs around them.
-        CU(cudaMemsetAsync(st_a, 0, m * 4, s->stream));
-        CU(cudaMemsetAsync(st_b, 0, m * 4, s->stream));
-        LAUNCH(s, k_g1_decompress, blocks(2 * m, 64), 64, d_c48, d_p48, n, aff_c, aff_p, st_a, st_b, 0);
-    }
     // The evaluations y are only needed for the scalar s of the record; the scalar multiplications of k_rlc need z and the points.  So
     // the evaluation (multiplier-bound) goes to the auxiliary stream HERE, beside the decompression and k_rlc (128-step ladders on few warps),
     // and for the last (or only) chunk of a call run_rlc joins it after k_rlc; an earlier chunk joins at once, because the next chunk's
@@ -1179,7 +1172,7 @@ static int h2d_blobs_hashed(kb200_setup* s, const uint8_t* blobs, size_t n, cons
     for (int j = 0; j < NCOL; j++) {
         CU(cudaStreamWaitEvent(s->stream, s->ev_col[j], 0));
         const int blk0 = (int)(j * W / 64), blk1 = (j == NCOL - 1) ? 2050 : (int)((j + 1) * W / 64);
-        LAUNCH(s, k_challenge_w2, blocks(n, 32), 64, s->blobs.as<uint32_t>(), d_c48, (int)n, (const int32_t*)nullptr, s->sha_state.as<uint32_t>(), d_z, blk0, blk1);
+        LAUNCH(s, k_challenge_w2, blocks(n, CH2_THREADS / 2), CH2_THREADS, s->blobs.as<uint32_t>(), d_c48, (int)n, (const int32_t*)nullptr, s->sha_state.as<uint32_t>(), d_z, blk0, blk1);
     }
     s->z_ready = true;
     return 0;

@@ -27,22 +27,22 @@ __device__ __forceinline__ void g1_from_affine(G1& r, const G1Affine& p) {
 // r = 2*(x, y) for an affine, finite point
 static __device__ __noinline__ void g1_dbl_affine(G1& r, const Fp& x, const Fp& y) {
     Fp u, v, w, s, m, t;
-    fp_dbl(u, y); fp_sqr(v, u); fp_mul(w, u, v); fp_mul(s, x, v);
-    fp_sqr(m, x); fp_dbl(t, m); fp_add(m, m, t);
-    fp_sqr(r.x, m); fp_sub(r.x, r.x, s); fp_sub(r.x, r.x, s);
-    fp_sub(t, s, r.x); fp_mul(t, m, t); fp_mul(u, w, y); fp_sub(r.y, t, u);
+    fp_dbl(u, y); FPS(v, u); FPM(w, u, v); FPM(s, x, v);
+    FPS(m, x); fp_dbl(t, m); fp_add(m, m, t);
+    FPS(r.x, m); fp_sub(r.x, r.x, s); fp_sub(r.x, r.x, s);
+    fp_sub(t, s, r.x); FPM(t, m, t); FPM(u, w, y); fp_sub(r.y, t, u);
     r.zz = v; r.zzz = w;
 }
 // p = 2*p
 static __device__ __noinline__ void g1_dbl(G1& p) {
     if (g1_is_inf(p)) return;
     Fp u, v, w, s, m, t;
-    fp_dbl(u, p.y); fp_sqr(v, u); fp_mul(w, u, v); fp_mul(s, p.x, v);
-    fp_sqr(m, p.x); fp_dbl(t, m); fp_add(m, m, t);
-    fp_mul(t, w, p.y);                      // W*Y1 before Y is overwritten
-    fp_sqr(p.x, m); fp_sub(p.x, p.x, s); fp_sub(p.x, p.x, s);
-    fp_sub(s, s, p.x); fp_mul(s, m, s); fp_sub(p.y, s, t);
-    fp_mul(p.zz, v, p.zz); fp_mul(p.zzz, w, p.zzz);
+    fp_dbl(u, p.y); FPS(v, u); FPM(w, u, v); FPM(s, p.x, v);
+    FPS(m, p.x); fp_dbl(t, m); fp_add(m, m, t);
+    FPM(t, w, p.y);                      // W*Y1 before Y is overwritten
+    FPS(p.x, m); fp_sub(p.x, p.x, s); fp_sub(p.x, p.x, s);
+    fp_sub(s, s, p.x); FPM(s, m, s); fp_sub(p.y, s, t);
+    FPM(p.zz, v, p.zz); FPM(p.zzz, w, p.zzz);
 }
 // p = 2^k * p.  Runs of three or more doublings leave XYZZ for Jacobian coordinates, where a doubling on this curve (a = 0) is
 // 2M + 5S (dbl-2009-l) against 9 products in XYZZ: (X, Y, ZZ, ZZZ) -> (X*ZZ, Y*ZZZ, Z = ZZ), back with ZZ = Z^2, ZZZ = Z^3.  E(Fp) has
@@ -51,19 +51,19 @@ static __device__ __noinline__ void g1_dbl_k(G1& p, int k) {
     if (k < 3) { for (int i = 0; i < k; i++) g1_dbl(p); return; }
     if (g1_is_inf(p)) return;
     Fp X, Y, Z, A, B, C, D, E, t;
-    fp_mul(X, p.x, p.zz); fp_mul(Y, p.y, p.zzz); Z = p.zz;
+    FPM(X, p.x, p.zz); FPM(Y, p.y, p.zzz); Z = p.zz;
 #pragma unroll 1
     for (int i = 0; i < k; i++) {
-        fp_sqr(A, X); fp_sqr(B, Y); fp_sqr(C, B);
-        fp_add(t, X, B); fp_sqr(t, t); fp_sub(t, t, A); fp_sub(t, t, C); fp_dbl(D, t);
+        FPS(A, X); FPS(B, Y); FPS(C, B);
+        fp_add(t, X, B); FPS(t, t); fp_sub(t, t, A); fp_sub(t, t, C); fp_dbl(D, t);
         fp_dbl(E, A); fp_add(E, E, A);
-        fp_mul(Z, Y, Z); fp_dbl(Z, Z);                     // Z3 = 2 Y1 Z1, before Y is overwritten
-        fp_sqr(t, E); fp_sub(t, t, D); fp_sub(X, t, D);    // X3 = E^2 - 2D
-        fp_sub(t, D, X); fp_mul(t, E, t);
+        FPM(Z, Y, Z); fp_dbl(Z, Z);                     // Z3 = 2 Y1 Z1, before Y is overwritten
+        FPS(t, E); fp_sub(t, t, D); fp_sub(X, t, D);    // X3 = E^2 - 2D
+        fp_sub(t, D, X); FPM(t, E, t);
         fp_dbl(C, C); fp_dbl(C, C); fp_dbl(C, C);
         fp_sub(Y, t, C);                                   // Y3 = E (D - X3) - 8C
     }
-    p.x = X; p.y = Y; fp_sqr(p.zz, Z); fp_mul(p.zzz, p.zz, Z);
+    p.x = X; p.y = Y; FPS(p.zz, Z); FPM(p.zzz, p.zz, Z);
 }
 // rare paths of the mixed addition, kept out of line so the hot loop stays small
 static __device__ __noinline__ void g1_madd_rare(G1* acc, const Fp* x2, const Fp* y2, bool same_y) {
@@ -81,6 +81,18 @@ __device__ __forceinline__ void g1_madd(G1& acc, const Fp& x2, const Fp& y2) {
     fp_sub(q, q, acc.x); fp_mul(q, r, q); fp_mul(t, acc.y, ppp); fp_sub(acc.y, q, t);
     fp_mul(acc.zz, acc.zz, pp); fp_mul(acc.zzz, acc.zzz, ppp);
 }
+// the same mixed addition out of line on the shared product (callers outside the MSM hot loop)
+static __device__ __noinline__ void g1_madd_c(G1& acc, const Fp& x2, const Fp& y2) {
+    if (g1_is_inf(acc)) { acc.x = x2; acc.y = y2; fp_set(acc.zz, c_k.fp_one); fp_set(acc.zzz, c_k.fp_one); return; }
+    Fp p, r, pp, ppp, q, t;
+    FPM(p, x2, acc.zz); fp_sub(p, p, acc.x);
+    FPM(r, y2, acc.zzz); fp_sub(r, r, acc.y);
+    if (fp_is_zero(p)) { G1 tmp = acc; g1_madd_rare(&tmp, &x2, &y2, fp_is_zero(r)); acc = tmp; return; }
+    FPS(pp, p); FPM(ppp, p, pp); FPM(q, acc.x, pp);
+    FPS(t, r); fp_sub(t, t, ppp); fp_sub(t, t, q); fp_sub(acc.x, t, q);
+    fp_sub(q, q, acc.x); FPM(q, r, q); FPM(t, acc.y, ppp); fp_sub(acc.y, q, t);
+    FPM(acc.zz, acc.zz, pp); FPM(acc.zzz, acc.zzz, ppp);
+}
 // acc += pt (affine, possibly the (0,0) infinity sentinel), optionally negated
 __device__ __forceinline__ void g1_madd_signed(G1& acc, const G1Affine& pt, bool neg) {
     if (g1a_is_inf(pt)) return;
@@ -92,26 +104,26 @@ static __device__ __noinline__ void g1_add(G1& acc, const G1& b) {
     if (g1_is_inf(b)) return;
     if (g1_is_inf(acc)) { acc = b; return; }
     Fp u1, u2, s1, s2, p, r, pp, ppp, q, t;
-    fp_mul(u1, acc.x, b.zz); fp_mul(u2, b.x, acc.zz);
-    fp_mul(s1, acc.y, b.zzz); fp_mul(s2, b.y, acc.zzz);
+    FPM(u1, acc.x, b.zz); FPM(u2, b.x, acc.zz);
+    FPM(s1, acc.y, b.zzz); FPM(s2, b.y, acc.zzz);
     fp_sub(p, u2, u1); fp_sub(r, s2, s1);
     if (fp_is_zero(p)) {
         if (fp_is_zero(r)) g1_dbl(acc); else g1_set_inf(acc);
         return;
     }
-    fp_sqr(pp, p); fp_mul(ppp, p, pp); fp_mul(q, u1, pp);
-    fp_sqr(t, r); fp_sub(t, t, ppp); fp_sub(t, t, q); fp_sub(acc.x, t, q);
-    fp_sub(q, q, acc.x); fp_mul(q, r, q); fp_mul(t, s1, ppp); fp_sub(acc.y, q, t);
-    fp_mul(acc.zz, acc.zz, b.zz); fp_mul(acc.zz, acc.zz, pp);
-    fp_mul(acc.zzz, acc.zzz, b.zzz); fp_mul(acc.zzz, acc.zzz, ppp);
+    FPS(pp, p); FPM(ppp, p, pp); FPM(q, u1, pp);
+    FPS(t, r); fp_sub(t, t, ppp); fp_sub(t, t, q); fp_sub(acc.x, t, q);
+    fp_sub(q, q, acc.x); FPM(q, r, q); FPM(t, s1, ppp); fp_sub(acc.y, q, t);
+    FPM(acc.zz, acc.zz, b.zz); FPM(acc.zz, acc.zz, pp);
+    FPM(acc.zzz, acc.zzz, b.zzz); FPM(acc.zzz, acc.zzz, ppp);
 }
 // XYZZ -> affine (one field inversion)
 static __device__ __noinline__ void g1_to_affine(G1Affine& r, const G1& p) {
     if (g1_is_inf(p)) { fp_zero(r.x); fp_zero(r.y); return; }
     Fp i3, zi, i2;
     fp_inv_bgcd(i3, p.zzz);                  // Z^-3 (branchless binary GCD, fp_bgcd.cuh; same value as a^(p-2))
-    fp_mul(zi, p.zz, i3); fp_sqr(i2, zi);    // Z^-1, Z^-2
-    fp_mul(r.x, p.x, i2); fp_mul(r.y, p.y, i3);
+    FPM(zi, p.zz, i3); FPS(i2, zi);    // Z^-1, Z^-2
+    FPM(r.x, p.x, i2); FPM(r.y, p.y, i3);
 }
 // r = [k]P for a plain 255-bit scalar (little-endian limbs); MSB-first double-and-add  (blst_p1_mult(..., 255))
 static __device__ __noinline__ void g1_mul(G1& r, const G1Affine& p, const Fr& k, int nbits = 255) {
@@ -177,9 +189,9 @@ static __device__ __noinline__ int g1_uncompress(G1Affine& r, const uint32_t* in
     if (fp_plain_geq_p(x)) return KB_G1_INVALID_ENCODING;
     Fp xm, y2, y, t, b;
     fp_to_mont(xm, x);
-    fp_sqr(y2, xm); fp_mul(y2, y2, xm); fp_set(b, c_k.fp_b4); fp_add(y2, y2, b);
+    FPS(y2, xm); FPM(y2, y2, xm); fp_set(b, c_k.fp_b4); fp_add(y2, y2, b);
     fp_pow_c(y, y2, c_k.fp_sqrt_exp);
-    fp_sqr(t, y);
+    FPS(t, y);
     if (!fp_eq(t, y2)) return KB_G1_NOT_ON_CURVE;
     fp_from_mont(t, y);
     bool want = (w0 & 0x20000000u) != 0;
@@ -198,7 +210,7 @@ static __device__ __noinline__ void g1_mul_bls_x(G1& acc, const Fp& bx, const Fp
         run++;
         if (((X >> i) & 1) || i == 0) {
             g1_dbl_k(acc, run); run = 0;
-            if ((X >> i) & 1) { if (AFFINE) g1_madd(acc, bx, by); else g1_add(acc, *bz); }
+            if ((X >> i) & 1) { if (AFFINE) g1_madd_c(acc, bx, by); else g1_add(acc, *bz); }
         }
     }
 }
@@ -216,9 +228,9 @@ static __device__ __noinline__ bool g1_in_subgroup(const G1Affine& p) {
     if (g1_is_inf(t2)) return false;
     // phi(P) == -t2  <=>  beta*x*ZZ == X  and  y*ZZZ == -Y
     Fp bx, l, ry;
-    fp_set(bx, c_k.fp_beta); fp_mul(bx, bx, p.x); fp_mul(l, bx, t2.zz);
+    fp_set(bx, c_k.fp_beta); FPM(bx, bx, p.x); FPM(l, bx, t2.zz);
     if (!fp_eq(l, t2.x)) return false;
-    fp_mul(l, p.y, t2.zzz); fp_neg(ry, t2.y);
+    FPM(l, p.y, t2.zzz); fp_neg(ry, t2.y);
     return fp_eq(l, ry);
 }
 // the definition, kept for the unit test that pins the fast test: [r]P == infinity

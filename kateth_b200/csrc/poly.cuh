@@ -220,11 +220,15 @@ __device__ __forceinline__ void ch2_block_words(uint32_t (&w)[16], int k, const 
         w[15] = 131152u * 8u;
     }
 }
-__global__ void __launch_bounds__(64) k_challenge_w2(const uint32_t* __restrict__ blobs, const uint32_t* __restrict__ comm48, int n, const int32_t* __restrict__ status,
+#define CH2_THREADS 128  // two producer/consumer pairs per CTA: 4096 blobs occupy 64 SMs, so that the point decompression of a batch check
+                         // (64 CTAs of its own) finds SMs to itself -- sharing an SM stretches the SHA chains from 2.4 to 5 ms
+__global__ void __launch_bounds__(CH2_THREADS) k_challenge_w2(const uint32_t* __restrict__ blobs, const uint32_t* __restrict__ comm48, int n, const int32_t* __restrict__ status,
                                                      uint32_t* __restrict__ state, Fr* __restrict__ z_out, int blk0, int blk1) {
-    __shared__ uint32_t kw[2][64][32];
-    const int lane = threadIdx.x & 31, role = threadIdx.x >> 5;
-    const int b = blockIdx.x * 32 + lane, bc = b < n ? b : n - 1;          // lanes past the end hash the last blob again and write nothing
+    __shared__ uint32_t kw_all[CH2_THREADS / 64][2][64][32];
+    const int lane = threadIdx.x & 31, role = (threadIdx.x >> 5) & 1, pair = threadIdx.x >> 6;
+    uint32_t (*kw)[64][32] = kw_all[pair];
+    const int bar0 = 4 * pair;                                               // named barriers of this pair
+    const int b = (blockIdx.x * (CH2_THREADS / 64) + pair) * 32 + lane, bc = b < n ? b : n - 1;          // lanes past the end hash the last blob again and write nothing
     const uint4* bp = reinterpret_cast<const uint4*>(blobs + (size_t)bc * (KB_N * 8));
     const uint32_t* cp = comm48 + (size_t)bc * 12;
     if (role == 1) {
@@ -234,7 +238,7 @@ __global__ void __launch_bounds__(64) k_challenge_w2(const uint32_t* __restrict_
             const int j = (k - blk0) & 1;
             uint32_t w[16];
             ch2_block_words(w, k, bp, cp);
-            if (k - blk0 >= 2) ch2_bar_sync(CH2_EMPTY + j);
+            if (k - blk0 >= 2) ch2_bar_sync(bar0 + CH2_EMPTY + j);
 #pragma unroll
             for (int i = 0; i < 64; i++) {
                 if (i >= 16) {
@@ -245,7 +249,7 @@ __global__ void __launch_bounds__(64) k_challenge_w2(const uint32_t* __restrict_
                 }
                 kw[j][i][lane] = w[i & 15] + c_sha_k[i];
             }
-            ch2_bar_arrive(CH2_FULL + j);
+            ch2_bar_arrive(bar0 + CH2_FULL + j);
         }
         return;
     }
@@ -259,11 +263,11 @@ __global__ void __launch_bounds__(64) k_challenge_w2(const uint32_t* __restrict_
 #pragma unroll 1
     for (int k = blk0; k < blk1; k++) {
         const int j = (k - blk0) & 1;
-        ch2_bar_sync(CH2_FULL + j);
+        ch2_bar_sync(bar0 + CH2_FULL + j);
         uint32_t x[64];
 #pragma unroll
         for (int i = 0; i < 64; i++) x[i] = kw[j][i][lane];
-        if (k + 2 < blk1) ch2_bar_arrive(CH2_EMPTY + j);
+        if (k + 2 < blk1) ch2_bar_arrive(bar0 + CH2_EMPTY + j);
         uint32_t a = h[0], bb = h[1], c = h[2], d = h[3], e = h[4], f = h[5], g = h[6], hh = h[7];
 #pragma unroll
         for (int i = 0; i < 64; i++) {

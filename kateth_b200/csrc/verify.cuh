@@ -30,7 +30,7 @@ static_assert(sizeof(RlcRecord) == 336, "record layout");
 // Two arrays of n compressed points each (the second may be null) in ONE launch, one thread per point: out = affine
 // Montgomery; status[i] set to 3/4/5 on failure (kept if already non-zero).  by_order != 0 uses the [r]P definition of
 // subgroup membership instead of the endomorphism test (unit test only).
-__global__ void __launch_bounds__(64) k_g1_decompress(const uint32_t* __restrict__ in_a, const uint32_t* __restrict__ in_b, int n,
+__global__ void __launch_bounds__(128) k_g1_decompress(const uint32_t* __restrict__ in_a, const uint32_t* __restrict__ in_b, int n,
                                                       G1Affine* __restrict__ out_a, G1Affine* __restrict__ out_b, int32_t* __restrict__ st_a,
                                                       int32_t* __restrict__ st_b, int by_order) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -175,7 +175,6 @@ __global__ void __launch_bounds__(RLC_THREADS / 2) k_rlc_s(const Fr* __restrict_
 #define RLCB_WINDOWS 16
 #define RLCB_ITEMS 1024                           // items per slice: 2048 terms, 8 per thread
 #define RLCB_PER_THREAD (2 * RLCB_ITEMS / RLCB_THREADS)
-static __device__ __noinline__ void g1_madd_ool(G1& acc, const Fp& x2, const Fp& y2) { g1_madd(acc, x2, y2); }
 
 // dig[(sel * 16 + j) * n + i] = byte j of k1 | byte j of k2 << 8, (k1, k2) = GLV halves of the canonical scalar of item i:
 // sel 0: w_i (sums A and C), sel 1: w_i z_i (sum B).  Items with a non-zero status get zero digits: they contribute nothing.
@@ -240,8 +239,8 @@ __global__ void __launch_bounds__(RLCB_THREADS, 2) k_rlc_bucket(const G1Affine* 
         const uint32_t t = sorted[q];
         G1Affine pt = pts[i0 + (int)(t >> 1)];
         if (g1a_is_inf(pt)) continue;
-        if (t & 1) { Fp b; fp_set(b, c_k.fp_beta); fp_mul(pt.x, pt.x, b); fp_neg(pt.y, pt.y); }        // Q = (beta x, -y)
-        g1_madd_ool(acc, pt.x, pt.y);
+        if (t & 1) { Fp b; fp_set(b, c_k.fp_beta); FPM(pt.x, pt.x, b); fp_neg(pt.y, pt.y); }        // Q = (beta x, -y)
+        g1_madd_c(acc, pt.x, pt.y);
     }
     __syncthreads();                               // the sort arrays are dead: their bytes become the bucket sums
     bkt[tid] = acc;
