@@ -57,7 +57,7 @@ struct kb200_setup {
     cudaStream_t stream = 0;
     G1Affine* d_bases = nullptr;     // g1_lagrange_brp, affine Montgomery   (src/kzg/setup.rs:39)
     Fr* d_roots = nullptr;           // roots_of_unity_brp, Montgomery       (src/kzg/setup.rs:41)
-    G1Affine* d_neg_g_pow = nullptr; // 2^(8w) * (-G1), w = 0..31 (verify.cuh, k_rlc_combine)
+    G1Affine* d_neg_g_pow = nullptr; // d * 2^(8w) * (-G1), w = 0..31, d = 0..255 (verify.cuh, k_rlc_combine)
     G1Affine* d_neg_g_bits = nullptr; // 2^k * (-G1), k = 0..254 (pairing.cuh, k_verify_proof_many)
     PairConsts* d_pair = nullptr;    // Miller-loop lines of [tau]_2 and G2 + Frobenius constants, device copy (pairing.cuh)
     uint4* d_table = nullptr;        // fixed-base window table (msm.cuh)
@@ -393,8 +393,8 @@ static int build_setup(kb200_setup* s, const uint8_t* g1, const uint8_t* g2, int
     // roots of unity, bit-reversed (src/kzg/setup.rs:74-75)
     CU(cudaMalloc(&s->d_roots, KB_N * sizeof(Fr)));
     LAUNCH(s, k_roots, KB_N / 256, 256, s->d_roots);
-    CU(cudaMalloc(&s->d_neg_g_pow, 32 * sizeof(G1Affine)));
-    LAUNCH(s, k_neg_g_table, 1, 32, s->d_neg_g_pow);
+    CU(cudaMalloc(&s->d_neg_g_pow, 32 * 256 * sizeof(G1Affine)));
+    LAUNCH(s, k_neg_g_table, 32, 256, s->d_neg_g_pow);
     {   // device copy of what the per-item pairing check needs (pairing.cuh): the host module's prepared lines, bit for bit
         static_assert(sizeof(PairLine) == sizeof(host::Line) && sizeof(Fp2) == sizeof(host::Fp2) && sizeof(Fp) == sizeof(host::Fp), "host and device field layouts");
         if (s->tau_prep.inf || s->g2_prep.inf || s->tau_prep.n != s->g2_prep.n || s->tau_prep.n > 68) { snprintf(g_err, sizeof g_err, "setup: degenerate G2 points"); return KB200_E_ARG; }

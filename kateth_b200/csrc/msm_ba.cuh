@@ -400,7 +400,10 @@ __device__ __forceinline__ void ba_stage_fwd(uint4* st, int c0, const BaCtx& C, 
 }
 #endif
 
-__global__ void __launch_bounds__(BA_THREADS, 4) k_msm_ba(BaArgs A) {
+#ifndef BA_MINB
+#define BA_MINB 4          // CTAs per SM the register budget is cut for (128 registers)
+#endif
+__global__ void __launch_bounds__(BA_THREADS, BA_MINB) k_msm_ba(BaArgs A) {
     static_assert(BA_UNITS == 1, "the GLV map below is applied to the accumulator of one unit");
 #if BA_STAGE
     G1* const sm = reinterpret_cast<G1*>(ba_smem);      // the tree reduction reuses the staging bytes (barriers on both sides)

@@ -338,36 +338,34 @@ __global__ void __launch_bounds__(32) k_rlc_merge(const RlcRecord* __restrict__ 
         for (int k = 0; k < 4; k++) out->err[k] = e[k];
     }
 }
-// neg_g_pow[w] = 2^(8w) * (-G1), affine, w = 0..31: fixed-base table for the [s](-G1) term of the combine step (built at setup)
-__global__ void k_neg_g_table(G1Affine* __restrict__ neg_g_pow) {
-    int w = threadIdx.x;
-    if (w >= 32) return;
+// neg_g_tab[w * 256 + d] = d * 2^(8w) * (-G1), affine, w = 0..31, d = 0..255 (d = 0: the infinity sentinel): fixed-base table for the
+// [s](-G1) term of the combine step, built at setup (768 KiB).  One thread per entry: 8w doublings, an 8-step ladder, one inversion.
+__global__ void __launch_bounds__(256) k_neg_g_table(G1Affine* __restrict__ neg_g_tab) {
+    const int w = blockIdx.x, d = threadIdx.x;
     G1Affine ng; fp_set(ng.x, c_k.g1_gen_x); fp_set(ng.y, c_k.g1_neg_gen_y);
     G1 t; g1_from_affine(t, ng);
+    g1_dbl_k(t, 8 * w);
+    G1 acc; g1_set_inf(acc);
 #pragma unroll 1
-    for (int k = 0; k < 8 * w; k++) g1_dbl(t);
-    G1Affine a; g1_to_affine(a, t);
-    neg_g_pow[w] = a;
+    for (int i = 7; i >= 0; i--) { g1_dbl(acc); if ((d >> i) & 1) g1_add(acc, t); }
+    G1Affine a; g1_to_affine(a, acc);
+    neg_g_tab[w * 256 + d] = a;
 }
 // Combine the records of all ranks into the two G1 pairing operands, as plain (non-Montgomery) affine coordinates:
 // out[0..11] = lhs.x, [12..23] = lhs.y, [24..35] = rhs.x, [36..47] = rhs.y, out[48] = lhs is infinity, out[49] = rhs is infinity,
 // out[50..53] = first error of each of the four classes over the records in rank order (0 = none).
 //   lhs = sum_g A_g        rhs = sum_g C_g + [sum_g s_g](-G1) + sum_g B_g
-// One warp: lane w multiplies the fixed point 2^(8w)(-G1) by byte w of s (8 double-and-add steps), the warp tree-sums the 32
-// terms, lane 0 adds the records, lanes 0 and 1 normalise one operand each.
-__global__ void __launch_bounds__(32) k_rlc_combine(const RlcRecord* __restrict__ recs, int nrec, const G1Affine* __restrict__ neg_g_pow,
+// One warp: lane w looks up [byte w of s] 2^(8w)(-G1) in the table, the warp tree-sums the 32 terms, lane 0 adds the records, lanes 0
+// and 1 normalise one operand each.
+__global__ void __launch_bounds__(32) k_rlc_combine(const RlcRecord* __restrict__ recs, int nrec, const G1Affine* __restrict__ neg_g_tab,
                                                     uint32_t* __restrict__ out) {
     __shared__ G1 sm[16];
     const int lane = threadIdx.x;
     Fr s; fr_zero(s);
     for (int g = 0; g < nrec; g++) { Fr t = recs[g].s; fr_add(s, s, t); }
     const uint32_t digit = (s.l[lane >> 2] >> (8 * (lane & 3))) & 0xffu;
-    G1 acc; g1_set_inf(acc);
-    {
-        G1Affine base = neg_g_pow[lane];
-#pragma unroll 1
-        for (int i = 7; i >= 0; i--) { g1_dbl(acc); if ((digit >> i) & 1) g1_madd(acc, base.x, base.y); }
-    }
+    G1 acc;
+    { G1Affine e = neg_g_tab[lane * 256 + digit]; g1_from_affine(acc, e); }
 #pragma unroll 1
     for (int stride = 16; stride >= 1; stride >>= 1) {
         if (lane >= stride && lane < 2 * stride) sm[lane - stride] = acc;
@@ -385,7 +383,9 @@ __global__ void __launch_bounds__(32) k_rlc_combine(const RlcRecord* __restrict_
         G1 A, B; g1_set_inf(A); g1_set_inf(B);
         for (int g = 0; g < nrec; g++) {
             RlcRecord r = recs[g];
-            g1_madd_signed(A, r.a, false); g1_madd_signed(B, r.b, false); g1_madd_signed(acc, r.c, false);
+            if (!g1a_is_inf(r.a)) g1_madd_c(A, r.a.x, r.a.y);
+            if (!g1a_is_inf(r.b)) g1_madd_c(B, r.b.x, r.b.y);
+            if (!g1a_is_inf(r.c)) g1_madd_c(acc, r.c.x, r.c.y);
         }
         g1_add(acc, B);
         sm[0] = A; sm[1] = acc;

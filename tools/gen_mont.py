@@ -153,9 +153,18 @@ def gen_addsub(name, n, mod):
     for k in range(n):
         opn = "add.cc.u32" if k == 0 else ("addc.cc.u32" if k < n - 1 else "addc.u32")
         s.op("%s %s, %s, %s" % (opn, s.ref("t[%d]" % k, True), s.ref("t[%d]" % k, True), s.ref("q[%d]" % k)))
+    # two forms of the correction.  KB200_SUB_PAR: u = t + p as a second chain that follows t limb by limb (it does not wait for the final
+    # borrow), then a select; default: t += (p & borrow mask), which can only start once the borrow is known.
+    s2 = Asm()
+    for k in range(n):
+        opn = "add.cc.u32" if k == 0 else ("addc.cc.u32" if k < n - 1 else "addc.u32")
+        s2.op("%s %s, %s, 0x%08x" % (opn, s2.ref("u[%d]" % k, True), s2.ref("t[%d]" % k), p[k]))
+    o += "#if defined(KB200_SUB_PAR) && KB200_SUB_PAR\n    uint32_t u[%d];\n" % n
+    o += s2.render().replace('"+r"', '"=&r"')
+    o += "    #pragma unroll\n    for (int i = 0; i < %d; i++) r[i] = bw ? u[i] : t[i];\n#else\n" % n
     o += "    uint32_t q[%d] = {%s};\n" % (n, ", ".join("bw & 0x%08xu" % x for x in p))
     o += s.render()
-    o += "    #pragma unroll\n    for (int i = 0; i < %d; i++) r[i] = t[i];\n}\n\n" % n
+    o += "    #pragma unroll\n    for (int i = 0; i < %d; i++) r[i] = t[i];\n#endif\n}\n\n" % n
     return o
 
 
