@@ -190,30 +190,26 @@ __global__ void k_challenge_range(const uint32_t* __restrict__ blobs, const uint
 #define CH2_EMPTY 3
 __device__ __forceinline__ void ch2_bar_sync(int id) { asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory"); }
 __device__ __forceinline__ void ch2_bar_arrive(int id) { asm volatile("bar.arrive %0, 64;" ::"r"(id) : "memory"); }
-// the sixteen big-endian message words of block k of  "FSBLOBVERIFY_V1_" | u128_be(4096) | blob | compress(C)
-__device__ __forceinline__ void ch2_block_words(uint32_t (&w)[16], int k, const uint4* __restrict__ bp, const uint32_t* __restrict__ cp) {
+// the sixteen big-endian message words of block k of  "FSBLOBVERIFY_V1_" | u128_be(4096) | blob | compress(C), in two steps so that
+// the producer can have the loads of block k + 1 in flight while it expands block k: the raw 16-byte pieces, then the words
+__device__ __forceinline__ void ch2_block_raw(uint4 (&v)[4], int k, const uint4* __restrict__ bp, const uint32_t* __restrict__ cp) {
+    if (k == 0) { v[0] = __ldg(bp); v[1] = __ldg(bp + 1); }
+    else if (k < 2048) { const uint4* p = bp + (4 * k - 2); v[0] = __ldg(p); v[1] = __ldg(p + 1); v[2] = __ldg(p + 2); v[3] = __ldg(p + 3); }
+    else if (k == 2048) {
+        const uint4* p = bp + (4 * 2048 - 2);
+        v[0] = __ldg(p); v[1] = __ldg(p + 1);
+        v[2] = make_uint4(cp[0], cp[1], cp[2], cp[3]); v[3] = make_uint4(cp[4], cp[5], cp[6], cp[7]);
+    } else v[0] = make_uint4(cp[8], cp[9], cp[10], cp[11]);
+}
+__device__ __forceinline__ void ch2_words4(uint32_t* w, const uint4& v) { w[0] = bswap32(v.x); w[1] = bswap32(v.y); w[2] = bswap32(v.z); w[3] = bswap32(v.w); }
+__device__ __forceinline__ void ch2_block_words(uint32_t (&w)[16], int k, const uint4 (&v)[4]) {
     if (k == 0) {
         w[0] = 0x4653424c; w[1] = 0x4f425645; w[2] = 0x52494659; w[3] = 0x5f56315f; w[4] = 0; w[5] = 0; w[6] = 0; w[7] = KB_N;
-        uint4 c0 = __ldg(bp), c1 = __ldg(bp + 1);
-        w[8] = bswap32(c0.x); w[9] = bswap32(c0.y); w[10] = bswap32(c0.z); w[11] = bswap32(c0.w);
-        w[12] = bswap32(c1.x); w[13] = bswap32(c1.y); w[14] = bswap32(c1.z); w[15] = bswap32(c1.w);
-    } else if (k < 2048) {
-        const uint4* p = bp + (4 * k - 2);
-        uint4 v0 = __ldg(p), v1 = __ldg(p + 1), v2 = __ldg(p + 2), v3 = __ldg(p + 3);
-        w[0] = bswap32(v0.x); w[1] = bswap32(v0.y); w[2] = bswap32(v0.z); w[3] = bswap32(v0.w);
-        w[4] = bswap32(v1.x); w[5] = bswap32(v1.y); w[6] = bswap32(v1.z); w[7] = bswap32(v1.w);
-        w[8] = bswap32(v2.x); w[9] = bswap32(v2.y); w[10] = bswap32(v2.z); w[11] = bswap32(v2.w);
-        w[12] = bswap32(v3.x); w[13] = bswap32(v3.y); w[14] = bswap32(v3.z); w[15] = bswap32(v3.w);
-    } else if (k == 2048) {
-        const uint4* p = bp + (4 * 2048 - 2);
-        uint4 v0 = __ldg(p), v1 = __ldg(p + 1);
-        w[0] = bswap32(v0.x); w[1] = bswap32(v0.y); w[2] = bswap32(v0.z); w[3] = bswap32(v0.w);
-        w[4] = bswap32(v1.x); w[5] = bswap32(v1.y); w[6] = bswap32(v1.z); w[7] = bswap32(v1.w);
-#pragma unroll
-        for (int q = 0; q < 8; q++) w[8 + q] = bswap32(cp[q]);
+        ch2_words4(w + 8, v[0]); ch2_words4(w + 12, v[1]);
+    } else if (k <= 2048) {
+        ch2_words4(w, v[0]); ch2_words4(w + 4, v[1]); ch2_words4(w + 8, v[2]); ch2_words4(w + 12, v[3]);
     } else {
-#pragma unroll
-        for (int q = 0; q < 4; q++) w[q] = bswap32(cp[8 + q]);
+        ch2_words4(w, v[0]);
         w[4] = 0x80000000u;
 #pragma unroll
         for (int q = 5; q < 15; q++) w[q] = 0;
@@ -233,11 +229,15 @@ __global__ void __launch_bounds__(CH2_THREADS) k_challenge_w2(const uint32_t* __
     const uint32_t* cp = comm48 + (size_t)bc * 12;
     if (role == 1) {
         // ---- producer: K[i] + w[i], i = 0..63, for every block of the range ----
+        uint4 nxt[4] = {};
+        ch2_block_raw(nxt, blk0, bp, cp);
 #pragma unroll 1
         for (int k = blk0; k < blk1; k++) {
             const int j = (k - blk0) & 1;
+            uint4 cur[4] = {nxt[0], nxt[1], nxt[2], nxt[3]};
+            if (k + 1 < blk1) ch2_block_raw(nxt, k + 1, bp, cp);       // in flight during the 48 schedule steps below
             uint32_t w[16];
-            ch2_block_words(w, k, bp, cp);
+            ch2_block_words(w, k, cur);
             if (k - blk0 >= 2) ch2_bar_sync(bar0 + CH2_EMPTY + j);
 #pragma unroll
             for (int i = 0; i < 64; i++) {
@@ -269,11 +269,17 @@ __global__ void __launch_bounds__(CH2_THREADS) k_challenge_w2(const uint32_t* __
         for (int i = 0; i < 64; i++) x[i] = kw[j][i][lane];
         if (k + 2 < blk1) ch2_bar_arrive(bar0 + CH2_EMPTY + j);
         uint32_t a = h[0], bb = h[1], c = h[2], d = h[3], e = h[4], f = h[5], g = h[6], hh = h[7];
+        // The chain of e is the critical path of a round (a is needed four rounds later): h + K + w and d + h + K + w are formed one
+        // round ahead from values that are already final, so e_new = (d + h + kw) + Sigma1(e) + Ch(e, f, g) is three dependent
+        // instructions (shift, xor, three-input add) instead of four.
+        uint32_t hx = hh + x[0], pre = d + hx;
 #pragma unroll
         for (int i = 0; i < 64; i++) {
-            const uint32_t t1 = hh + x[i] + (rotr(e, 6) ^ rotr(e, 11) ^ rotr(e, 25)) + ((e & f) ^ (~e & g));
-            const uint32_t t2 = (rotr(a, 2) ^ rotr(a, 13) ^ rotr(a, 22)) + ((a & bb) ^ (a & c) ^ (bb & c));
-            hh = g; g = f; f = e; e = d + t1; d = c; c = bb; bb = a; a = t1 + t2;
+            const uint32_t s1 = rotr(e, 6) ^ rotr(e, 11) ^ rotr(e, 25), ch = (e & f) ^ (~e & g);
+            const uint32_t en = pre + s1 + ch, t1 = hx + s1 + ch;
+            const uint32_t an = t1 + (rotr(a, 2) ^ rotr(a, 13) ^ rotr(a, 22)) + ((a & bb) ^ (a & c) ^ (bb & c));
+            hh = g; g = f; f = e; e = en; d = c; c = bb; bb = a; a = an;
+            if (i < 63) { hx = hh + x[i + 1]; pre = d + hx; }
         }
         h[0] += a; h[1] += bb; h[2] += c; h[3] += d; h[4] += e; h[5] += f; h[6] += g; h[7] += hh;
     }
