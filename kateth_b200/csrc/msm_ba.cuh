@@ -42,6 +42,9 @@ namespace kb200 {
 #ifndef BA_STAGE
 #define BA_STAGE 1
 #endif
+#ifndef BA_SPLIT_TAB
+#define BA_SPLIT_TAB 0   // 1: two instantiations of a round's loops (table operands / scratch operands)
+#endif
 #ifndef BA_SMEM_BYTES
 #define BA_STAGE_SLOTS 25
 #define BA_SMEM_BYTES (BA_STAGE ? BA_STAGE_SLOTS * BA_THREADS * 16 : 0)            // dynamic shared memory of k_msm_ba
@@ -60,6 +63,11 @@ struct BaOffset { uint32_t l[8]; };     // sum_{j < nwin-1} 2^(c-1) * 2^(c*j)
 static __device__ __noinline__ Fp fp_mulc(Fp a, Fp b) { Fp r; fp_mul(r, a, b); return r; }
 #define BA_MUL(r, a, b) r = fp_mulc(a, b)
 #define BA_SQR(r, a) r = fp_mulc(a, a)
+// BA_INLINE_MASK (experiment): bit i set = product i of the backward pass (0 dinv, 1 inv*d, 2 lambda, 3 lambda^2, 4 lambda*(x1-x3)) is inlined
+#ifndef BA_INLINE_MASK
+#define BA_INLINE_MASK 0
+#endif
+#define BA_MULX(i, r, a, b) do { if ((BA_INLINE_MASK >> (i)) & 1) fp_mul(r, a, b); else r = fp_mulc(a, b); } while (0)
 
 // g1_dbl_affine / g1_dbl / g1_madd / g1_add (g1.cuh) on the shared product.  All inlined into the kernel: nothing in
 // k_msm_ba passes a pointer to a local object to an out-of-line function, so every operand stays in registers.
@@ -273,6 +281,10 @@ __device__ __forceinline__ void ba_prefetch(const BaRef& r) {
 // plain table has one half (i1 = k); with two halves the operands of half h sit at [2*h*Kh, 2*(h+1)*Kh) and its sums land in
 // [h*Kh, (h+1)*Kh), so the halves never mix and every round halves both.  The sums are written in ascending k: slot k is
 // never an operand of a later pair.
+struct BaTabYes {}; struct BaTabNo {};     // compile-time operand source of a round (BA_SPLIT_TAB); a plain bool keeps it a run-time value
+__device__ __forceinline__ constexpr bool ba_tab_value(BaTabYes) { return true; }
+__device__ __forceinline__ constexpr bool ba_tab_value(BaTabNo) { return false; }
+__device__ __forceinline__ constexpr bool ba_tab_value(bool b) { return b; }
 __device__ __forceinline__ int ba_i1(int k, int Kh) { return k + (k >= Kh ? Kh : 0); }
 
 // Exceptional pairs (an operand at infinity, or x1 == x2) leave the hot loops through these two out-of-line functions;
@@ -433,6 +445,12 @@ __global__ void __launch_bounds__(BA_THREADS, BA_MINB) k_msm_ba(BaArgs A) {
                 const bool tab = round == 0;
                 const int K = Kh * halves;
 #if BA_STAGE
+                // The body of a round, instantiated twice when BA_SPLIT_TAB is set: round 0 reads its operands from the window table
+                // (96 contiguous bytes per point, digits decide sign and row), later rounds from the scratch slots (rows 2 KiB apart);
+                // with the source known at compile time the sixteen request addresses of a pair become one base + immediates.
+                auto stage_round = [&](auto tabc) {
+                const bool tab = ba_tab_value(tabc);
+                const int round = tab ? 0 : 1;      // (shadows the loop variable) only "round == 0" matters to the helpers
                 uint4* const st = ba_smem + tid;
                 // ---- forward (k descending): prefix products of the denominators.  The x coordinates of pairs k-1 and k-2 are on
                 // their way into the two halves of the staging column while pair k is multiplied in.
@@ -457,7 +475,11 @@ __global__ void __launch_bounds__(BA_THREADS, BA_MINB) k_msm_ba(BaArgs A) {
                             ba_stage_fwd(st, c0, C, round, k - 2, Kh, dn1, dn2);
                             if (tab && k >= 3) { const int i1 = ba_i1(k - 3, Kh); dn1 = ba_digit(C, i1); dn2 = ba_digit(C, i1 + Kh); }
                         }
+#if defined(BA_FWD_CALL) && BA_FWD_CALL
+                        BA_MUL(run, run, d);
+#else
                         fp_mul(run, run, d);
+#endif
                     }
                 }
                 Fp inv = ba_inv(run);
@@ -496,8 +518,8 @@ __global__ void __launch_bounds__(BA_THREADS, BA_MINB) k_msm_ba(BaArgs A) {
                             }
                         } else {
                             Fp dinv, t, lam, x3, y3;
-                            BA_MUL(dinv, inv, pk);
-                            BA_MUL(inv, inv, d);
+                            BA_MULX(0, dinv, inv, pk);
+                            BA_MULX(1, inv, inv, d);
                             {
                                 Fp y1, y2;
                                 { Fp r; ba_lds(r, st, 9 * b + 6); ba_cneg_nz(y1, r, (negs & 1u) != 0); }
@@ -511,16 +533,22 @@ __global__ void __launch_bounds__(BA_THREADS, BA_MINB) k_msm_ba(BaArgs A) {
                                 if (tab && k + 2 < K) ba_stage_digits(st, 2 * b, C, k + 2, Kh);
                                 negs_next = ba_stage_bwd(st, b ^ 1, C, pre, round, k + 1, Kh, dn1, dn2);
                             }
-                            BA_MUL(lam, t, dinv);
-                            BA_SQR(x3, lam);
+                            BA_MULX(2, lam, t, dinv);
+                            BA_MULX(3, x3, lam, lam);
                             { Fp x1, x2; ba_lds(x1, st, 9 * b); ba_lds(x2, st, 9 * b + 3); fp_sub(x3, x3, x1); fp_sub(x3, x3, x2); fp_sub(t, x1, x3); }
-                            BA_MUL(t, lam, t);
+                            BA_MULX(4, t, lam, t);
                             { Fp y1; ba_lds(y1, st, 9 * b + 6); fp_sub(y3, t, y1); }
                             uint4* o = pts + (size_t)k * 6 * BA_THREADS;
                             ba_st(o, x3); ba_st(o + 3 * BA_THREADS, y3);
                         }
                     }
                 }
+                };
+#if BA_SPLIT_TAB
+                if (tab) stage_round(BaTabYes{}); else stage_round(BaTabNo{});
+#else
+                stage_round(tab);
+#endif
 #else
                 // ---- forward (k descending): prefix products of the denominators.  Operands of the next pair are loaded
                 // before the product of this pair is issued, the digits of the pair after that before that.
