@@ -850,8 +850,18 @@ def test_bucket_sums_equal_ladder_sums(engine_setup):
             assert s.verify_proof(pr[:48], comm[:48], zs[:32], ys[:32]) is True
             ops.append(s.last_pairing_operands())
         assert ops[0] == ops[2] and ops[1] == ops[3]
+        # the consensus-spec challenge (weights 1, r, r^2, ... from the transcript) through both forms
+        pr, st = s.blob_proof_many(cat, comm, n)
+        s.set_batch_challenge(1)
+        spec_ops = []
+        for mode in (1, 2):
+            s.set_rlc_mode(mode)
+            assert s.verify_blob_proof_batch_concat(cat, comm, pr, n) is True
+            spec_ops.append(s.last_pairing_operands())
+        assert spec_ops[0] == spec_ops[1] and spec_ops[0] != ops[0]
     finally:
         s.set_rlc_mode(0)
+        s.set_batch_challenge(0)
 
 
 # ---------------------------------------------------------------- loader extras
