@@ -73,7 +73,7 @@ struct kb200_setup {
     // batch-affine MSM (msm_ba.cuh): 0 = automatic (batches that fill the GPU), 1 = always k_msm, 2 = always k_msm_ba
     int msm_mode = 0, ba_grid = 0, last_ba = 0;
     int rlc_mode = 0;                // sums of batch verification: 0 = automatic (buckets from RLC_BUCKET_MIN items), 1 = ladders (k_rlc), 2 = buckets (k_rlc_bucket)
-    DBuf rlc_dig, rlc_wsum;
+    DBuf rlc_dig, rlc_wsum, prodh;
     int challenge_mode = 0;          // batch-verification challenge: 0 = kateth's (parity with the reference), 1 = consensus-spec transcript
     DBuf transcript;
     unsigned int* d_counter = nullptr;
@@ -629,7 +629,7 @@ extern "C" void kb200_setup_free(kb200_setup* s) {
     for (int j = 0; j < 8; j++) if (s->ev_col[j]) cudaEventDestroy(s->ev_col[j]);
     s->sha_state.release();
     DBuf* bufs[] = {&s->blobs, &s->c48, &s->p48, &s->zy32, &s->out48, &s->out32, &s->st_blob, &s->st_a, &s->st_b, &s->status, &s->z, &s->y, &s->prod,
-                    &s->indom, &s->q, &s->partials, &s->aff_c, &s->aff_p, &s->rlc_part, &s->rlc_s, &s->rmont, &s->records, &s->combine, &s->dig, &s->scr_pts, &s->scr_pre, &s->transcript, &s->st_tmp, &s->rlc_dig, &s->rlc_wsum};
+                    &s->indom, &s->q, &s->partials, &s->aff_c, &s->aff_p, &s->rlc_part, &s->rlc_s, &s->rmont, &s->records, &s->combine, &s->dig, &s->scr_pts, &s->scr_pre, &s->transcript, &s->st_tmp, &s->rlc_dig, &s->rlc_wsum, &s->prodh};
     for (DBuf* b : bufs) b->release();
     for (cudaEvent_t e : s->prof_ev) cudaEventDestroy(e);
     delete s;
@@ -738,7 +738,15 @@ static int run_eval(kb200_setup* s, const uint32_t* d_blobs, size_t n, const int
     if (int rc = s->prod.ensure(n * sizeof(Fr))) return rc;
     if (int rc = s->indom.ensure(n * 4)) return rc;
     if (WANT_Q) if (int rc = s->q.ensure(n * (size_t)KB_BLOB_BYTES)) return rc;
-    LAUNCH(s, k_eval_prod, (unsigned)n, EV_THREADS, d_z, s->d_roots, (int)n, s->prod.as<Fr>(), s->indom.as<int32_t>());
+    static const bool halves = !(getenv("KB200_EVAL2") && atoi(getenv("KB200_EVAL2")) == 0);     // evaluation-only form in two halves (k_eval_finish2)
+    if (!WANT_Q && halves) {
+        if (int rc = s->prodh.ensure(2 * n * sizeof(Fr))) return rc;
+        LAUNCH(s, k_eval_prod, (unsigned)n, EV_THREADS, d_z, s->d_roots, (int)n, s->prod.as<Fr>(), s->indom.as<int32_t>(), s->prodh.as<Fr>());
+        LAUNCH(s, k_eval_inv, blocks(n, 32), 32, s->prod.as<Fr>(), (int)n);
+        LAUNCH(s, k_eval_finish2, (unsigned)n, EV2_THREADS, d_blobs, d_z, s->d_roots, s->prod.as<Fr>(), s->prodh.as<Fr>(), s->indom.as<int32_t>(), d_status, (int)n, d_y);
+        return 0;
+    }
+    LAUNCH(s, k_eval_prod, (unsigned)n, EV_THREADS, d_z, s->d_roots, (int)n, s->prod.as<Fr>(), s->indom.as<int32_t>(), (Fr*)nullptr);
     LAUNCH(s, k_eval_inv, blocks(n, 32), 32, s->prod.as<Fr>(), (int)n);
     LAUNCH(s, (k_eval_finish<WANT_Q>), (unsigned)n, EV_THREADS, d_blobs, d_z, s->d_roots, s->prod.as<Fr>(), s->indom.as<int32_t>(), d_status,
            (int)n, d_y, s->q.as<uint32_t>());

@@ -314,8 +314,9 @@ __device__ __forceinline__ void cta_tree_up(Fr* tree, const Fr& leaf, int tid) {
         __syncthreads();
     }
 }
+// half_out != nullptr: also the products of the factors of elements [0, 2048) and [2048, 4096) (k_eval_finish2 works in halves)
 __global__ void __launch_bounds__(EV_THREADS) k_eval_prod(const Fr* __restrict__ z_canon, const Fr* __restrict__ roots, int n,
-                                                           Fr* __restrict__ prod_out, int32_t* __restrict__ indomain_out) {
+                                                           Fr* __restrict__ prod_out, int32_t* __restrict__ indomain_out, Fr* __restrict__ half_out) {
     __shared__ Fr tree[2 * EV_THREADS];
     __shared__ int s_m;
     const int b = blockIdx.x, tid = threadIdx.x;
@@ -323,14 +324,25 @@ __global__ void __launch_bounds__(EV_THREADS) k_eval_prod(const Fr* __restrict__
     __syncthreads();
     Fr z; { Fr zc = z_canon[b]; fr_to_mont(z, zc); }
     Fr local; fr_set(local, c_k.fr_one);
+    Fr lo = local;
 #pragma unroll 1
     for (int k = 0; k < EV_PER; k++) {
         int i = k * EV_THREADS + tid;
+        if (k == EV_PER / 2) { lo = local; fr_set(local, c_k.fr_one); }       // elements below 2048 are done
         Fr d; fr_sub(d, z, roots[i]);
         if (fr_is_zero(d)) s_m = i; else fr_mul(local, local, d);
     }
+    if (half_out == nullptr) {
+        fr_mul(local, local, lo);
+        cta_tree_up(tree, local, tid);
+        if (tid == 0) { prod_out[b] = tree[1]; indomain_out[b] = s_m; }
+        return;
+    }
+    cta_tree_up(tree, lo, tid);
+    Fr p0 = tree[1];
+    __syncthreads();
     cta_tree_up(tree, local, tid);
-    if (tid == 0) { prod_out[b] = tree[1]; indomain_out[b] = s_m; }
+    if (tid == 0) { Fr p1 = tree[1], t; fr_mul(t, p0, p1); prod_out[b] = t; half_out[2 * b] = p0; half_out[2 * b + 1] = p1; indomain_out[b] = s_m; }
 }
 // phase 2: one thread per blob inverts the product (32 blobs per warp, one Fermat inversion per lane)
 __global__ void k_eval_inv(Fr* __restrict__ prod, int n) {
@@ -451,6 +463,93 @@ __global__ void __launch_bounds__(EV_THREADS, 1) k_eval_finish(const uint32_t* _
             uint4* dst = reinterpret_cast<uint4*>(q_out + ((size_t)b * KB_N + m) * 8);
             dst[0] = make_uint4(nq.l[0], nq.l[1], nq.l[2], nq.l[3]); dst[1] = make_uint4(nq.l[4], nq.l[5], nq.l[6], nq.l[7]);
         }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Evaluation only (batch verification), in two halves of 2048 elements on 256 threads: the same arithmetic as k_eval_finish<false>,
+// but two CTAs fit on an SM (128 registers x 256 threads), so the tree sweeps of one -- nine barriers with ever fewer threads at work --
+// are covered by the bulk loops of the other.  The inverse of a half's product is prod_inv * (the other half's product).
+// ---------------------------------------------------------------------------------------------------------
+#define EV2_THREADS 256
+__global__ void __launch_bounds__(EV2_THREADS, 2) k_eval_finish2(const uint32_t* __restrict__ blobs, const Fr* __restrict__ z_canon,
+                                                                const Fr* __restrict__ roots, const Fr* __restrict__ prod_inv,
+                                                                const Fr* __restrict__ half_prod, const int32_t* __restrict__ indomain,
+                                                                const int32_t* __restrict__ status, int n, Fr* __restrict__ y_out) {
+    __shared__ Fr tree[2 * EV2_THREADS];
+    const int b = blockIdx.x, tid = threadIdx.x;
+    if (status[b] != 0) return;
+    const int m = indomain[b];
+    Fr z; { Fr zc = z_canon[b]; fr_to_mont(z, zc); }
+    Fr one; fr_set(one, c_k.fr_one);
+    Fr acc; fr_zero(acc);
+#pragma unroll 1
+    for (int h = 0; h < 2; h++) {
+        Fr pre[EV_PER];
+        Fr local = one;
+#pragma unroll
+        for (int k = 0; k < EV_PER; k++) {
+            const int i = (h * EV_PER + k) * EV2_THREADS + tid;
+            Fr d; fr_sub(d, z, roots[i]);
+            pre[k] = local;
+            if (i != m) fr_mul(local, local, d);
+        }
+        // up-sweep over 256 leaves
+        tree[EV2_THREADS + tid] = local;
+        __syncthreads();
+#pragma unroll 1
+        for (int width = EV2_THREADS / 2; width >= 1; width >>= 1) {
+            if (tid < width) { Fr a = tree[2 * (width + tid)], c = tree[2 * (width + tid) + 1], r; fr_mul(r, a, c); tree[width + tid] = r; }
+            __syncthreads();
+        }
+        if (tid == 0) { Fr pi = prod_inv[b], po = half_prod[2 * b + (1 - h)], ih; fr_mul(ih, pi, po); tree[1] = ih; }
+        __syncthreads();
+#pragma unroll 1
+        for (int width = 1; width < EV2_THREADS; width <<= 1) {
+            if (tid < width) {
+                const int nd = width + tid;
+                Fr inv = tree[nd], l = tree[2 * nd], r = tree[2 * nd + 1], il, ir;
+                fr_mul(il, inv, r); fr_mul(ir, inv, l);
+                tree[2 * nd] = il; tree[2 * nd + 1] = ir;
+            }
+            __syncthreads();
+        }
+        Fr run = tree[EV2_THREADS + tid];
+        __syncthreads();
+#pragma unroll
+        for (int k = EV_PER - 1; k >= 0; k--) {
+            const int i = (h * EV_PER + k) * EV2_THREADS + tid;
+            if (i == m) continue;
+            Fr w = roots[i];
+            Fr d; fr_sub(d, z, w);
+            Fr inv; fr_mul(inv, run, pre[k]);
+            fr_mul(run, run, d);
+            Fr f; fr_load_be(f, blobs + ((size_t)b * KB_N + i) * 8);
+            Fr t; fr_mul(t, w, inv); fr_mul(t, f, t);
+            fr_add(acc, acc, t);
+        }
+    }
+    tree[tid] = acc;
+    __syncthreads();
+#pragma unroll 1
+    for (int stride = EV2_THREADS / 2; stride >= 1; stride >>= 1) {
+        if (tid < stride) { Fr a = tree[tid], c = tree[tid + stride]; fr_add(a, a, c); tree[tid] = a; }
+        __syncthreads();
+    }
+    if (tid == 0) {
+        Fr y;
+        if (m >= 0) fr_load_be(y, blobs + ((size_t)b * KB_N + m) * 8);
+        else {
+            Fr zn = z;
+#pragma unroll 1
+            for (int k = 0; k < 12; k++) fr_sqr(zn, zn);
+            fr_sub(zn, zn, one);
+            Fr ninv; fr_set(ninv, c_k.fr_ninv);
+            fr_mul(zn, zn, ninv);
+            Fr s = tree[0];
+            fr_mul(y, s, zn);
+        }
+        y_out[b] = y;
     }
 }
 
