@@ -472,11 +472,16 @@ __global__ void __launch_bounds__(EV_THREADS, 1) k_eval_finish(const uint32_t* _
 // are covered by the bulk loops of the other.  The inverse of a half's product is prod_inv * (the other half's product).
 // ---------------------------------------------------------------------------------------------------------
 #define EV2_THREADS 256
+// WANT_Q: the inverses 1/(z - w_i) are parked in the quotient's own slots (Montgomery form; a thread reads back only what it wrote, the
+// resident CTAs' 128 KiB each stay in L2) until y is known, then q_i = (y - f_i) * inv_i overwrites them (poly.rs:45-63 as in k_eval_finish).
+template <bool WANT_Q>
 __global__ void __launch_bounds__(EV2_THREADS, 2) k_eval_finish2(const uint32_t* __restrict__ blobs, const Fr* __restrict__ z_canon,
                                                                 const Fr* __restrict__ roots, const Fr* __restrict__ prod_inv,
                                                                 const Fr* __restrict__ half_prod, const int32_t* __restrict__ indomain,
-                                                                const int32_t* __restrict__ status, int n, Fr* __restrict__ y_out) {
+                                                                const int32_t* __restrict__ status, int n, Fr* __restrict__ y_out,
+                                                                uint32_t* __restrict__ q_out) {
     __shared__ Fr tree[2 * EV2_THREADS];
+    __shared__ Fr s_y;
     const int b = blockIdx.x, tid = threadIdx.x;
     if (status[b] != 0) return;
     const int m = indomain[b];
@@ -524,6 +529,10 @@ __global__ void __launch_bounds__(EV2_THREADS, 2) k_eval_finish2(const uint32_t*
             Fr d; fr_sub(d, z, w);
             Fr inv; fr_mul(inv, run, pre[k]);
             fr_mul(run, run, d);
+            if (WANT_Q) {
+                uint4* dst = reinterpret_cast<uint4*>(q_out + ((size_t)b * KB_N + i) * 8);
+                dst[0] = make_uint4(inv.l[0], inv.l[1], inv.l[2], inv.l[3]); dst[1] = make_uint4(inv.l[4], inv.l[5], inv.l[6], inv.l[7]);
+            }
             Fr f; fr_load_be(f, blobs + ((size_t)b * KB_N + i) * 8);
             Fr t; fr_mul(t, w, inv); fr_mul(t, f, t);
             fr_add(acc, acc, t);
@@ -550,6 +559,40 @@ __global__ void __launch_bounds__(EV2_THREADS, 2) k_eval_finish2(const uint32_t*
             fr_mul(y, s, zn);
         }
         y_out[b] = y;
+        if (WANT_Q) s_y = y;
+    }
+    if (!WANT_Q) return;
+    __syncthreads();
+    const Fr y = s_y;
+    Fr qsum; fr_zero(qsum);
+#pragma unroll 1
+    for (int k = 0; k < 2 * EV_PER; k++) {
+        const int i = k * EV2_THREADS + tid;
+        if (i == m) continue;
+        uint4* slot = reinterpret_cast<uint4*>(q_out + ((size_t)b * KB_N + i) * 8);
+        const uint4 v0 = slot[0], v1 = slot[1];
+        Fr inv; inv.l[0] = v0.x; inv.l[1] = v0.y; inv.l[2] = v0.z; inv.l[3] = v0.w; inv.l[4] = v1.x; inv.l[5] = v1.y; inv.l[6] = v1.z; inv.l[7] = v1.w;
+        Fr f; fr_load_be(f, blobs + ((size_t)b * KB_N + i) * 8);
+        Fr q; fr_sub(q, y, f); fr_mul(q, q, inv);            // canonical
+        slot[0] = make_uint4(q.l[0], q.l[1], q.l[2], q.l[3]); slot[1] = make_uint4(q.l[4], q.l[5], q.l[6], q.l[7]);
+        if (m >= 0) { Fr t; fr_mul(t, q, roots[i]); fr_add(qsum, qsum, t); }
+    }
+    if (m >= 0) {          // uniform across the CTA
+        __syncthreads();
+        tree[tid] = qsum;
+        __syncthreads();
+#pragma unroll 1
+        for (int stride = EV2_THREADS / 2; stride >= 1; stride >>= 1) {
+            if (tid < stride) { Fr a = tree[tid], c = tree[tid + stride]; fr_add(a, a, c); tree[tid] = a; }
+            __syncthreads();
+        }
+        if (tid == 0) {
+            const uint32_t e = brp12((uint32_t)m);
+            Fr winv = roots[brp12((KB_N - e) & (KB_N - 1))];
+            Fr q = tree[0], nq; fr_mul(q, q, winv); fr_neg(nq, q);
+            uint4* dst = reinterpret_cast<uint4*>(q_out + ((size_t)b * KB_N + m) * 8);
+            dst[0] = make_uint4(nq.l[0], nq.l[1], nq.l[2], nq.l[3]); dst[1] = make_uint4(nq.l[4], nq.l[5], nq.l[6], nq.l[7]);
+        }
     }
 }
 
