@@ -3,7 +3,8 @@
 //
 // Replaces (file:line in /root/reference):
 //   P1::decompress                    src/bls.rs:505-531        (k_g1_decompress)
-//   Setup::verify_proof_batch         src/kzg/setup.rs:115-161  (k_batch_r, k_rlc, k_rlc_finish, k_rlc_combine) up to,
+//   Setup::verify_proof_batch         src/kzg/setup.rs:115-161  (k_batch_r; k_rlc or k_rlc_scalars / k_rlc_bucket / k_rlc_shift; k_rlc_s,
+//                                                               k_rlc_finish, k_rlc_combine) up to,
 //                                                               but not including, the two-pairing check (host)
 //   Setup::verify_proof_inner         src/kzg/setup.rs:84-94    (same kernels in "raw" mode, weights = 1)
 // kateth's quirks are reproduced: r = SHA-256("RCKZGBATCH___V1_" | u128_be(4096) | u128_be(n)) mod r depends on n
