@@ -255,8 +255,9 @@ int kb200_set_profiling(kb200_setup* s, int on);
  * CTA per blob; XYZZ accumulation with several CTAs per blob below that), 1 = always XYZZ (k_msm), 2 = always batch-affine
  * (k_msm_ba).  Both produce the same bytes; the switch exists for the parity tests and for profiling. */
 int kb200_set_msm_mode(kb200_setup* s, int mode);
-/* How a shard of a batch check forms its three sums (verify.cuh): 0 = automatic (bucket method from 512 items, one 128-step ladder per
- * term below), 1 = always ladders (k_rlc), 2 = always buckets (k_rlc_bucket).  Same record bytes; for the parity tests and profiling.
+/* How a shard of a batch check forms its three sums (verify.cuh): 0 = automatic (the bucket method: measured faster at every batch size,
+ * a single verify_proof included), 1 = one 128-step ladder per term (k_rlc), 2 = buckets (k_rlc_bucket).  Same record bytes; for the
+ * parity tests and profiling.
  * Environment: KB200_RLC_MODE. */
 int kb200_set_rlc_mode(kb200_setup* s, int mode);
 int kb200_get_msm_profile(kb200_setup* s, double* ms_total, uint64_t* launches, uint64_t* msms);
