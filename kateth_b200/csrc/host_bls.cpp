@@ -3,6 +3,9 @@
 #include "constants.cuh"
 #include <string.h>
 #include <mutex>
+#ifdef KB200_HOST_SELFTEST
+#include <chrono>
+#endif
 
 namespace kb200 { namespace host {
 
@@ -367,6 +370,16 @@ bool verify_pairings(const G1A& a1, const G2Prepared& q1, const G1A& b1, const G
 }
 
 #ifdef KB200_HOST_SELFTEST
+// build_ab / tools harness only: nanoseconds per dependent Fp product
+double selftest_fmul_ns(int iters) {
+    init();
+    Fp a = R2_, b = R2_;
+    auto t0 = std::chrono::steady_clock::now();
+    for (int i = 0; i < iters; i++) fmul(a, a, b);
+    double ns = std::chrono::duration<double, std::nano>(std::chrono::steady_clock::now() - t0).count() / iters;
+    volatile uint64_t sink = a.l[0]; (void)sink;
+    return ns;
+}
 // build_ab harness only: the cyclotomic squaring against the generic one on an element of the cyclotomic subgroup
 bool selftest_cyclotomic(const G1A& a1, const G2Prepared& q1) {
     init();

@@ -6,7 +6,7 @@
 #include <chrono>
 #include <cstdio>
 using namespace kb200::host;
-namespace kb200 { namespace host { bool selftest_cyclotomic(const G1A&, const G2Prepared&); } }
+namespace kb200 { namespace host { bool selftest_cyclotomic(const G1A&, const G2Prepared&); double selftest_fmul_ns(int); } }
 static void parse(const char* h, uint32_t* l) { for (int i = 0; i < 12; i++) { unsigned v; sscanf(h + 8 * (11 - i), "%8x", &v); l[i] = v; } }
 static G1A point(const char* x, const char* y) {
     uint32_t lx[12], ly[12]; parse(x, lx); parse(y, ly);
@@ -24,6 +24,7 @@ int main() {
     auto t0 = std::chrono::steady_clock::now();
     bool ok = true;
     for (int i = 0; i < N; i++) ok = verify_pairings(g1, p, g1, p) && ok;
+    printf("fmul_ns %.1f\n", selftest_fmul_ns(2000000));
     printf("ms_per_check %.3f\n", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count() / N);
     return (cyc && same && !diff && ok) ? 0 : 1;
 }
